@@ -1,0 +1,144 @@
+"""Device context + the batched preprocess surface (additive to the reference's per-file API).
+
+PyTorch is used for device memory and streams only; every number is produced by the CUDA
+kernels behind the C ABI (``include/njucloud_b200.h``)."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+_default_ctx = {}
+
+
+class Context:
+    """One nc_ctx: bound to one device, not thread-safe (one per thread / process)."""
+
+    def __init__(self, device=0):
+        if not torch.cuda.is_available():
+            raise RuntimeError("no CUDA device: njucloud-b200 has no CPU fallback")
+        self.device = int(device)
+        h = C.c_void_p()
+        _lib.check(None, _lib.lib().nc_init(self.device, C.byref(h)))
+        self.handle = h
+        self.tdev = torch.device("cuda", self.device)
+
+    def close(self):
+        if getattr(self, "handle", None):
+            _lib.lib().nc_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.tdev).cuda_stream)
+
+    @property
+    def launches(self):
+        return int(_lib.lib().nc_launch_count(self.handle))
+
+    # ---------------------------------------------------------------- train-side chain (P2-P4)
+    def resize_gray_norm(self, src, out_u8=None, out_f32=None, want_u8=True, want_f32=True):
+        """src: uint8 tensor [N,H,W,3] (BGR, as cv2.imread) or [N,H,W] / [N,H,W,1].
+
+        CUDA tensor -> nc_pp_resize_gray_norm; CPU tensor (pinned or not) ->
+        nc_pp_resize_gray_norm_host.  Returns (u8[N,28,28] | None, f32[N,784] | None) on device.
+        Stands in for preprocess.resize + imread(,0) + DataSet normalise
+        (apps/preprocess/preprocess.py:28-30,40; construct_distribute.py:503-504)."""
+        if src.dtype != torch.uint8:
+            raise ValueError("src must be uint8")
+        if src.dim() == 3:
+            src = src.unsqueeze(-1)
+        if src.dim() != 4:
+            raise ValueError("src must be [N,H,W,C]")
+        n, h, w, c = src.shape
+        if not src[0].is_contiguous() if n else False:
+            raise ValueError("each picture must be contiguous HWC")
+        stride = src.stride(0) if n > 1 else h * w * c
+        if want_u8 and out_u8 is None:
+            out_u8 = torch.empty((n, 28, 28), dtype=torch.uint8, device=self.tdev)
+        if want_f32 and out_f32 is None:
+            out_f32 = torch.empty((n, 784), dtype=torch.float32, device=self.tdev)
+        p_u8 = C.c_void_p(out_u8.data_ptr()) if out_u8 is not None else None
+        p_f32 = C.c_void_p(out_f32.data_ptr()) if out_f32 is not None else None
+        L = _lib.lib()
+        if src.is_cuda:
+            rc = L.nc_pp_resize_gray_norm(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, stride, 0,
+                                          p_u8, p_f32, self._stream())
+        else:
+            staged = C.c_int(0)
+            rc = L.nc_pp_resize_gray_norm_host(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, stride, 0,
+                                               p_u8, p_f32, C.byref(staged), self._stream())
+        _lib.check(self.handle, rc)
+        return out_u8, out_f32
+
+    # ---------------------------------------------------------------- predict-side chain (P5)
+    def predict_chain(self, src, channel_order="RGB", compat=False, want_small20=False):
+        """src: uint8 CUDA tensor [N,H,W,3] or [N,H,W] ('L').  Returns (f32[N,784], status[N] int32
+        (1 where the reference raises IndexError; only meaningful with compat), small20 | None).
+        Stands in for construct_inference.py:312-330."""
+        if src.dtype != torch.uint8 or not src.is_cuda:
+            raise ValueError("src must be a uint8 CUDA tensor")
+        if src.dim() == 3:
+            src = src.unsqueeze(-1)
+        n, h, w, c = src.shape
+        stride = src.stride(0) if n > 1 else h * w * c
+        out = torch.empty((n, 784), dtype=torch.float32, device=self.tdev)
+        status = torch.zeros((n,), dtype=torch.int32, device=self.tdev)
+        small = torch.empty((n, 20, 20), dtype=torch.uint8, device=self.tdev) if want_small20 else None
+        order = {"RGB": 0, "BGR": 1}[channel_order]
+        rc = _lib.lib().nc_pp_predict_chain(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, stride, order,
+                                            1 if compat else 0, C.c_void_p(out.data_ptr()),
+                                            C.c_void_p(small.data_ptr()) if small is not None else None,
+                                            C.c_void_p(status.data_ptr()), self._stream())
+        _lib.check(self.handle, rc)
+        return out, status, small
+
+    # ---------------------------------------------------------------- the 14 ops (P6-P19)
+    def op(self, op_id, imgs, v1=None, v2=None, draws=None, out=None):
+        """imgs: uint8 CUDA tensor [N,28,28]; one reference op applied to every picture."""
+        if imgs.dtype != torch.uint8 or not imgs.is_cuda or tuple(imgs.shape[1:]) != (28, 28):
+            raise ValueError("imgs must be a uint8 CUDA tensor [N,28,28]")
+        imgs = imgs.contiguous()
+        n = imgs.shape[0]
+        if out is None:
+            out = torch.empty_like(imgs)
+        is_int = (1 if isinstance(v1, (int, np.integer)) and not isinstance(v1, bool) else 0) | \
+                 (2 if isinstance(v2, (int, np.integer)) and not isinstance(v2, bool) else 0)
+        dptr, per = None, 0
+        if draws is not None:
+            d = np.ascontiguousarray(np.asarray(draws, np.float64).reshape(n, -1))
+            per = d.shape[1]
+            dptr = d.ctypes.data_as(C.c_void_p)
+        rc = _lib.lib().nc_pp_op(self.handle, int(op_id), C.c_void_p(imgs.data_ptr()), C.c_void_p(out.data_ptr()), n,
+                                 float(0.0 if v1 is None else v1), float(0.0 if v2 is None else v2), is_int,
+                                 dptr, per, self._stream())
+        _lib.check(self.handle, rc)
+        return out
+
+    def normalise(self, imgs_u8):
+        imgs_u8 = imgs_u8.contiguous()
+        n = imgs_u8.shape[0]
+        out = torch.empty((n, imgs_u8.numel() // max(n, 1)), dtype=torch.float32, device=self.tdev)
+        rc = _lib.lib().nc_pp_normalise(self.handle, C.c_void_p(imgs_u8.data_ptr()), imgs_u8.numel(),
+                                        C.c_void_p(out.data_ptr()), self._stream())
+        _lib.check(self.handle, rc)
+        return out
+
+
+def default_context(device=None):
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+    if device not in _default_ctx:
+        _default_ctx[device] = Context(device)
+    return _default_ctx[device]
+
+
+def preprocess_batch(src, device=None):
+    """Batched train-side chain: decoded uploads [N,H,W,3] uint8 (BGR) -> (u8[N,28,28], f32[N,784])."""
+    return default_context(device).resize_gray_norm(src)

@@ -1,0 +1,69 @@
+// Internal declarations shared by the .cu files of libnjucloud_b200 (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string>
+#include <vector>
+#include <map>
+#include <utility>
+
+#include "../../include/njucloud_b200.h"
+
+struct nc_dev_table {  // a small coefficient table resident in device memory, cached per shape
+    void* dptr = nullptr;
+    size_t bytes = 0;
+    std::vector<unsigned char> host;  // host copy of the table header
+};
+
+struct nc_ctx {
+    int device = 0;
+    int sm_count = 148;
+    int64_t launches = 0;
+    std::string err;
+    // PIL antialias tables keyed by (in_size, out_size)
+    std::map<std::pair<int, int>, nc_dev_table> pil_tables;
+    // reusable device workspace (grown on demand, never shrunk)
+    void* ws = nullptr;
+    size_t ws_bytes = 0;
+    // small pinned host staging buffer for host_draws etc.
+    void* pinned = nullptr;
+    size_t pinned_bytes = 0;
+};
+
+int nc_set_error(nc_ctx* ctx, int code, const char* fmt, ...);
+int nc_ws_reserve(nc_ctx* ctx, size_t bytes);       // ctx->ws valid for >= bytes afterwards
+int nc_pinned_reserve(nc_ctx* ctx, size_t bytes);
+
+#define NC_CUDA(ctx, call)                                                                     \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess)                                                                \
+            return nc_set_error((ctx), NC_ECUDA, "%s failed: %s (%s:%d)", #call,               \
+                                cudaGetErrorString(e__), __FILE__, __LINE__);                  \
+    } while (0)
+
+#define NC_LAUNCH_CHECK(ctx)                                                                   \
+    do {                                                                                       \
+        (ctx)->launches++;                                                                     \
+        cudaError_t e__ = cudaGetLastError();                                                  \
+        if (e__ != cudaSuccess)                                                                \
+            return nc_set_error((ctx), NC_ECUDA, "kernel launch failed: %s (%s:%d)",           \
+                                cudaGetErrorString(e__), __FILE__, __LINE__);                  \
+    } while (0)
+
+// ---- host-side coefficient tables (pp_tables.cpp; compiled with -ffp-contract=off) ----------
+struct CvCubicAxis {      // OpenCV INTER_CUBIC, one axis, dst == 28
+    int ofs[28][4];       // clamped source index of the 4 taps
+    short coef[28][4];    // round(c * 2048)
+};
+void nc_cv_cubic_axis(int src, int dst, CvCubicAxis* out);
+
+struct PilAxisHost {      // Pillow BICUBIC antialias tables for one axis
+    int out_size = 0, ksize = 0;
+    std::vector<int> xmin, cnt;   // [out]
+    std::vector<int> kk;          // [out][ksize], 22-bit fixed point
+};
+void nc_pil_bicubic_axis(int in_size, int out_size, PilAxisHost* out);
+std::vector<int> nc_gaussian_kernel_q8(int k);

@@ -1,0 +1,191 @@
+// Train-side preprocess chain, fused: cubic resize (OpenCV arithmetic) -> BGR2GRAY -> *1/255.
+//
+// Replaces, for a batch of decoded uploads resident in HBM:
+//   cv2.resize(im1,(28,28),interpolation=cv2.INTER_CUBIC)      apps/preprocess/preprocess.py:29
+//   gray conversion of cv2.imread(dir,0)                        apps/preprocess/preprocess.py:40
+//   images.astype(float32) * (1/255)      apps/construction/util/construct_distribute.py:503-504
+//
+// One CTA per picture.  A non-antialiased cubic resize touches only 4x4 source pixels per
+// output pixel (28*28*16*C bytes of a 2.36 MB upload), so the kernel is a gather: it is bound by
+// DRAM sectors and load issue, not by streaming bandwidth.  Stage 1 computes the horizontal pass
+// for the 112 (dy,tap) source rows into shared memory as exact int32; stage 2 the vertical pass
+// (float32 for the first 80 interleaved elements of a row -- OpenCV's 128-bit SIMD body -- and
+// integer for the tail, see oracle/pp_restate.py:cv_resize_cubic_u8); stage 3 gray + normalise.
+#include "nc_internal.h"
+
+namespace {
+
+struct TrainTabs {
+    CvCubicAxis x, y;
+};
+
+constexpr int kThreads = 256;
+
+template <int C>
+__global__ void __launch_bounds__(kThreads)
+train_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h, int w,
+                   const __grid_constant__ TrainTabs tabs, uint8_t* __restrict__ out_u8,
+                   float* __restrict__ out_f32, int identity) {
+    constexpr int E = 28 * C;               // interleaved elements per output row
+    constexpr int NSIMD = (E / 8) * 8;      // OpenCV v_int16x8 body
+    __shared__ int hp[112][E];
+    __shared__ uint8_t col[28][E];
+    __shared__ int s_xofs[28][4];
+    __shared__ int s_xcoef[28][4];
+    __shared__ int s_yofs[28][4];
+    __shared__ int s_ycoef[28][4];
+
+    const int tid = threadIdx.x;
+    const uint8_t* base = src + (long long)blockIdx.x * img_stride;
+
+    if (!identity) {
+        for (int i = tid; i < 112; i += kThreads) {
+            s_xofs[i >> 2][i & 3] = tabs.x.ofs[i >> 2][i & 3] * C;
+            s_xcoef[i >> 2][i & 3] = tabs.x.coef[i >> 2][i & 3];
+            s_yofs[i >> 2][i & 3] = tabs.y.ofs[i >> 2][i & 3];
+            s_ycoef[i >> 2][i & 3] = tabs.y.coef[i >> 2][i & 3];
+        }
+        __syncthreads();
+
+        // ---- stage 1: horizontal pass, HResizeCubic<uchar,int,short>
+        const long long row_bytes = (long long)w * C;
+        for (int idx = tid; idx < 112 * 28; idx += kThreads) {
+            const int slot = idx / 28, dx = idx - slot * 28;
+            const uint8_t* rp = base + (long long)s_yofs[slot >> 2][slot & 3] * row_bytes;
+            int acc[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) acc[c] = 0;
+            unsigned char px[4][C];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const uint8_t* p = rp + s_xofs[dx][t];
+#pragma unroll
+                for (int c = 0; c < C; ++c) px[t][c] = __ldg(p + c);
+            }
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int a = s_xcoef[dx][t];
+#pragma unroll
+                for (int c = 0; c < C; ++c) acc[c] += (int)px[t][c] * a;
+            }
+#pragma unroll
+            for (int c = 0; c < C; ++c) hp[slot][dx * C + c] = acc[c];
+        }
+        __syncthreads();
+
+        // ---- stage 2: vertical pass, VResizeCubic<uchar,int,short,FixedPtCast<22>,VResizeCubicVec_32s8u>
+        const float scale = 1.0f / (2048.0f * 2048.0f);
+        for (int idx = tid; idx < 28 * E; idx += kThreads) {
+            const int dy = idx / E, e = idx - dy * E;
+            const int S0 = hp[dy * 4 + 0][e], S1 = hp[dy * 4 + 1][e];
+            const int S2 = hp[dy * 4 + 2][e], S3 = hp[dy * 4 + 3][e];
+            const int b0 = s_ycoef[dy][0], b1 = s_ycoef[dy][1], b2 = s_ycoef[dy][2], b3 = s_ycoef[dy][3];
+            int v;
+            if (e < NSIMD) {
+                // v_round(f(S0)*b0 + (f(S1)*b1 + (f(S2)*b2 + f(S3)*b3))), separate mul / add
+                const float f0 = __fmul_rn((float)b0, scale), f1 = __fmul_rn((float)b1, scale);
+                const float f2 = __fmul_rn((float)b2, scale), f3 = __fmul_rn((float)b3, scale);
+                float t = __fmul_rn(__int2float_rn(S3), f3);
+                t = __fadd_rn(__fmul_rn(__int2float_rn(S2), f2), t);
+                t = __fadd_rn(__fmul_rn(__int2float_rn(S1), f1), t);
+                t = __fadd_rn(__fmul_rn(__int2float_rn(S0), f0), t);
+                v = __float2int_rn(t);
+            } else {
+                // 32-bit wrap-around arithmetic exactly as the C code (int)
+                const int sum = S0 * b0 + S1 * b1 + S2 * b2 + S3 * b3;
+                v = (sum + (1 << 21)) >> 22;
+            }
+            v = v < 0 ? 0 : (v > 255 ? 255 : v);
+            col[dy][e] = (uint8_t)v;
+        }
+        __syncthreads();
+    }
+
+    // ---- stage 3: BGR2GRAY (cv2 4.13: 15-bit coefficients) and float32 normalise
+    const float inv255 = (float)(1.0 / 255.0);
+    for (int idx = tid; idx < 784; idx += kThreads) {
+        int g;
+        if (C == 3) {
+            int b, gg, r;
+            if (identity) {
+                const uint8_t* p = base + idx * 3;
+                b = __ldg(p); gg = __ldg(p + 1); r = __ldg(p + 2);
+            } else {
+                const uint8_t* p = &col[0][0] + idx * 3;
+                b = p[0]; gg = p[1]; r = p[2];
+            }
+            g = (3735 * b + 19235 * gg + 9798 * r + (1 << 14)) >> 15;
+        } else {
+            g = identity ? (int)__ldg(base + idx) : (int)(&col[0][0])[idx];
+        }
+        if (out_u8) out_u8[(long long)blockIdx.x * 784 + idx] = (uint8_t)g;
+        if (out_f32) out_f32[(long long)blockIdx.x * 784 + idx] = __fmul_rn((float)g, inv255);
+    }
+}
+
+}  // namespace
+
+static int launch_train_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
+                              int64_t img_stride, uint8_t* out_u8, float* out_f32, cudaStream_t st) {
+    TrainTabs tabs;
+    const int identity = (h == 28 && w == 28) ? 1 : 0;
+    if (!identity) {
+        nc_cv_cubic_axis(w, 28, &tabs.x);
+        nc_cv_cubic_axis(h, 28, &tabs.y);
+    } else {
+        memset(&tabs, 0, sizeof(tabs));
+    }
+    if (c == 3)
+        train_chain_kernel<3><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity);
+    else
+        train_chain_kernel<1><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity);
+    NC_LAUNCH_CHECK(ctx);
+    return NC_OK;
+}
+
+static int check_train_args(nc_ctx* ctx, const void* src, int n, int h, int w, int c, int64_t img_stride,
+                            int mode, const void* o1, const void* o2) {
+    if (!ctx) return nc_set_error(nullptr, NC_EINVAL, "ctx is NULL");
+    if (n < 0 || h <= 0 || w <= 0) return nc_set_error(ctx, NC_EINVAL, "bad shape n=%d h=%d w=%d", n, h, w);
+    if (c != 1 && c != 3) return nc_set_error(ctx, NC_EINVAL, "channels must be 1 or 3, got %d", c);
+    if (img_stride < (int64_t)h * w * c) return nc_set_error(ctx, NC_EINVAL, "img_stride %lld < h*w*c", (long long)img_stride);
+    if (mode != 0) return nc_set_error(ctx, NC_EUNSUPPORTED, "resize mode %d (only 0 = OpenCV-native arithmetic)", mode);
+    if (n > 0 && !src) return nc_set_error(ctx, NC_EINVAL, "src is NULL");
+    if (!o1 && !o2) return nc_set_error(ctx, NC_EINVAL, "both outputs are NULL");
+    return NC_OK;
+}
+
+extern "C" int nc_pp_resize_gray_norm(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
+                                      int64_t img_stride, int mode, uint8_t* out_u8, float* out_f32,
+                                      void* stream) {
+    int rc = check_train_args(ctx, src, n, h, w, c, img_stride, mode, out_u8, out_f32);
+    if (rc != NC_OK) return rc;
+    if (n == 0) return NC_OK;
+    NC_CUDA(ctx, cudaSetDevice(ctx->device));
+    return launch_train_chain(ctx, src, n, h, w, c, img_stride, out_u8, out_f32, (cudaStream_t)stream);
+}
+
+extern "C" int nc_pp_resize_gray_norm_host(nc_ctx* ctx, const uint8_t* host_src, int n, int h, int w, int c,
+                                           int64_t img_stride, int mode, uint8_t* out_u8, float* out_f32,
+                                           int* staged, void* stream) {
+    int rc = check_train_args(ctx, host_src, n, h, w, c, img_stride, mode, out_u8, out_f32);
+    if (rc != NC_OK) return rc;
+    if (staged) *staged = 0;
+    if (n == 0) return NC_OK;
+    NC_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaPointerAttributes attr;
+    cudaError_t e = cudaPointerGetAttributes(&attr, host_src);
+    if (e != cudaSuccess) { cudaGetLastError(); attr.type = cudaMemoryTypeUnregistered; }
+    if (attr.type == cudaMemoryTypeHost && attr.devicePointer != nullptr) {
+        // pinned + mapped: gather the taps straight from host memory over PCIe (zero copy)
+        return launch_train_chain(ctx, (const uint8_t*)attr.devicePointer, n, h, w, c, img_stride, out_u8, out_f32, st);
+    }
+    // pageable: stage the whole batch through the workspace
+    const size_t bytes = (size_t)n * (size_t)img_stride;
+    rc = nc_ws_reserve(ctx, bytes);
+    if (rc != NC_OK) return rc;
+    NC_CUDA(ctx, cudaMemcpyAsync(ctx->ws, host_src, bytes, cudaMemcpyHostToDevice, st));
+    if (staged) *staged = 1;
+    return launch_train_chain(ctx, (const uint8_t*)ctx->ws, n, h, w, c, img_stride, out_u8, out_f32, st);
+}

@@ -1,0 +1,186 @@
+/*
+ * njucloud_b200.h -- C ABI of the B200-native hot path behind NJUCloud (view-sonic/Cloud-Server).
+ *
+ * The reference is pure Python; its arithmetic sits in third-party wheels (OpenCV, Pillow,
+ * TensorFlow 1.x).  This library replaces those calls for ONE path only: the batched image
+ * preprocess chain of apps/preprocess + construct_inference.py, and forward / backward / update of
+ * the CNN graphs that construct_distribute.py builds.  Each entry point cites the reference
+ * call it stands in for (paths relative to the reference root).
+ *
+ * Conventions
+ *  - plain C, no exceptions cross the boundary; every function returns NC_OK (0) or a negative
+ *    NC_E* code; nc_last_error(ctx) returns the message of the last failure on that ctx
+ *    (ctx == NULL: the last failure of a call that had no ctx, thread-local).
+ *  - the caller allocates and owns every data buffer.  Pointers are DEVICE pointers unless the
+ *    parameter name starts with host_.  The library owns only its handles, small coefficient
+ *    tables, workspaces and the flat parameter / gradient / optimizer-state buffers of a net.
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls are
+ *    asynchronous on that stream unless stated otherwise.
+ *  - a ctx is bound to one device; it is not thread-safe: one ctx per thread / process.
+ *    Data parallel training = one process per GPU, gradients exchanged by the host binding
+ *    (torch.distributed / NCCL) on the flat gradient buffer between nc_net_backward and
+ *    nc_net_apply.
+ */
+#ifndef NJUCLOUD_B200_H
+#define NJUCLOUD_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NC_OK            0
+#define NC_EINVAL       -1   /* bad argument (the Python shim raises ValueError)            */
+#define NC_ECUDA        -2   /* a CUDA runtime call or kernel launch failed                  */
+#define NC_ENOMEM       -3   /* device or host allocation failed                            */
+#define NC_EUNSUPPORTED -4   /* valid in the reference but not implemented by this library  */
+#define NC_ECONFIG      -5   /* malformed --config JSON / unknown layer (reference: assert) */
+#define NC_ECV          -6   /* the reference's cv2 call would raise cv2.error here          */
+
+typedef struct nc_ctx nc_ctx;
+typedef struct nc_net nc_net;
+
+/* ---- context -------------------------------------------------------------------------- */
+int nc_version(void);
+int nc_init(int device, nc_ctx** out);
+int nc_destroy(nc_ctx* ctx);
+const char* nc_last_error(nc_ctx* ctx);
+/* number of kernels this ctx has launched so far (bench.py's gpu_launches) */
+int64_t nc_launch_count(nc_ctx* ctx);
+
+/* ---- P2+P3+P4: train-side preprocess chain ---------------------------------------------
+ * Replaces, fused and batched, for n decoded uploads src[n][h][w][c] (uint8, c == 3 BGR as
+ * cv2.imread returns it, or c == 1):
+ *   cv2.resize(im1,(28,28),interpolation=cv2.INTER_CUBIC)     apps/preprocess/preprocess.py:29
+ *   the BGR->gray of cv2.imread(dir, 0) on the resized picture apps/preprocess/preprocess.py:40
+ *   images.astype(float32) * (1/255)    apps/construction/util/construct_distribute.py:503-504
+ * img_stride = bytes between consecutive images (>= h*w*c).  mode 0 = OpenCV's own arithmetic
+ * (cv2 4.13 with IPP disabled: int32 horizontal pass, float32 SIMD-body / integer-tail
+ * vertical pass) -- bit exact.  Other modes: NC_EUNSUPPORTED.
+ * out_u8[n][28][28] and/or out_f32[n][784] (either may be NULL). */
+int nc_pp_resize_gray_norm(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
+                           int64_t img_stride, int mode, uint8_t* out_u8, float* out_f32,
+                           void* stream);
+
+/* Same chain with the source in HOST memory (what the REST view has after decoding).  If
+ * host_src is pinned (cudaHostAlloc / cudaHostRegister) the kernel gathers the 4x4 taps it
+ * needs straight over PCIe; pageable memory is staged through the ctx workspace.  Outputs are
+ * device pointers.  Synchronous with respect to host_src on return only if the function says
+ * so via *staged (1 = a staging copy was made and host_src may be reused immediately). */
+int nc_pp_resize_gray_norm_host(nc_ctx* ctx, const uint8_t* host_src, int n, int h, int w, int c,
+                                int64_t img_stride, int mode, uint8_t* out_u8, float* out_f32,
+                                int* staged, void* stream);
+
+/* ---- P5: predict-side preprocess chain -------------------------------------------------
+ * Replaces apps/construction/util/construct_inference.py:312-330 for n decoded pictures:
+ *   Image.open(f).convert('L')        (:312)  rgb2l fixed point; c == 1 is taken as 'L'
+ *   im.resize((20,20))                (:315)  Pillow BICUBIC, antialiased, 8bpc two-pass
+ *   > 150 -> 254 on a 28x28 zero canvas at offset 4, /255.0   (:317-330)
+ * channel_order: 0 = RGB (PIL), 1 = BGR (cv2 buffers).  compat != 0 reproduces the reference's
+ * `arr[bizar+i][bizar+j] = 220` statement (:325-326) including its IndexError: status[i] is set
+ * to 1 where the reference raises (out_f32 row i is then all zero), else 0.  status may be NULL
+ * when compat == 0.  out_small20 (nullable) receives the 20x20 'L' picture after the resize. */
+int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
+                        int64_t img_stride, int channel_order, int compat, float* out_f32,
+                        uint8_t* out_small20, int* status, void* stream);
+
+/* ---- P6-P19: the 14 per-picture ops on 28x28 8-bit gray --------------------------------
+ * in/out: [n][28][28] uint8 device buffers (in == out allowed).  One call = one op applied
+ * to every picture, as PreprocessView.execute's loop does (apps/preprocess/views.py:118-126).
+ * v1 / v2 are the op's value1 / value2 (views.py:123-126).  v_is_int: bit0 = v1 was a Python
+ * int, bit1 = v2 was (only adjust_brightness_contrast cares).  host_draws: the uniform [0,1)
+ * doubles the reference draws on the host for NC_OP_SALT_PEPPER (4*m per picture, m =
+ * int(784*percent), in call order: preprocess.py:163-165, :174-176); NULL otherwise. */
+enum nc_op {
+    NC_OP_FLIP_UP_DOWN = 0,        /* preprocess.py:33-45   cv2.flip(img, 0)                  */
+    NC_OP_FLIP_LEFT_RIGHT = 1,     /* preprocess.py:48-60   cv2.flip(img, 1)                  */
+    NC_OP_TRANSPOSE_IMAGE = 2,     /* preprocess.py:63-75   cv2.flip(img, -1)                 */
+    NC_OP_BRIGHTNESS_CONTRAST = 3, /* preprocess.py:78-99   p*alpha+beta stored into uint8    */
+    NC_OP_MEAN_FILTER = 4,         /* preprocess.py:123-129 cv2.blur(img,(k,k))               */
+    NC_OP_GAUSSIAN_BLUR = 5,       /* preprocess.py:132-138 cv2.GaussianBlur(img,(k,k),0)     */
+    NC_OP_MEDIAN_FILTER = 6,       /* preprocess.py:141-148 cv2.medianBlur(img,k)             */
+    NC_OP_NL_DENOISE = 7,          /* preprocess.py:151-157 cv2.fastNlMeansDenoising(,h,7,21) */
+    NC_OP_SALT_PEPPER = 8,         /* preprocess.py:160-188                                   */
+    NC_OP_EQUALIZE_HIST = 9,       /* preprocess.py:191-197 cv2.equalizeHist                  */
+    NC_OP_CLAHE = 10,              /* preprocess.py:200-207 cv2.createCLAHE().apply           */
+    NC_OP_ERODE = 11,              /* preprocess.py:210-217 cv2.erode(img, ones(k,k))         */
+    NC_OP_DILATE = 12              /* preprocess.py:220-227 cv2.dilate(img, ones(k,k))        */
+    /* random_brightness_contrast (preprocess.py:102-120) draws alpha/beta on the host with
+     * Python's `random` and is then NC_OP_BRIGHTNESS_CONTRAST.                               */
+};
+int nc_pp_op(nc_ctx* ctx, int op_id, const uint8_t* in, uint8_t* out, int n, double v1, double v2,
+             int v_is_int, const double* host_draws, int64_t draws_per_image, void* stream);
+
+/* Host-only introspection of the per-shape coefficient tables the kernels consume (no GPU
+ * needed; used by the CPU tests to check the host logic against the oracle).
+ *  nc_pp_cubic_table: OpenCV INTER_CUBIC taps for one axis src -> 28 (preprocess.py:29):
+ *                     ofs[28*4] clamped source indices, coef[28*4] = round(c*2048).
+ *  nc_pp_pil_table:   Pillow BICUBIC antialias taps for one axis in_size -> out_size
+ *                     (construct_inference.py:315): xmin[out], cnt[out], kk[out*ksize] 22-bit
+ *                     fixed point; returns ksize (or a negative error); kk may be NULL to query.
+ *  nc_pp_gaussian_q8: cv2.GaussianBlur(k,k,0) 8-bit fixed-point kernel (preprocess.py:134). */
+int nc_pp_cubic_table(int src, int32_t* ofs, int16_t* coef);
+int nc_pp_pil_table(int in_size, int out_size, int32_t* xmin, int32_t* cnt, int32_t* kk, int kk_capacity);
+int nc_pp_gaussian_q8(int k, int32_t* q);
+
+/* [n][28][28] uint8 -> [n][784] float32, x * float32(1/255)
+ * (DataSet.__init__, construct_distribute.py:503-504). */
+int nc_pp_normalise(nc_ctx* ctx, const uint8_t* in, int64_t count, float* out, void* stream);
+
+/* ---- CNN graph: construct / forward / backward / update --------------------------------
+ * nc_net_create replaces cnn() + get_net() (construct_distribute.py:208-281, identical copy in
+ * construct_inference.py:53-279): it interprets net_config_json = the value of
+ * config["net_config"] ({"middle_layer":[...]}) with the defaults of :222-250 and appends the
+ * implicit dense->classes output layer (:262-264).  The reference fixes the input at
+ * 28x28x1 (:216) and classes at 10 (:261-264); they are parameters here.
+ * Parameters live in ONE flat float32 buffer in variable-creation order (conv: HWIO filter then
+ * bias if any; norm: scale then offset; connect: W[in][out] then b; output W then b).
+ * Initial values follow weight_variable/bias_variable (:57-87) from `seed`; parity tests
+ * overwrite them with nc_net_set_params. */
+int nc_net_create(nc_ctx* ctx, const char* net_config_json, int in_h, int in_w, int in_c,
+                  int classes, uint64_t seed, nc_net** out);
+int nc_net_destroy(nc_net* net);
+int64_t nc_net_param_count(nc_net* net);
+/* number of parameter tensors and, for tensor i, its element offset / size in the flat buffer */
+int nc_net_tensor_count(nc_net* net);
+int nc_net_tensor_info(nc_net* net, int i, int64_t* offset, int64_t* size, int* ndim, int64_t dims[4]);
+/* device pointers to the library-owned flat buffers (float32[param_count]) */
+float* nc_net_params(nc_net* net);
+float* nc_net_grads(nc_net* net);
+int nc_net_set_params(nc_net* net, const float* host_params);   /* synchronous H2D */
+int nc_net_get_params(nc_net* net, float* host_params);         /* synchronous D2H */
+/* math: 0 = fp32 SIMT everywhere, 1 = TF32 tcgen05 tensor-core tiles for conv/dense with fp32
+ * accumulate (default) */
+int nc_net_set_math(nc_net* net, int math);
+
+/* logits[n][classes] = net(x[n][in_h*in_w*in_c])   -- sess.run(y_conv / argmax)
+ * (construct_distribute.py:408, construct_inference.py:340-342) */
+int nc_net_forward(nc_net* net, const float* x, int n, float* logits, void* stream);
+/* labels[n] = argmax(logits, 1)  (construct_inference.py:335) */
+int nc_net_predict(nc_net* net, const float* x, int n, int32_t* labels, void* stream);
+/* forward + loss (loss_function :285-298; loss_name 0 = entropy, 1 = mse) + backward into the
+ * flat gradient buffer; loss_out (device float, nullable) receives the batch-mean loss and
+ * correct_out (device int32, nullable) the number of argmax hits (accuracy :381-382).
+ * grad_scale multiplies dLoss (1/world for data parallel ranks holding n of world*n rows). */
+int nc_net_backward(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name,
+                    float grad_scale, float* loss_out, int32_t* correct_out, void* stream);
+/* optimizer update on the flat buffers (ApplyAdagrad / ApplyGradientDescent / ApplyAdam):
+ * opt 0 = Adagrad (what runs: AdagradOptimizer(1e-4), construct_distribute.py:372-373;
+ * accumulator starts at 0.1, no epsilon), 1 = SGD (optimizer_function :309), 2 = Adam (TF1
+ * defaults b1=.9 b2=.999 eps=1e-8; offered by options.py:28).  Increments global_step. */
+int nc_net_apply(nc_net* net, int opt, float lr, void* stream);
+/* nc_net_backward + nc_net_apply: one sess.run(train_op) (construct_distribute.py:413) */
+int nc_net_train_step(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name,
+                      int opt, float lr, float* loss_out, int32_t* correct_out, void* stream);
+int64_t nc_net_global_step(nc_net* net);
+/* optimizer state (Adagrad accumulator / Adam m,v) for checkpoints: float32[slots*param_count] */
+int nc_net_state_slots(nc_net* net, int opt);
+int nc_net_get_state(nc_net* net, int opt, float* host_state);
+int nc_net_set_state(nc_net* net, int opt, const float* host_state, int64_t global_step);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NJUCLOUD_B200_H */
