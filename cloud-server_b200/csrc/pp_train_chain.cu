@@ -151,7 +151,7 @@ static int check_train_args(nc_ctx* ctx, const void* src, int n, int h, int w, i
     if (img_stride < (int64_t)h * w * c) return nc_set_error(ctx, NC_EINVAL, "img_stride %lld < h*w*c", (long long)img_stride);
     if (mode != 0) return nc_set_error(ctx, NC_EUNSUPPORTED, "resize mode %d (only 0 = OpenCV-native arithmetic)", mode);
     if (n > 0 && !src) return nc_set_error(ctx, NC_EINVAL, "src is NULL");
-    if (!o1 && !o2) return nc_set_error(ctx, NC_EINVAL, "both outputs are NULL");
+    if (n > 0 && !o1 && !o2) return nc_set_error(ctx, NC_EINVAL, "both outputs are NULL");
     return NC_OK;
 }
 
