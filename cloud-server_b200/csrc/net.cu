@@ -1,0 +1,709 @@
+// CNN graph construction, forward, backward and optimizer update behind the C ABI.
+//
+// Replaces what apps/construction/util/construct_distribute.py asks TensorFlow to do:
+//   cnn()/get_net()  :208-281  -> nc_net_create (same JSON, same defaults, same variable order)
+//   sess.run(y_conv / accuracy) :406-408, :416-417 -> nc_net_forward / nc_net_predict
+//   AdagradOptimizer(1e-4).minimize(loss) + sess.run(train_op) :372-373, :413 -> nc_net_train_step
+// (identical graph code in construct_inference.py:53-279, argmax at :335).
+// Layout: activations NHWC, conv filters HWIO, dense weights [in][out]; all parameters in one
+// flat fp32 buffer, gradients and optimizer state in matching flat buffers.
+#include "nc_internal.h"
+#include "net_kernels.cuh"
+#include <cmath>
+#include <cstring>
+#include <cstdlib>
+#include <memory>
+
+using namespace nck;
+
+// ------------------------------------------------------------------------------------------------
+// minimal JSON (objects, arrays, strings, numbers, true/false/null) -- enough for --config
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct JVal {
+    enum T { NUL, BOOL, NUM, STR, ARR, OBJ } t = NUL;
+    double num = 0; bool b = false; std::string s;
+    std::vector<JVal> arr;
+    std::vector<std::pair<std::string, JVal>> obj;
+    const JVal* get(const char* k) const {
+        for (auto& kv : obj) if (kv.first == k) return &kv.second;
+        return nullptr;
+    }
+};
+struct JParser {
+    const char* p; const char* e; std::string err;
+    void ws() { while (p < e && (*p == ' ' || *p == '\n' || *p == '\t' || *p == '\r')) ++p; }
+    bool fail(const char* m) { if (err.empty()) err = m; return false; }
+    bool parse(JVal& v) {
+        ws();
+        if (p >= e) return fail("unexpected end of JSON");
+        if (*p == '{') {
+            v.t = JVal::OBJ; ++p; ws();
+            if (p < e && *p == '}') { ++p; return true; }
+            for (;;) {
+                ws(); JVal k;
+                if (p >= e || *p != '"' || !str(k.s)) return fail("expected object key");
+                ws(); if (p >= e || *p != ':') return fail("expected ':'"); ++p;
+                JVal c; if (!parse(c)) return false;
+                v.obj.emplace_back(k.s, std::move(c));
+                ws(); if (p < e && *p == ',') { ++p; continue; }
+                if (p < e && *p == '}') { ++p; return true; }
+                return fail("expected ',' or '}'");
+            }
+        }
+        if (*p == '[') {
+            v.t = JVal::ARR; ++p; ws();
+            if (p < e && *p == ']') { ++p; return true; }
+            for (;;) {
+                JVal c; if (!parse(c)) return false;
+                v.arr.push_back(std::move(c));
+                ws(); if (p < e && *p == ',') { ++p; continue; }
+                if (p < e && *p == ']') { ++p; return true; }
+                return fail("expected ',' or ']'");
+            }
+        }
+        if (*p == '"') { v.t = JVal::STR; return str(v.s); }
+        if (!strncmp(p, "true", 4)) { v.t = JVal::BOOL; v.b = true; p += 4; return true; }
+        if (!strncmp(p, "false", 5)) { v.t = JVal::BOOL; v.b = false; p += 5; return true; }
+        if (!strncmp(p, "null", 4)) { v.t = JVal::NUL; p += 4; return true; }
+        char* end = nullptr;
+        v.num = strtod(p, &end);
+        if (end == p) return fail("bad JSON value");
+        v.t = JVal::NUM; p = end; return true;
+    }
+    bool str(std::string& out) {
+        ++p;
+        while (p < e && *p != '"') {
+            if (*p == '\\' && p + 1 < e) {
+                ++p;
+                switch (*p) {
+                    case 'n': out += '\n'; break; case 't': out += '\t'; break;
+                    case 'u': out += '?'; p += 4; break;   // non-ASCII escapes do not matter for layer names
+                    default: out += *p;
+                }
+                ++p;
+            } else out += *p++;
+        }
+        if (p >= e) return fail("unterminated string");
+        ++p; return true;
+    }
+};
+
+// Python-ish coercions the reference relies on (json numbers may arrive as strings from the UI)
+bool jnum(const JVal* v, double* out) {
+    if (!v) return false;
+    if (v->t == JVal::NUM) { *out = v->num; return true; }
+    if (v->t == JVal::STR) { char* e = nullptr; double d = strtod(v->s.c_str(), &e); if (e != v->s.c_str()) { *out = d; return true; } }
+    return false;
+}
+bool jpair(const JVal* v, int* a, int* b) {
+    if (!v || v->t != JVal::ARR || v->arr.size() < 2) return false;
+    double x, y;
+    if (!jnum(&v->arr[0], &x) || !jnum(&v->arr[1], &y)) return false;
+    *a = (int)x; *b = (int)y; return true;
+}
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+enum LKind { L_CONV = 0, L_POOL, L_ACT, L_CONNECT, L_NORM };
+enum InitKind { INIT_ZERO = 0, INIT_NORM, INIT_XAVIER, INIT_CONST };
+
+struct Layer {
+    int kind = 0;
+    int ih = 0, iw = 0, ic = 0, oh = 0, ow = 0, oc = 0;     // spatial shapes (dense: 1 x 1 x features)
+    int64_t in_size = 0, out_size = 0;                     // floats per sample
+    int fh = 0, fw = 0, sh = 1, sw = 1, pt = 0, pl = 0;
+    int act = 0; float slope = 0.2f; float eps = 1e-3f;
+    int64_t w_off = -1, b_off = -1;                         // into the flat parameter buffer
+    int64_t out_off = 0;                                    // activation arena offset (floats per sample)
+    int64_t aux_off = -1;                                   // pool argmax (bytes/sample) or norm xhat (floats/sample)
+    int64_t stat_off = -1;                                  // norm: inv-std per channel (floats, absolute)
+    bool in_is_4d = true;
+};
+
+struct TensorInfo { int64_t off, size; int ndim; int64_t dims[4]; int init; double arg; };
+
+struct nc_net {
+    nc_ctx* ctx = nullptr;
+    int in_h = 28, in_w = 28, in_c = 1, classes = 10;
+    std::vector<Layer> layers;
+    std::vector<TensorInfo> tensors;
+    int64_t nparams = 0;
+    float *params = nullptr, *grads = nullptr;
+    float *st_adagrad = nullptr, *st_adam = nullptr;
+    int64_t global_step = 0;
+    int math = 0;
+    // activation arena, sized for `cap` samples
+    int cap = 0;
+    int64_t act_floats = 0, aux_bytes = 0, stat_floats = 0, max_out = 0;
+    float* act = nullptr; unsigned char* aux = nullptr; float* stat = nullptr;
+    float *dbuf0 = nullptr, *dbuf1 = nullptr;
+    float* ws = nullptr; size_t ws_bytes = 0;              // split-K partial sums (scratch)
+    std::string err;
+};
+
+static int net_err(nc_net* net, int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    if (net && net->ctx) net->ctx->err = buf;
+    else nc_set_error(nullptr, code, "%s", buf);
+    return code;
+}
+#define NET_CUDA(net, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) \
+    return net_err((net), NC_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
+#define NET_LAUNCH(net) do { (net)->ctx->launches++; cudaError_t e__ = cudaGetLastError(); if (e__ != cudaSuccess) \
+    return net_err((net), NC_ECUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
+
+static void same_pad(int n, int k, int s, bool same, int* out, int* before) {
+    // tf.nn.conv2d / max_pool: SAME out = ceil(n/s), pad = max((out-1)*s+k-n, 0), before = pad/2
+    if (same) { *out = (n + s - 1) / s; int tot = (*out - 1) * s + k - n; if (tot < 0) tot = 0; *before = tot / 2; }
+    else { *out = (n - k + 1 + s - 1) / s; *before = 0; }
+}
+
+static int grid_for(long long count, int sm) {
+    long long b = (count + 255) / 256;
+    const long long cap = (long long)sm * 16;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+// ------------------------------------------------------------------------------------------------
+// construction
+// ------------------------------------------------------------------------------------------------
+static int add_tensor(nc_net* net, int ndim, const int64_t* dims, int init, double arg, int64_t* off) {
+    TensorInfo t{};
+    t.off = net->nparams; t.ndim = ndim; t.size = 1; t.init = init; t.arg = arg;
+    for (int i = 0; i < 4; ++i) { t.dims[i] = i < ndim ? dims[i] : 1; if (i < ndim) t.size *= dims[i]; }
+    *off = t.off;
+    net->nparams += t.size;
+    net->tensors.push_back(t);
+    return NC_OK;
+}
+
+static int build_layers(nc_net* net, const JVal& cfg) {
+    const JVal* mid = cfg.get("middle_layer");
+    if (!mid || mid->t != JVal::ARR) return net_err(net, NC_ECONFIG, "KeyError: net_config has no \"middle_layer\" list");
+    int h = net->in_h, w = net->in_w, c = net->in_c;
+    bool is4d = true;
+    int64_t feat = (int64_t)h * w * c;
+    for (size_t li = 0; li < mid->arr.size(); ++li) {
+        const JVal& L = mid->arr[li];
+        const JVal* name = L.get("layer");
+        if (L.t != JVal::OBJ || !name || name->t != JVal::STR)
+            return net_err(net, NC_ECONFIG, "KeyError: middle_layer[%zu] has no \"layer\" name", li);
+        Layer y;
+        y.in_is_4d = is4d;
+        y.ih = h; y.iw = w; y.ic = c; y.in_size = feat;
+        if (name->s == "conv") {
+            if (!is4d) return net_err(net, NC_ECONFIG, "middle_layer[%zu]: conv after a dense layer (TF: rank error)", li);
+            const JVal* f = L.get("filter");
+            double d0, d1, d2;
+            if (!f || f->t != JVal::ARR || f->arr.size() < 3 || !jnum(&f->arr[0], &d0) || !jnum(&f->arr[1], &d1) || !jnum(&f->arr[2], &d2))
+                return net_err(net, NC_ECONFIG, "KeyError: conv layer %zu needs \"filter\": [h, w, out]", li);
+            y.kind = L_CONV; y.fh = (int)d0; y.fw = (int)d1; y.oc = (int)d2;
+            if (y.fh <= 0 || y.fw <= 0 || y.oc <= 0) return net_err(net, NC_ECONFIG, "conv layer %zu: bad filter", li);
+            jpair(L.get("stride"), &y.sh, &y.sw);
+            if (y.sh <= 0 || y.sw <= 0) return net_err(net, NC_ECONFIG, "conv layer %zu: bad stride", li);
+            bool same = true;
+            if (const JVal* p = L.get("padding")) {
+                if (p->t == JVal::STR && p->s == "VALID") same = false;
+                else if (!(p->t == JVal::STR && p->s == "SAME")) return net_err(net, NC_ECONFIG, "conv layer %zu: padding must be SAME or VALID", li);
+            }
+            int init = INIT_NORM;
+            if (const JVal* p = L.get("init")) {
+                if (p->t == JVal::STR && p->s == "zero") init = INIT_ZERO;
+                else if (p->t == JVal::STR && p->s == "norm") init = INIT_NORM;
+                else if (p->t == JVal::STR && p->s == "xavier") init = INIT_XAVIER;
+                else return net_err(net, NC_ECONFIG, "AssertionError: %s is not a legal init (weight_variable :76)", p->t == JVal::STR ? p->s.c_str() : "?");
+            }
+            // isBias: True unless the JSON value is the string "False" (construct_distribute.py:228)
+            bool bias = false;
+            if (const JVal* p = L.get("isBias")) bias = !(p->t == JVal::STR && p->s == "False");
+            double bias_c = 0.1, stddev = 0.1;
+            jnum(L.get("bias_constant"), &bias_c);
+            jnum(L.get("stddev_norm"), &stddev);
+            same_pad(h, y.fh, y.sh, same, &y.oh, &y.pt);
+            same_pad(w, y.fw, y.sw, same, &y.ow, &y.pl);
+            if (y.oh <= 0 || y.ow <= 0) return net_err(net, NC_ECONFIG, "conv layer %zu: empty output", li);
+            const int64_t wd[4] = {y.fh, y.fw, c, y.oc};
+            add_tensor(net, 4, wd, init, stddev, &y.w_off);
+            if (bias) { const int64_t bd[1] = {y.oc}; add_tensor(net, 1, bd, INIT_CONST, bias_c, &y.b_off); }
+            h = y.oh; w = y.ow; c = y.oc; feat = (int64_t)h * w * c;
+        } else if (name->s == "pool") {
+            if (!is4d) return net_err(net, NC_ECONFIG, "middle_layer[%zu]: pool after a dense layer (TF: rank error)", li);
+            y.kind = L_POOL; y.fh = 2; y.fw = 2; y.sh = 2; y.sw = 2;
+            jpair(L.get("kernel"), &y.fh, &y.fw);
+            jpair(L.get("stride"), &y.sh, &y.sw);
+            if (y.fh <= 0 || y.fw <= 0 || y.sh <= 0 || y.sw <= 0 || y.fh * y.fw > 255) return net_err(net, NC_ECONFIG, "pool layer %zu: bad kernel/stride", li);
+            bool same = true;
+            if (const JVal* p = L.get("padding")) same = !(p->t == JVal::STR && p->s == "VALID");
+            same_pad(h, y.fh, y.sh, same, &y.oh, &y.pt);
+            same_pad(w, y.fw, y.sw, same, &y.ow, &y.pl);
+            if (y.oh <= 0 || y.ow <= 0) return net_err(net, NC_ECONFIG, "pool layer %zu: empty output", li);
+            y.oc = c; h = y.oh; w = y.ow; feat = (int64_t)h * w * c;
+        } else if (name->s == "active") {
+            y.kind = L_ACT; y.act = ACT_SIGMOID;   // default sigmoid (:242)
+            if (const JVal* p = L.get("active_func")) {
+                if (p->t == JVal::STR && p->s == "relu") y.act = ACT_RELU;
+                else if (p->t == JVal::STR && p->s == "sigmoid") y.act = ACT_SIGMOID;
+                else if (p->t == JVal::STR && p->s == "leaky_relu") y.act = ACT_LEAKY;
+                else return net_err(net, NC_ECONFIG, "AssertionError: %s is not a legal activation (active :152)", p->t == JVal::STR ? p->s.c_str() : "?");
+            }
+            y.slope = 0.2f;
+            if (const JVal* p = L.get("param")) { double s; if (p->t == JVal::ARR && !p->arr.empty() && jnum(&p->arr[0], &s)) y.slope = (float)s; }
+            y.oh = h; y.ow = w; y.oc = c;
+        } else if (name->s == "connect") {
+            y.kind = L_CONNECT;
+            double hid = 512; jnum(L.get("hidden"), &hid);
+            if (hid < 1) return net_err(net, NC_ECONFIG, "connect layer %zu: bad hidden", li);
+            y.oh = 1; y.ow = 1; y.oc = (int)hid;
+            const int64_t wd[2] = {feat, (int64_t)hid}; add_tensor(net, 2, wd, INIT_NORM, 0.1, &y.w_off);
+            const int64_t bd[1] = {(int64_t)hid}; add_tensor(net, 1, bd, INIT_CONST, 0.1, &y.b_off);
+            is4d = false; h = 1; w = 1; c = (int)hid; feat = c;
+        } else if (name->s == "norm") {
+            y.kind = L_NORM;
+            double eps = 1e-3; jnum(L.get("epsilon"), &eps); y.eps = (float)eps;
+            y.oh = h; y.ow = w; y.oc = c;
+            const int64_t d[1] = {c};
+            add_tensor(net, 1, d, INIT_CONST, 1.0, &y.w_off);   // scale
+            add_tensor(net, 1, d, INIT_CONST, 0.0, &y.b_off);   // offset
+        } else {
+            continue;   // unknown names fall through the reference's if/elif chain (:219-250)
+        }
+        y.out_size = feat;
+        net->layers.push_back(y);
+    }
+    // implicit output layer (:253-264).  The reference reshapes `x` instead of `last` when the last
+    // middle layer is 4-D (:257), which only type-checks when H*W*C == 784 and then ignores the whole
+    // net; this library flattens `last` (the evident intent) -- see DESIGN.md "known divergences".
+    Layer o;
+    o.kind = L_CONNECT; o.in_is_4d = is4d; o.ih = h; o.iw = w; o.ic = c; o.in_size = feat;
+    o.oh = 1; o.ow = 1; o.oc = net->classes; o.out_size = net->classes;
+    const int64_t wd[2] = {feat, net->classes}; add_tensor(net, 2, wd, INIT_NORM, 0.1, &o.w_off);
+    const int64_t bd[1] = {net->classes}; add_tensor(net, 1, bd, INIT_CONST, 0.1, &o.b_off);
+    net->layers.push_back(o);
+    // arena offsets
+    int64_t act = 0, aux = 0, stat = 0, mx = (int64_t)net->in_h * net->in_w * net->in_c;
+    for (auto& L : net->layers) {
+        L.out_off = act; act += L.out_size;
+        if (L.kind == L_POOL) { L.aux_off = aux; aux += L.out_size; }
+        if (L.kind == L_NORM) { L.aux_off = act; act += L.out_size; L.stat_off = stat; stat += L.oc; }
+        if (L.out_size > mx) mx = L.out_size;
+        if (L.in_size > mx) mx = L.in_size;
+    }
+    net->act_floats = act; net->aux_bytes = aux; net->stat_floats = stat; net->max_out = mx;
+    return NC_OK;
+}
+
+// splitmix64 + Box-Muller; truncated normal = resample beyond 2 sigma (tf.truncated_normal)
+static inline uint64_t splitmix(uint64_t& s) {
+    uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; return z ^ (z >> 31);
+}
+static inline double uni(uint64_t& s) { return ((splitmix(s) >> 11) + 0.5) * (1.0 / 9007199254740992.0); }
+static double trunc_normal(uint64_t& s) {
+    for (;;) {
+        const double u1 = uni(s), u2 = uni(s);
+        const double r = std::sqrt(-2.0 * std::log(u1));
+        const double a = r * std::cos(6.283185307179586 * u2);
+        if (std::fabs(a) <= 2.0) return a;
+        const double b = r * std::sin(6.283185307179586 * u2);
+        if (std::fabs(b) <= 2.0) return b;
+    }
+}
+
+static void free_net(nc_net* net) {
+    if (!net) return;
+    cudaFree(net->params); cudaFree(net->grads); cudaFree(net->st_adagrad); cudaFree(net->st_adam);
+    cudaFree(net->act); cudaFree(net->aux); cudaFree(net->stat); cudaFree(net->dbuf0); cudaFree(net->dbuf1); cudaFree(net->ws);
+    delete net;
+}
+
+extern "C" int nc_net_create(nc_ctx* ctx, const char* net_config_json, int in_h, int in_w, int in_c, int classes,
+                             uint64_t seed, nc_net** out) {
+    if (!ctx) return nc_set_error(nullptr, NC_EINVAL, "ctx is NULL");
+    if (!out || !net_config_json) return nc_set_error(ctx, NC_EINVAL, "NULL argument");
+    *out = nullptr;
+    if (in_h <= 0 || in_w <= 0 || in_c <= 0 || classes <= 0) return nc_set_error(ctx, NC_EINVAL, "bad input shape");
+    JParser jp{net_config_json, net_config_json + strlen(net_config_json), ""};
+    JVal cfg;
+    if (!jp.parse(cfg) || cfg.t != JVal::OBJ) return nc_set_error(ctx, NC_ECONFIG, "ValueError: net_config is not a JSON object (%s)", jp.err.c_str());
+    const JVal* root = cfg.get("net_config") ? cfg.get("net_config") : &cfg;   // accept the whole --config too
+    nc_net* net = new (std::nothrow) nc_net();
+    if (!net) return nc_set_error(ctx, NC_ENOMEM, "out of host memory");
+    net->ctx = ctx; net->in_h = in_h; net->in_w = in_w; net->in_c = in_c; net->classes = classes;
+    int rc = build_layers(net, *root);
+    if (rc != NC_OK) { delete net; return rc; }
+    cudaSetDevice(ctx->device);
+    const size_t pb = (size_t)net->nparams * sizeof(float);
+    if (cudaMalloc(&net->params, pb) != cudaSuccess || cudaMalloc(&net->grads, pb) != cudaSuccess) {
+        cudaGetLastError(); free_net(net); return nc_set_error(ctx, NC_ENOMEM, "cudaMalloc of %zu parameter bytes failed", pb);
+    }
+    cudaMemset(net->grads, 0, pb);
+    if (net->stat_floats) cudaMalloc(&net->stat, net->stat_floats * sizeof(float));
+    // initial values (weight_variable / bias_variable :57-87)
+    std::vector<float> host((size_t)net->nparams);
+    uint64_t s = seed ? seed : 0x243F6A8885A308D3ull;
+    for (auto& t : net->tensors) {
+        float* p = host.data() + t.off;
+        if (t.init == INIT_CONST) for (int64_t i = 0; i < t.size; ++i) p[i] = (float)t.arg;
+        else if (t.init == INIT_ZERO) for (int64_t i = 0; i < t.size; ++i) p[i] = 0.0f;
+        else {
+            double sd = t.arg;
+            if (t.init == INIT_XAVIER) sd = t.arg * 1.0 / (double)(t.dims[1] * t.dims[2] * t.dims[3]);   // shape[1]*shape[2]*shape[3] (:72)
+            for (int64_t i = 0; i < t.size; ++i) p[i] = (float)(trunc_normal(s) * sd);
+        }
+    }
+    if (cudaMemcpy(net->params, host.data(), pb, cudaMemcpyHostToDevice) != cudaSuccess) { free_net(net); return nc_set_error(ctx, NC_ECUDA, "parameter upload failed"); }
+    *out = net;
+    return NC_OK;
+}
+
+extern "C" int nc_net_destroy(nc_net* net) { if (net) { cudaSetDevice(net->ctx->device); free_net(net); } return NC_OK; }
+extern "C" int64_t nc_net_param_count(nc_net* net) { return net ? net->nparams : 0; }
+extern "C" int nc_net_tensor_count(nc_net* net) { return net ? (int)net->tensors.size() : 0; }
+extern "C" int nc_net_tensor_info(nc_net* net, int i, int64_t* offset, int64_t* size, int* ndim, int64_t dims[4]) {
+    if (!net || i < 0 || i >= (int)net->tensors.size()) return nc_set_error(net ? net->ctx : nullptr, NC_EINVAL, "tensor index out of range");
+    const TensorInfo& t = net->tensors[i];
+    if (offset) *offset = t.off;
+    if (size) *size = t.size;
+    if (ndim) *ndim = t.ndim;
+    if (dims) for (int k = 0; k < 4; ++k) dims[k] = t.dims[k];
+    return NC_OK;
+}
+extern "C" float* nc_net_params(nc_net* net) { return net ? net->params : nullptr; }
+extern "C" float* nc_net_grads(nc_net* net) { return net ? net->grads : nullptr; }
+extern "C" int nc_net_set_params(nc_net* net, const float* host_params) {
+    if (!net || !host_params) return nc_set_error(net ? net->ctx : nullptr, NC_EINVAL, "NULL argument");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    NET_CUDA(net, cudaMemcpy(net->params, host_params, (size_t)net->nparams * sizeof(float), cudaMemcpyHostToDevice));
+    return NC_OK;
+}
+extern "C" int nc_net_get_params(nc_net* net, float* host_params) {
+    if (!net || !host_params) return nc_set_error(net ? net->ctx : nullptr, NC_EINVAL, "NULL argument");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    NET_CUDA(net, cudaMemcpy(host_params, net->params, (size_t)net->nparams * sizeof(float), cudaMemcpyDeviceToHost));
+    return NC_OK;
+}
+extern "C" int nc_net_set_math(nc_net* net, int math) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (math != 0 && math != 1) return net_err(net, NC_EINVAL, "math must be 0 (fp32 SIMT) or 1 (TF32 tensor cores)");
+    net->math = math;
+    return NC_OK;
+}
+extern "C" int64_t nc_net_global_step(nc_net* net) { return net ? net->global_step : 0; }
+
+// ------------------------------------------------------------------------------------------------
+// buffers
+// ------------------------------------------------------------------------------------------------
+static int reserve_batch(nc_net* net, int n) {
+    if (n <= net->cap) return NC_OK;
+    cudaFree(net->act); cudaFree(net->aux); cudaFree(net->dbuf0); cudaFree(net->dbuf1);
+    net->act = nullptr; net->aux = nullptr; net->dbuf0 = net->dbuf1 = nullptr; net->cap = 0;
+    const size_t a = (size_t)net->act_floats * n * sizeof(float);
+    const size_t d = (size_t)net->max_out * n * sizeof(float);
+    if (cudaMalloc(&net->act, a ? a : 4) != cudaSuccess || cudaMalloc(&net->aux, net->aux_bytes ? (size_t)net->aux_bytes * n : 4) != cudaSuccess ||
+        cudaMalloc(&net->dbuf0, d) != cudaSuccess || cudaMalloc(&net->dbuf1, d) != cudaSuccess) {
+        cudaGetLastError();
+        return net_err(net, NC_ENOMEM, "activation arena for batch %d (%zu + 2*%zu bytes) does not fit", n, a, d);
+    }
+    net->cap = n;
+    return NC_OK;
+}
+static int reserve_ws(nc_net* net, size_t bytes) {
+    if (bytes <= net->ws_bytes) return NC_OK;
+    cudaFree(net->ws); net->ws = nullptr; net->ws_bytes = 0;
+    bytes = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+    if (cudaMalloc(&net->ws, bytes) != cudaSuccess) { cudaGetLastError(); return net_err(net, NC_ENOMEM, "split-K workspace of %zu bytes", bytes); }
+    net->ws_bytes = bytes;
+    return NC_OK;
+}
+static inline float* act_ptr(nc_net* net, const Layer& L) { return net->act + L.out_off * net->cap; }
+
+// ------------------------------------------------------------------------------------------------
+// GEMM dispatch (SIMT path), with deterministic split-K through the workspace
+// ------------------------------------------------------------------------------------------------
+template <bool AKF, bool BNF, class AF, class BF>
+static int run_gemm(nc_net* net, int M, int N, int K, AF A, BF B, float* C, const float* bias, cudaStream_t st) {
+    const int tm = (M + BM - 1) / BM, tn = (N + BN - 1) / BN;
+    const long long tiles = (long long)tm * tn;
+    int splits = 1;
+    const int sms = net->ctx->sm_count;
+    if (tiles < 2 * sms && K >= 512) {
+        splits = (int)((2LL * sms + tiles - 1) / tiles);
+        const int maxs = K / 128;
+        if (splits > maxs) splits = maxs;
+        if (splits < 1) splits = 1;
+    }
+    if (splits == 1) {
+        dim3 grid(tn, tm, 1);
+        gemm_kernel<AKF, BNF><<<grid, 256, 0, st>>>(M, N, K, K, A, B, EpiStore{C, N, bias});
+        NET_LAUNCH(net);
+        return NC_OK;
+    }
+    int kslice = (K + splits - 1) / splits;
+    kslice = (kslice + BK - 1) / BK * BK;
+    splits = (K + kslice - 1) / kslice;
+    const long long plane = (long long)M * N;
+    int rc = reserve_ws(net, (size_t)plane * splits * sizeof(float));
+    if (rc != NC_OK) return rc;
+    dim3 grid(tn, tm, splits);
+    gemm_kernel<AKF, BNF><<<grid, 256, 0, st>>>(M, N, K, kslice, A, B, EpiPartial{net->ws, N, plane});
+    NET_LAUNCH(net);
+    reduce_partials_kernel<<<grid_for(plane, sms), 256, 0, st>>>(C, net->ws, splits, plane, bias, N);
+    NET_LAUNCH(net);
+    return NC_OK;
+}
+
+static int run_colsum(nc_net* net, const float* y, int rows, int cols, float* out, cudaStream_t st) {
+    int splits = (rows + 2047) / 2048;
+    if (splits < 1) splits = 1;
+    if (splits > 256) splits = 256;
+    const int rps = (rows + splits - 1) / splits;
+    splits = (rows + rps - 1) / rps;
+    int rc = reserve_ws(net, (size_t)splits * cols * sizeof(float));
+    if (rc != NC_OK) return rc;
+    dim3 grid((cols + 31) / 32, splits);
+    colsum_partial_kernel<<<grid, 256, 0, st>>>(y, rows, cols, rps, net->ws);
+    NET_LAUNCH(net);
+    reduce_partials_kernel<<<grid_for(cols, net->ctx->sm_count), 256, 0, st>>>(out, net->ws, splits, cols, nullptr, cols);
+    NET_LAUNCH(net);
+    return NC_OK;
+}
+
+static ConvGeom geom(const Layer& L) { return ConvGeom{L.ih, L.iw, L.ic, L.oh, L.ow, L.oc, L.fh, L.fw, L.sh, L.sw, L.pt, L.pl}; }
+static PoolGeom pgeom(const Layer& L) { return PoolGeom{L.ih, L.iw, L.ic, L.oh, L.ow, L.fh, L.fw, L.sh, L.sw, L.pt, L.pl}; }
+
+// ------------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------------
+static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st) {
+    int rc = reserve_batch(net, n);
+    if (rc != NC_OK) return rc;
+    const int sms = net->ctx->sm_count;
+    const float* in = x;
+    for (auto& L : net->layers) {
+        float* out = act_ptr(net, L);
+        const float* W = L.w_off >= 0 ? net->params + L.w_off : nullptr;
+        const float* Bp = L.b_off >= 0 ? net->params + L.b_off : nullptr;
+        switch (L.kind) {
+        case L_CONV: {
+            const int M = n * L.oh * L.ow, N = L.oc, K = L.fh * L.fw * L.ic;
+            rc = run_gemm<true, true>(net, M, N, K, Im2col{in, geom(L)}, RowMajor{W, N}, out, Bp, st);
+            if (rc != NC_OK) return rc;
+            break;
+        }
+        case L_CONNECT: {
+            const int M = n, N = L.oc, K = (int)L.in_size;
+            rc = run_gemm<true, true>(net, M, N, K, RowMajor{in, K}, RowMajor{W, N}, out, Bp, st);
+            if (rc != NC_OK) return rc;
+            break;
+        }
+        case L_POOL: {
+            const long long total = (long long)n * L.out_size;
+            maxpool_fwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(in, out, net->aux + L.aux_off * net->cap, pgeom(L), total);
+            NET_LAUNCH(net);
+            break;
+        }
+        case L_ACT: {
+            const long long total = (long long)n * L.out_size;
+            act_fwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(in, out, total, L.act, L.slope);
+            NET_LAUNCH(net);
+            break;
+        }
+        case L_NORM: {
+            const long long rows = (long long)n * (L.out_size / L.oc);
+            norm_fwd_kernel<<<L.oc, 256, 0, st>>>(in, out, net->act + L.aux_off * net->cap, net->stat + L.stat_off, W, Bp, rows, L.oc, L.eps);
+            NET_LAUNCH(net);
+            break;
+        }
+        }
+        in = out;
+    }
+    return NC_OK;
+}
+
+static int check_io(nc_net* net, const void* x, int n) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (n <= 0) return net_err(net, NC_EINVAL, "batch size must be positive, got %d", n);
+    if (!x) return net_err(net, NC_EINVAL, "x is NULL");
+    return NC_OK;
+}
+
+extern "C" int nc_net_forward(nc_net* net, const float* x, int n, float* logits, void* stream) {
+    int rc = check_io(net, x, n);
+    if (rc != NC_OK) return rc;
+    if (!logits) return net_err(net, NC_EINVAL, "logits is NULL");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = forward_impl(net, x, n, st);
+    if (rc != NC_OK) return rc;
+    NET_CUDA(net, cudaMemcpyAsync(logits, act_ptr(net, net->layers.back()), (size_t)n * net->classes * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    return NC_OK;
+}
+
+extern "C" int nc_net_predict(nc_net* net, const float* x, int n, int32_t* labels, void* stream) {
+    int rc = check_io(net, x, n);
+    if (rc != NC_OK) return rc;
+    if (!labels) return net_err(net, NC_EINVAL, "labels is NULL");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = forward_impl(net, x, n, st);
+    if (rc != NC_OK) return rc;
+    argmax_kernel<<<(n + 127) / 128, 128, 0, st>>>(act_ptr(net, net->layers.back()), n, net->classes, labels);
+    NET_LAUNCH(net);
+    return NC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward
+// ------------------------------------------------------------------------------------------------
+extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name, float grad_scale,
+                               float* loss_out, int32_t* correct_out, void* stream) {
+    int rc = check_io(net, x, n);
+    if (rc != NC_OK) return rc;
+    if (!y_onehot) return net_err(net, NC_EINVAL, "y_onehot is NULL");
+    if (loss_name != 0 && loss_name != 1)
+        return net_err(net, NC_ECONFIG, "loss_function returns None for this loss_name (reference: ValueError in minimize); use entropy or mse");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = forward_impl(net, x, n, st);
+    if (rc != NC_OK) return rc;
+    const int sms = net->ctx->sm_count;
+    float* d = net->dbuf0;
+    float* dn = net->dbuf1;
+    loss_kernel<<<1, 1024, 0, st>>>(act_ptr(net, net->layers.back()), y_onehot, d, n, net->classes, loss_name, grad_scale, loss_out, (int*)correct_out);
+    NET_LAUNCH(net);
+    for (int li = (int)net->layers.size() - 1; li >= 0; --li) {
+        Layer& L = net->layers[li];
+        const float* in = li == 0 ? x : act_ptr(net, net->layers[li - 1]);
+        const float* out = act_ptr(net, L);
+        const float* W = L.w_off >= 0 ? net->params + L.w_off : nullptr;
+        float* dW = L.w_off >= 0 ? net->grads + L.w_off : nullptr;
+        float* dB = L.b_off >= 0 ? net->grads + L.b_off : nullptr;
+        const bool need_dx = li > 0;
+        switch (L.kind) {
+        case L_CONNECT: {
+            const int M = n, N = L.oc, K = (int)L.in_size;
+            // dW[K][N] = X^T[K][M] * dY[M][N]
+            rc = run_gemm<false, true>(net, K, N, M, ColMajor{in, K}, RowMajor{d, N}, dW, nullptr, st);
+            if (rc != NC_OK) return rc;
+            rc = run_colsum(net, d, M, N, dB, st);
+            if (rc != NC_OK) return rc;
+            if (need_dx) {   // dX[M][K] = dY[M][N] * W^T[N][K]
+                rc = run_gemm<true, false>(net, M, K, N, RowMajor{d, N}, ColMajor{W, N}, dn, nullptr, st);
+                if (rc != NC_OK) return rc;
+            }
+            break;
+        }
+        case L_CONV: {
+            const int M = n * L.oh * L.ow, N = L.oc, K = L.fh * L.fw * L.ic;
+            rc = run_gemm<false, true>(net, K, N, M, Im2colT{Im2col{in, geom(L)}}, RowMajor{d, N}, dW, nullptr, st);
+            if (rc != NC_OK) return rc;
+            if (dB) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
+            if (need_dx) {
+                const int Mi = n * L.ih * L.iw, Ki = L.fh * L.fw * L.oc;
+                rc = run_gemm<true, false>(net, Mi, L.ic, Ki, DgradA{d, geom(L)}, DgradB{W, geom(L)}, dn, nullptr, st);
+                if (rc != NC_OK) return rc;
+            }
+            break;
+        }
+        case L_POOL:
+            if (need_dx) {
+                const long long total_in = (long long)n * L.in_size;
+                maxpool_bwd_kernel<<<grid_for(total_in, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_in);
+                NET_LAUNCH(net);
+            }
+            break;
+        case L_ACT:
+            if (need_dx) {
+                const long long total = (long long)n * L.out_size;
+                act_bwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(in, out, d, dn, total, L.act, L.slope);
+                NET_LAUNCH(net);
+            }
+            break;
+        case L_NORM: {
+            const long long rows = (long long)n * (L.out_size / L.oc);
+            norm_bwd_kernel<<<L.oc, 256, 0, st>>>(d, net->act + L.aux_off * net->cap, net->stat + L.stat_off, W, dn, dW, dB, rows, L.oc);
+            NET_LAUNCH(net);
+            break;
+        }
+        }
+        if (need_dx) { float* t = d; d = dn; dn = t; }
+    }
+    return NC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// optimizer
+// ------------------------------------------------------------------------------------------------
+static int ensure_state(nc_net* net, int opt, cudaStream_t st) {
+    const size_t pb = (size_t)net->nparams * sizeof(float);
+    if (opt == 0 && !net->st_adagrad) {
+        if (cudaMalloc(&net->st_adagrad, pb) != cudaSuccess) { cudaGetLastError(); return net_err(net, NC_ENOMEM, "Adagrad accumulator"); }
+        fill_kernel<<<grid_for(net->nparams, net->ctx->sm_count), 256, 0, st>>>(net->st_adagrad, net->nparams, 0.1f);   // initial_accumulator_value
+        NET_LAUNCH(net);
+    }
+    if (opt == 2 && !net->st_adam) {
+        if (cudaMalloc(&net->st_adam, 2 * pb) != cudaSuccess) { cudaGetLastError(); return net_err(net, NC_ENOMEM, "Adam moments"); }
+        NET_CUDA(net, cudaMemsetAsync(net->st_adam, 0, 2 * pb, st));
+    }
+    return NC_OK;
+}
+
+extern "C" int nc_net_apply(nc_net* net, int opt, float lr, void* stream) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (opt < 0 || opt > 2) return net_err(net, NC_EINVAL, "optimizer must be 0 (Adagrad), 1 (SGD) or 2 (Adam)");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = ensure_state(net, opt, st);
+    if (rc != NC_OK) return rc;
+    const int grid = grid_for(net->nparams, net->ctx->sm_count);
+    if (opt == 0) adagrad_kernel<<<grid, 256, 0, st>>>(net->params, net->grads, net->st_adagrad, net->nparams, lr);
+    else if (opt == 1) sgd_kernel<<<grid, 256, 0, st>>>(net->params, net->grads, net->nparams, lr);
+    else {
+        const double t = (double)(net->global_step + 1);
+        const double b1 = 0.9, b2 = 0.999;
+        const float lr_t = (float)((double)lr * std::sqrt(1.0 - std::pow(b2, t)) / (1.0 - std::pow(b1, t)));
+        adam_kernel<<<grid, 256, 0, st>>>(net->params, net->grads, net->st_adam, net->st_adam + net->nparams, net->nparams, lr_t, 0.9f, 0.999f, 1e-8f);
+    }
+    NET_LAUNCH(net);
+    net->global_step++;
+    return NC_OK;
+}
+
+extern "C" int nc_net_train_step(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name, int opt, float lr,
+                                 float* loss_out, int32_t* correct_out, void* stream) {
+    int rc = nc_net_backward(net, x, y_onehot, n, loss_name, 1.0f, loss_out, correct_out, stream);
+    if (rc != NC_OK) return rc;
+    return nc_net_apply(net, opt, lr, stream);
+}
+
+extern "C" int nc_net_state_slots(nc_net* net, int opt) { (void)net; return opt == 0 ? 1 : opt == 2 ? 2 : 0; }
+
+extern "C" int nc_net_get_state(nc_net* net, int opt, float* host_state) {
+    if (!net || !host_state) return nc_set_error(net ? net->ctx : nullptr, NC_EINVAL, "NULL argument");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    int rc = ensure_state(net, opt, 0);
+    if (rc != NC_OK) return rc;
+    const size_t pb = (size_t)net->nparams * sizeof(float);
+    if (opt == 0) NET_CUDA(net, cudaMemcpy(host_state, net->st_adagrad, pb, cudaMemcpyDeviceToHost));
+    else if (opt == 2) NET_CUDA(net, cudaMemcpy(host_state, net->st_adam, 2 * pb, cudaMemcpyDeviceToHost));
+    return NC_OK;
+}
+
+extern "C" int nc_net_set_state(nc_net* net, int opt, const float* host_state, int64_t global_step) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    if (host_state) {
+        int rc = ensure_state(net, opt, 0);
+        if (rc != NC_OK) return rc;
+        NET_CUDA(net, cudaDeviceSynchronize());
+        const size_t pb = (size_t)net->nparams * sizeof(float);
+        if (opt == 0) NET_CUDA(net, cudaMemcpy(net->st_adagrad, host_state, pb, cudaMemcpyHostToDevice));
+        else if (opt == 2) NET_CUDA(net, cudaMemcpy(net->st_adam, host_state, 2 * pb, cudaMemcpyHostToDevice));
+    }
+    net->global_step = global_step;
+    return NC_OK;
+}

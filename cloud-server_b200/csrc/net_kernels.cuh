@@ -1,0 +1,414 @@
+// fp32 SIMT kernels of the CNN path (math mode 0, and every shape the tensor-core path does not
+// take).  All contractions go through one tiled implicit-GEMM kernel parameterised by element
+// functors (dense / im2col / transposed views), so conv fwd, dgrad, wgrad and the dense layers
+// share one verified inner loop.  TF-1.x semantics as restated in oracle/tfref.py.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nck {
+
+// ---------------------------------------------------------------------------------------------
+// element functors: value of the virtual matrix at (row, col); rows/cols outside are never asked
+// ---------------------------------------------------------------------------------------------
+struct RowMajor {           // M x K (or K x N) dense, leading dimension ld
+    const float* p; int ld;
+    __device__ __forceinline__ float operator()(int r, int c) const { return __ldg(p + (long long)r * ld + c); }
+};
+struct ColMajor {           // element (r, c) stored at p[c*ld + r]   (a transposed view)
+    const float* p; int ld;
+    __device__ __forceinline__ float operator()(int r, int c) const { return __ldg(p + (long long)c * ld + r); }
+};
+
+struct ConvGeom {
+    int ih, iw, ic, oh, ow, oc, fh, fw, sh, sw, pt, pl;
+};
+
+// im2col view of the NHWC input: row m = (n, oy, ox), col k = (i, j, c)
+struct Im2col {
+    const float* x; ConvGeom g;
+    __device__ __forceinline__ float operator()(int m, int k) const {
+        const int c = k % g.ic; const int ij = k / g.ic; const int j = ij % g.fw, i = ij / g.fw;
+        const int ox = m % g.ow; const int t = m / g.ow; const int oy = t % g.oh, n = t / g.oh;
+        const int y = oy * g.sh - g.pt + i, xx = ox * g.sw - g.pl + j;
+        if (y < 0 || y >= g.ih || xx < 0 || xx >= g.iw) return 0.0f;
+        return __ldg(x + (((long long)n * g.ih + y) * g.iw + xx) * g.ic + c);
+    }
+};
+// transposed im2col (for wgrad): row k = (i, j, c), col m = (n, oy, ox)
+struct Im2colT {
+    Im2col v;
+    __device__ __forceinline__ float operator()(int k, int m) const { return v(m, k); }
+};
+// dgrad view of dY: row m = (n, y, x) of the INPUT, col k = (i, j, co)
+struct DgradA {
+    const float* dy; ConvGeom g;
+    __device__ __forceinline__ float operator()(int m, int k) const {
+        const int co = k % g.oc; const int ij = k / g.oc; const int j = ij % g.fw, i = ij / g.fw;
+        const int xx = m % g.iw; const int t = m / g.iw; const int y = t % g.ih, n = t / g.ih;
+        const int ny = y + g.pt - i, nx = xx + g.pl - j;
+        if (ny < 0 || nx < 0 || ny % g.sh || nx % g.sw) return 0.0f;
+        const int oy = ny / g.sh, ox = nx / g.sw;
+        if (oy >= g.oh || ox >= g.ow) return 0.0f;
+        return __ldg(dy + (((long long)n * g.oh + oy) * g.ow + ox) * g.oc + co);
+    }
+};
+// dgrad view of the HWIO filter: row k = (i, j, co), col c
+struct DgradB {
+    const float* w; ConvGeom g;
+    __device__ __forceinline__ float operator()(int k, int c) const {
+        const int co = k % g.oc; const int ij = k / g.oc;
+        return __ldg(w + ((long long)ij * g.ic + c) * g.oc + co);
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// epilogues
+// ---------------------------------------------------------------------------------------------
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_LEAKY = 3 };
+
+struct EpiStore {           // C[m][n] = acc (+ bias[n])
+    float* c; int ldc; const float* bias;
+    __device__ __forceinline__ void operator()(int m, int n, float acc, int) const {
+        if (bias) acc += __ldg(bias + n);
+        c[(long long)m * ldc + n] = acc;
+    }
+};
+struct EpiPartial {         // split-K partial: ws[split][m][n]
+    float* ws; int ldc; long long plane;
+    __device__ __forceinline__ void operator()(int m, int n, float acc, int split) const {
+        ws[(long long)split * plane + (long long)m * ldc + n] = acc;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// tiled SIMT GEMM: C[M,N] = A[M,K] * B[K,N], 64x64x16 tiles, 256 threads, 4x4 per thread.
+// AKF: A's contiguous memory axis is k (true) or m (false); BNF: B's contiguous axis is n / k.
+// gridDim.z = split-K slices of length kslice.
+// ---------------------------------------------------------------------------------------------
+constexpr int BM = 64, BN = 64, BK = 16;
+
+template <bool AKF, bool BNF, class AF, class BF, class Epi>
+__global__ void __launch_bounds__(256)
+gemm_kernel(int M, int N, int K, int kslice, AF A, BF B, Epi epi) {
+    __shared__ float As[BK][BM + 4];
+    __shared__ float Bs[BK][BN + 4];
+    const int tid = threadIdx.x;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int kbeg = blockIdx.z * kslice;
+    const int kend = min(K, kbeg + kslice);
+    const int tx = tid % 16, ty = tid / 16;       // thread tile: rows ty*4.., cols tx*4..
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+
+    for (int k0 = kbeg; k0 < kend; k0 += BK) {
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            const int e = tid + l * 256;
+            int mm, kk;
+            if (AKF) { kk = e % BK; mm = e / BK; } else { mm = e % BM; kk = e / BM; }
+            const int gm = m0 + mm, gk = k0 + kk;
+            As[kk][mm] = (gm < M && gk < kend) ? A(gm, gk) : 0.0f;
+            int nn, kb;
+            if (BNF) { nn = e % BN; kb = e / BN; } else { kb = e % BK; nn = e / BK; }
+            const int gn = n0 + nn, gkb = k0 + kb;
+            Bs[kb][nn] = (gn < N && gkb < kend) ? B(gkb, gn) : 0.0f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < BK; ++kk) {
+            const float4 a4 = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+            const float4 b4 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+            const float a[4] = {a4.x, a4.y, a4.z, a4.w};
+            const float b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gm = m0 + ty * 4 + i;
+        if (gm >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gn = n0 + tx * 4 + j;
+            if (gn < N) epi(gm, gn, acc[i][j], blockIdx.z);
+        }
+    }
+}
+
+// dst[i] = sum_s ws[s*count + i]   (fixed order: deterministic)
+__global__ void reduce_partials_kernel(float* __restrict__ dst, const float* __restrict__ ws, int splits, long long count,
+                                       const float* __restrict__ bias, int ncols) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        float s = 0.0f;
+        for (int k = 0; k < splits; ++k) s += ws[(long long)k * count + i];
+        if (bias) s += __ldg(bias + (int)(i % ncols));
+        dst[i] = s;
+    }
+}
+
+// column sums of Y[rows][cols] (bias gradients): partial[split][col]
+__global__ void colsum_partial_kernel(const float* __restrict__ y, int rows, int cols, int rows_per_split, float* __restrict__ ws) {
+    const int col = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int lane_row = threadIdx.x >> 5;            // 8 row lanes
+    const int r0 = blockIdx.y * rows_per_split, r1 = min(rows, r0 + rows_per_split);
+    float s = 0.0f;
+    if (col < cols)
+        for (int r = r0 + lane_row; r < r1; r += 8) s += __ldg(y + (long long)r * cols + col);
+    __shared__ float sh[8][33];
+    sh[lane_row][threadIdx.x & 31] = s;
+    __syncthreads();
+    if (lane_row == 0 && col < cols) {
+        float t = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x & 31];
+        ws[(long long)blockIdx.y * cols + col] = t;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// pooling  (tf.nn.max_pool, construct_distribute.py:121-130)
+// ---------------------------------------------------------------------------------------------
+struct PoolGeom { int ih, iw, c, oh, ow, kh, kw, sh, sw, pt, pl; };
+
+__global__ void maxpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ arg,
+                                   PoolGeom g, long long total) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        const int c = idx % g.c; long long t = idx / g.c;
+        const int ox = t % g.ow; t /= g.ow;
+        const int oy = t % g.oh; const int n = (int)(t / g.oh);
+        float best = -INFINITY; int bi = 0;
+        for (int i = 0; i < g.kh; ++i) {
+            const int yy = oy * g.sh - g.pt + i;
+            if (yy < 0 || yy >= g.ih) continue;
+            for (int j = 0; j < g.kw; ++j) {
+                const int xx = ox * g.sw - g.pl + j;
+                if (xx < 0 || xx >= g.iw) continue;
+                const float v = __ldg(x + (((long long)n * g.ih + yy) * g.iw + xx) * g.c + c);
+                if (v > best) { best = v; bi = i * g.kw + j; }   // strict '>': first maximum wins
+            }
+        }
+        y[idx] = best;
+        arg[idx] = (uint8_t)bi;
+    }
+}
+
+// gather form (deterministic, handles overlapping windows): each input element sums the dy of the
+// windows whose argmax it is
+__global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ arg, float* __restrict__ dx,
+                                   PoolGeom g, long long total_in) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total_in; idx += stride) {
+        const int c = idx % g.c; long long t = idx / g.c;
+        const int xx = t % g.iw; t /= g.iw;
+        const int yy = t % g.ih; const int n = (int)(t / g.ih);
+        float s = 0.0f;
+        for (int i = 0; i < g.kh; ++i) {
+            const int ny = yy + g.pt - i;
+            if (ny < 0 || ny % g.sh) continue;
+            const int oy = ny / g.sh;
+            if (oy >= g.oh) continue;
+            for (int j = 0; j < g.kw; ++j) {
+                const int nx = xx + g.pl - j;
+                if (nx < 0 || nx % g.sw) continue;
+                const int ox = nx / g.sw;
+                if (ox >= g.ow) continue;
+                const long long o = (((long long)n * g.oh + oy) * g.ow + ox) * g.c + c;
+                if (arg[o] == i * g.kw + j) s += __ldg(dy + o);
+            }
+        }
+        dx[idx] = s;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// activations (active(), construct_distribute.py:133-152)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float act_apply(int fn, float x, float slope) {
+    if (fn == ACT_RELU) return fmaxf(x, 0.0f);
+    if (fn == ACT_SIGMOID) return 1.0f / (1.0f + expf(-x));
+    if (fn == ACT_LEAKY) return fmaxf(x, slope * x);
+    return x;
+}
+
+__global__ void act_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long count, int fn, float slope) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride)
+        y[i] = act_apply(fn, __ldg(x + i), slope);
+}
+
+// dx = dy * f'(x): relu from y > 0 (tf ReluGrad), sigmoid y(1-y), leaky: x >= slope*x ? 1 : slope (tf.maximum grad)
+__global__ void act_bwd_kernel(const float* __restrict__ x, const float* __restrict__ y, const float* __restrict__ dy,
+                               float* __restrict__ dx, long long count, int fn, float slope) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        const float g = __ldg(dy + i);
+        float r;
+        if (fn == ACT_RELU) r = __ldg(y + i) > 0.0f ? g : 0.0f;
+        else if (fn == ACT_SIGMOID) { const float v = __ldg(y + i); r = g * v * (1.0f - v); }
+        else { const float v = __ldg(x + i); r = (v >= slope * v) ? g : slope * g; }
+        dx[i] = r;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// batch normalisation with batch statistics (normalize(), construct_distribute.py:155-165)
+// rows x C matrix (rows = N*H*W), one CTA per channel
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    float t = 0.0f;
+    const int nw = blockDim.x >> 5;
+    for (int i = 0; i < nw; ++i) t += sh[i];
+    return t;
+}
+
+__global__ void __launch_bounds__(256)
+norm_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, float* __restrict__ xhat, float* __restrict__ inv_out,
+                const float* __restrict__ scale, const float* __restrict__ offset, long long rows, int C, float eps) {
+    __shared__ float sh[8];
+    const int c = blockIdx.x;
+    float s = 0.0f;
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) s += __ldg(x + r * C + c);
+    const float mean = block_sum(s, sh) / (float)rows;
+    float q = 0.0f;
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) { const float d = __ldg(x + r * C + c) - mean; q += d * d; }
+    const float var = block_sum(q, sh) / (float)rows;
+    const float inv = 1.0f / sqrtf(var + eps);
+    if (threadIdx.x == 0) inv_out[c] = inv;
+    const float sc = __ldg(scale + c), of = __ldg(offset + c);
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) {
+        const float h = (__ldg(x + r * C + c) - mean) * inv;
+        xhat[r * C + c] = h;
+        y[r * C + c] = h * sc + of;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+norm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, const float* __restrict__ inv_in,
+                const float* __restrict__ scale, float* __restrict__ dx, float* __restrict__ dscale, float* __restrict__ doffset,
+                long long rows, int C) {
+    __shared__ float sh[8];
+    const int c = blockIdx.x;
+    float s1 = 0.0f, s2 = 0.0f;
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) {
+        const float g = __ldg(dy + r * C + c);
+        s1 += g; s2 += g * __ldg(xhat + r * C + c);
+    }
+    const float sum_dy = block_sum(s1, sh);
+    const float sum_dyx = block_sum(s2, sh);
+    if (threadIdx.x == 0) { doffset[c] = sum_dy; dscale[c] = sum_dyx; }
+    const float sc = __ldg(scale + c), inv = __ldg(inv_in + c), m = (float)rows;
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) {
+        const float g = __ldg(dy + r * C + c) * sc;
+        dx[r * C + c] = inv / m * (m * g - sum_dy * sc - __ldg(xhat + r * C + c) * sum_dyx * sc);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// loss (loss_function, :285-298) fused with its gradient and the accuracy count (:381-382).
+// One CTA; rows strided over threads; deterministic in-block reduction.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024)
+loss_kernel(const float* __restrict__ z, const float* __restrict__ y, float* __restrict__ dz, int n, int classes,
+            int loss_name, float grad_scale, float* __restrict__ loss_out, int* __restrict__ correct_out) {
+    __shared__ float sh[32];
+    __shared__ int shi[32];
+    float lsum = 0.0f; int hits = 0;
+    for (int r = threadIdx.x; r < n; r += blockDim.x) {
+        const float* zr = z + (long long)r * classes;
+        const float* yr = y + (long long)r * classes;
+        float zmax = -INFINITY, ymax = -INFINITY; int za = 0, ya = 0;
+        for (int j = 0; j < classes; ++j) {
+            const float a = zr[j], b = yr[j];
+            if (a > zmax) { zmax = a; za = j; }
+            if (b > ymax) { ymax = b; ya = j; }
+        }
+        hits += (za == ya);
+        if (loss_name == 0) {
+            float se = 0.0f;
+            for (int j = 0; j < classes; ++j) se += expf(zr[j] - zmax);
+            const float lse = zmax + logf(se);
+            float l = 0.0f;
+            for (int j = 0; j < classes; ++j) {
+                const float logp = zr[j] - lse;
+                l -= yr[j] * logp;
+                if (dz) dz[(long long)r * classes + j] = (expf(logp) - yr[j]) * grad_scale / (float)n;
+            }
+            lsum += l;
+        } else {
+            float l = 0.0f;
+            for (int j = 0; j < classes; ++j) {
+                const float d = zr[j] - yr[j];
+                l += d * d;
+                if (dz) dz[(long long)r * classes + j] = 2.0f * d * grad_scale / ((float)n * (float)classes);
+            }
+            lsum += l / (float)classes;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) { lsum += __shfl_xor_sync(0xffffffffu, lsum, o); hits += __shfl_xor_sync(0xffffffffu, hits, o); }
+    if ((threadIdx.x & 31) == 0) { sh[threadIdx.x >> 5] = lsum; shi[threadIdx.x >> 5] = hits; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f; int hh = 0;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { t += sh[i]; hh += shi[i]; }
+        if (loss_out) *loss_out = t / (float)n;
+        if (correct_out) *correct_out = hh;
+    }
+}
+
+__global__ void argmax_kernel(const float* __restrict__ z, int n, int classes, int32_t* __restrict__ out) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const float* zr = z + (long long)r * classes;
+    float best = zr[0]; int bi = 0;
+    for (int j = 1; j < classes; ++j) if (zr[j] > best) { best = zr[j]; bi = j; }
+    out[r] = bi;
+}
+
+// ---------------------------------------------------------------------------------------------
+// optimizers on the flat buffers (ApplyAdagrad / ApplyGradientDescent / ApplyAdam, TF 1.x)
+// ---------------------------------------------------------------------------------------------
+__global__ void adagrad_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ acc, long long count, float lr) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        const float gi = g[i];
+        const float a = acc[i] + gi * gi;
+        acc[i] = a;
+        w[i] -= lr * gi * rsqrtf(a);
+    }
+}
+__global__ void sgd_kernel(float* __restrict__ w, const float* __restrict__ g, long long count, float lr) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) w[i] -= lr * g[i];
+}
+__global__ void adam_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                            long long count, float lr_t, float b1, float b2, float eps) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        const float gi = g[i];
+        const float mi = m[i] + (gi - m[i]) * (1.0f - b1);
+        const float vi = v[i] + (gi * gi - v[i]) * (1.0f - b2);
+        m[i] = mi; v[i] = vi;
+        w[i] -= lr_t * mi / (sqrtf(vi) + eps);
+    }
+}
+__global__ void fill_kernel(float* __restrict__ p, long long count, float v) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) p[i] = v;
+}
+
+}  // namespace nck

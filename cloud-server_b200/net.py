@@ -1,0 +1,167 @@
+"""Host-side mirror of the reference's graph interface (construct_distribute.py:208-311) over the
+C ABI: ``Net(net_config)`` interprets the same JSON ``cnn()`` does; forward / backward / optimizer
+steps run in the CUDA library.  PyTorch supplies device tensors, streams and (for data parallel
+training) the NCCL process group -- plumbing only."""
+import ctypes as C
+import json
+
+import numpy as np
+import torch
+
+from . import _lib
+from .context import default_context
+
+LOSS = {"entropy": 0, "mse": 1}
+# optimizer_name values of the UI (apps/construction/util/options.py:22-31) -> library ids.
+# "compat" = what the reference actually runs whatever the config says: AdagradOptimizer(1e-4)
+# (construct_distribute.py:372-373).
+OPT = {"AdagradOptimizer": 0, "Adagrad": 0, "adagrad": 0, "GradientDescentOptimizer": 1, "SGD": 1, "sgd": 1,
+       "AdamOptimizer": 2, "Adam": 2, "adam": 2}
+
+
+class _DevMem:
+    """Exposes library-owned device memory to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr, count, owner):
+        self._owner = owner
+        self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class Net:
+    def __init__(self, net_config, ctx=None, in_h=28, in_w=28, in_c=1, classes=10, seed=1):
+        self.ctx = ctx or default_context()
+        if not isinstance(net_config, str):
+            net_config = json.dumps(net_config)
+        self.config = net_config
+        self.classes, self.in_features = classes, in_h * in_w * in_c
+        h = C.c_void_p()
+        L = _lib.lib()
+        _lib.check(self.ctx.handle, L.nc_net_create(self.ctx.handle, net_config.encode(), in_h, in_w, in_c, classes,
+                                                    C.c_uint64(seed), C.byref(h)))
+        self.handle = h
+        self.param_count = int(L.nc_net_param_count(h))
+        self.tensors = []
+        for i in range(L.nc_net_tensor_count(h)):
+            off, size, nd = C.c_int64(), C.c_int64(), C.c_int()
+            dims = (C.c_int64 * 4)()
+            _lib.check(self.ctx.handle, L.nc_net_tensor_info(h, i, C.byref(off), C.byref(size), C.byref(nd), C.byref(dims)))
+            self.tensors.append((off.value, size.value, tuple(dims[k] for k in range(nd.value))))
+        dev = self.ctx.tdev
+        self.params = torch.as_tensor(_DevMem(L.nc_net_params(h), self.param_count, self), device=dev)
+        self.grads = torch.as_tensor(_DevMem(L.nc_net_grads(h), self.param_count, self), device=dev)
+        self._loss = torch.zeros(1, dtype=torch.float32, device=dev)
+        self._correct = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def close(self):
+        if getattr(self, "handle", None):
+            _lib.lib().nc_net_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- parameters (flat, variable-creation order; conv HWIO, dense [in][out])
+    def set_params(self, flat):
+        flat = np.ascontiguousarray(np.asarray(flat, np.float32).reshape(-1))
+        if flat.size != self.param_count:
+            raise ValueError("expected %d parameters, got %d" % (self.param_count, flat.size))
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_set_params(self.handle, flat.ctypes.data_as(C.c_void_p)))
+
+    def get_params(self):
+        out = np.empty(self.param_count, np.float32)
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_get_params(self.handle, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def set_math(self, math):
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_set_math(self.handle, int(math)))
+
+    @property
+    def global_step(self):
+        return int(_lib.lib().nc_net_global_step(self.handle))
+
+    def get_state(self, opt):
+        slots = _lib.lib().nc_net_state_slots(self.handle, opt)
+        out = np.empty(slots * self.param_count, np.float32)
+        if slots:
+            _lib.check(self.ctx.handle, _lib.lib().nc_net_get_state(self.handle, opt, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def set_state(self, opt, state, global_step):
+        p = None
+        if state is not None and len(state):
+            state = np.ascontiguousarray(state, np.float32)
+            p = state.ctypes.data_as(C.c_void_p)
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_set_state(self.handle, opt, p, int(global_step)))
+
+    # ---- compute
+    def _x(self, x):
+        if x.dtype != torch.float32 or not x.is_cuda:
+            raise ValueError("x must be a float32 CUDA tensor [N, %d]" % self.in_features)
+        x = x.reshape(x.shape[0], -1).contiguous()
+        if x.shape[1] != self.in_features:
+            raise ValueError("x has %d features, the net takes %d" % (x.shape[1], self.in_features))
+        return x
+
+    def forward(self, x):
+        x = self._x(x)
+        out = torch.empty((x.shape[0], self.classes), dtype=torch.float32, device=x.device)
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_forward(self.handle, C.c_void_p(x.data_ptr()), x.shape[0],
+                                                              C.c_void_p(out.data_ptr()), self.ctx._stream()))
+        return out
+
+    def predict(self, x):
+        x = self._x(x)
+        out = torch.empty((x.shape[0],), dtype=torch.int32, device=x.device)
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_predict(self.handle, C.c_void_p(x.data_ptr()), x.shape[0],
+                                                              C.c_void_p(out.data_ptr()), self.ctx._stream()))
+        return out
+
+    def backward(self, x, y, loss_name="entropy", grad_scale=1.0):
+        """forward + loss + gradients into self.grads; returns (loss[1], correct[1]) device tensors."""
+        x = self._x(x)
+        y = y.reshape(x.shape[0], -1).contiguous()
+        if y.dtype != torch.float32 or y.shape[1] != self.classes:
+            raise ValueError("y must be float32 one-hot [N, %d]" % self.classes)
+        if loss_name not in LOSS:
+            raise ValueError("loss_function returns None for %r" % (loss_name,))
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_backward(
+            self.handle, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()), x.shape[0], LOSS[loss_name],
+            C.c_float(grad_scale), C.c_void_p(self._loss.data_ptr()), C.c_void_p(self._correct.data_ptr()), self.ctx._stream()))
+        return self._loss, self._correct
+
+    def apply(self, opt="compat", lr=1e-4):
+        oid, lr = (0, 1e-4) if opt == "compat" else (OPT[opt] if isinstance(opt, str) else int(opt), lr)
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_apply(self.handle, oid, C.c_float(lr), self.ctx._stream()))
+
+    def train_step(self, x, y, loss_name="entropy", opt="compat", lr=1e-4):
+        """One sess.run(train_op) (construct_distribute.py:413)."""
+        r = self.backward(x, y, loss_name, 1.0)
+        self.apply(opt, lr)
+        return r
+
+
+class DataParallel:
+    """Synchronous data parallel training, one process per GPU: every rank holds the same weights
+    and a contiguous slice of the global batch; gradients are summed with one NCCL all-reduce of
+    the flat gradient buffer (loss is a batch mean, so each rank scales its dLoss by 1/world).
+    The reference's own 'distribution' is a 1 ps + 1 worker gRPC parameter server
+    (construct_distribute.py:344-357, cmd.py:63-69); the parity target is the single-device step at
+    the global batch."""
+
+    def __init__(self, net, group=None):
+        import torch.distributed as dist
+        self.net, self.dist, self.group = net, dist, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if self.world > 1:
+            dist.broadcast(net.params, src=0, group=group)     # identical initial weights
+
+    def train_step(self, x_local, y_local, loss_name="entropy", opt="compat", lr=1e-4):
+        loss, correct = self.net.backward(x_local, y_local, loss_name, 1.0 / self.world)
+        if self.world > 1:
+            self.dist.all_reduce(self.net.grads, group=self.group)
+        self.net.apply(opt, lr)
+        return loss, correct

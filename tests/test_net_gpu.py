@@ -1,0 +1,149 @@
+"""GPU parity tests of the CNN half through the C ABI against oracle/tfref.py (numpy restatement of
+the TF-1.x graph the reference builds).  Tolerance (north_star): logits, loss and post-step weights
+within 1e-3 relative (TF32 tensor-core tiles, fp32 accumulate); the fp32 SIMT path (math 0) is held
+to 2e-5.  Predicted labels exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import tfref
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = {
+    "lenet": (tfref.LENET, 28, 28, 1, 16),
+    "api_example": (tfref.API_EXAMPLE, 28, 28, 1, 10),
+    "strided_valid_leaky": ({"middle_layer": [
+        {"layer": "conv", "filter": [3, 3, 4], "stride": [2, 2], "padding": "VALID", "isBias": "True"},
+        {"layer": "active", "active_func": "leaky_relu", "param": [0.1]},
+        {"layer": "conv", "filter": [2, 3, 5], "stride": [1, 2], "padding": "SAME"},
+        {"layer": "pool", "kernel": [3, 3], "stride": [2, 2]}, {"layer": "norm", "epsilon": 1e-2},
+        {"layer": "active", "active_func": "relu"},
+        {"layer": "connect", "hidden": 16}, {"layer": "norm"}, {"layer": "active"}]}, 13, 11, 2, 6),
+    "deep": (tfref.DEEPNET, 32, 32, 3, 8),
+    "dense_only": ({"middle_layer": [{"layer": "connect", "hidden": 64}, {"layer": "active", "active_func": "relu"}]}, 28, 28, 1, 33),
+    "overlap_pool": ({"middle_layer": [{"layer": "conv", "filter": [3, 3, 8], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
+                                       {"layer": "pool", "kernel": [3, 3], "stride": [1, 1]}, {"layer": "pool", "kernel": [2, 2], "stride": [2, 2], "padding": "VALID"}]},
+                     9, 10, 3, 5),
+}
+
+
+def rel_err(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-12))
+
+
+def make(name, ctx, seed=0):
+    from cloud_server_b200.net import Net
+    cfg, h, w, c, n = CONFIGS[name]
+    rng = np.random.default_rng(seed)
+    ref = tfref.Net(cfg, h, w, c)
+    params = tfref.init_params(ref.param_specs, rng)
+    params = [p + np.float32(0.02) * rng.standard_normal(p.shape).astype(np.float32) for p in params]
+    flat = ref.flatten(params)
+    net = Net(cfg, ctx, h, w, c)
+    assert net.param_count == ref.param_count()
+    assert [t[2] for t in net.tensors] == [tuple(s[1]) for s in ref.param_specs]
+    net.set_params(flat)
+    x = rng.random((n, h * w * c), dtype=np.float32)
+    y = np.eye(10, dtype=np.float32)[rng.integers(0, 10, n)]
+    return ref, net, flat, x, y
+
+
+@pytest.mark.parametrize("name", list(CONFIGS))
+def test_forward_and_labels(ctx, name):
+    ref, net, flat, x, y = make(name, ctx)
+    net.set_math(0)
+    want = ref.forward(x, ref.unflatten(flat))
+    got = net.forward(torch.from_numpy(x).cuda()).cpu().numpy()
+    assert rel_err(got, want) < 2e-5, name
+    labels = net.predict(torch.from_numpy(x).cuda()).cpu().numpy()
+    margin = np.sort(want, 1)[:, -1] - np.sort(want, 1)[:, -2]
+    sure = margin > 1e-3 * np.abs(want).max()
+    assert np.array_equal(labels[sure], want.argmax(1)[sure])
+
+
+@pytest.mark.parametrize("name", list(CONFIGS))
+@pytest.mark.parametrize("loss", ["entropy", "mse"])
+def test_gradients(ctx, name, loss):
+    ref, net, flat, x, y = make(name, ctx, seed=1)
+    net.set_math(0)
+    params = ref.unflatten(flat)
+    logits, cache = ref.forward(x, params, keep=True)
+    lref, dz = ref.loss_and_grad(logits, y, loss)
+    gref = ref.flatten(ref.backward(dz, params, cache))
+    lgot, correct = net.backward(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), loss)
+    assert abs(float(lgot.item()) - lref) < 2e-5 * max(1.0, abs(lref))
+    assert int(correct.item()) == int((logits.argmax(1) == y.argmax(1)).sum())
+    g = net.grads.cpu().numpy()
+    for (off, size, shape), spec in zip(net.tensors, ref.param_specs):
+        a, b = g[off:off + size], gref[off:off + size]
+        assert rel_err(a, b) < 1e-4, (name, spec[0], rel_err(a, b))
+
+
+@pytest.mark.parametrize("opt,lr", [("compat", 1e-4), ("adagrad", 0.05), ("sgd", 0.05), ("adam", 0.01)])
+def test_train_steps_post_step_weights(ctx, opt, lr):
+    ref, net, flat, x, y = make("lenet", ctx, seed=2)
+    net.set_math(0)
+    w = flat.copy()
+    o = {"compat": lambda: tfref.Adagrad(w.size, 1e-4), "adagrad": lambda: tfref.Adagrad(w.size, lr),
+         "sgd": lambda: tfref.SGD(w.size, lr), "adam": lambda: tfref.Adam(w.size, lr)}[opt]()
+    xd, yd = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    for step in range(3):
+        lref, _, _ = tfref.train_step(ref, w, x, y, o)
+        lgot, _ = net.train_step(xd, yd, "entropy", opt, lr)
+        assert abs(float(lgot.item()) - lref) < 1e-3 * max(1.0, abs(lref)), (opt, step)
+    assert net.global_step == 3
+    got = net.get_params()
+    delta_ref = w - flat
+    assert rel_err(got - flat, delta_ref) < 1e-3, opt          # the update itself, not just the weights
+    assert rel_err(got, w) < 1e-5
+
+
+def test_config_errors_and_defaults(ctx):
+    from cloud_server_b200.net import Net
+    with pytest.raises(ValueError):
+        Net({"middle_layer": [{"layer": "active", "active_func": "tanh"}]}, ctx)          # active(): assert False
+    with pytest.raises(ValueError):
+        Net({"middle_layer": [{"layer": "conv", "filter": [3, 3, 4], "init": "he"}]}, ctx)  # weight_variable: assert False
+    with pytest.raises(ValueError):
+        Net({"no_middle": []}, ctx)
+    n = Net({"middle_layer": [{"layer": "conv", "filter": [2, 2, 3], "isBias": False}, {"layer": "mystery"}]}, ctx)
+    assert [t[2] for t in n.tensors] == [(2, 2, 1, 3), (3,), (2352, 10), (10,)]     # isBias != "False" -> bias
+    with pytest.raises(ValueError):
+        n.backward(torch.zeros((2, 784), device="cuda"), torch.zeros((2, 10), device="cuda"), "hinge")
+
+
+def test_init_statistics(ctx):
+    from cloud_server_b200.net import Net
+    net = Net(tfref.LENET, ctx, seed=7)
+    p = net.get_params()
+    off, size, shape = net.tensors[4]            # fc1 weights 3136x1024: truncated normal sigma 0.1
+    w = p[off:off + size]
+    assert abs(w.std() - 0.1 * 0.8796) < 2e-3 and np.abs(w).max() <= 0.2 + 1e-6
+    off, size, _ = net.tensors[5]
+    assert np.all(p[off:off + size] == np.float32(0.1))      # bias_variable constant 0.1
+
+
+def test_full_size_batch_properties(ctx):
+    """BASELINE configs 3/4 shapes: LeNet at batch 256 / 2048 -- (1) the batch result equals the
+    per-sample result (forward is row-independent), (2) gradient linearity: the B=2048 gradient is
+    the mean of its eight B=256 slice gradients (what data parallel training relies on)."""
+    ref, net, flat, _, _ = make("lenet", ctx, seed=3)
+    net.set_math(0)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.rand((2048, 784), device="cuda", generator=g)
+    y = torch.nn.functional.one_hot(torch.randint(0, 10, (2048,), device="cuda", generator=g), 10).float()
+    full = net.forward(x)
+    part = torch.cat([net.forward(x[i:i + 256]) for i in range(0, 2048, 256)])
+    assert torch.allclose(full, part, rtol=1e-5, atol=1e-5)
+    net.backward(x, y)
+    gfull = net.grads.clone()
+    acc = torch.zeros_like(gfull)
+    for i in range(0, 2048, 256):
+        net.backward(x[i:i + 256], y[i:i + 256], "entropy", 1.0 / 8)
+        acc += net.grads
+    assert float((acc - gfull).abs().max() / gfull.abs().max()) < 1e-4
+    # spot-check 4 rows of the big batch against the oracle
+    want = ref.forward(x[:4].cpu().numpy(), ref.unflatten(flat))
+    assert rel_err(full[:4].cpu().numpy(), want) < 2e-5
