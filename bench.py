@@ -207,6 +207,96 @@ def max_over_ranks(torch, ms, dist_on, device):
     return float(t.item())
 
 
+# LeNet step model: 82.05 MFLOP / picture; HBM bytes per step (fp32, every saved
+# activation and activation gradient written once + read once, parameters read fwd + dgrad, gradient
+# written, Adagrad reads g,w,acc and writes w,acc)
+LENET_FLOP_PER_IMG = 82.05e6
+LENET_PARAMS = 3274634
+
+
+def lenet_step_bytes(b):
+    return 4 * b * (2 * 48858 + 2 * 48074) + 4 * 8 * LENET_PARAMS
+
+
+def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
+    """LeNet (BASELINE configs 2-3): train step images/s (data parallel over the ranks, NCCL
+    all-reduce of the flat gradient buffer) and inference images/s.  Synthetic MNIST-shaped data
+    resident in HBM (60 000 x 784 float32), random-init weights."""
+    from cloud_server_b200.net import Net, DataParallel
+    from cloud_server_b200.configs import LENET
+    out = {}
+    g = torch.Generator(device=device)
+    g.manual_seed(99)        # same data on every rank; each rank takes its slice of the global batch
+    n_img = 60000
+    xs = torch.rand((n_img, 784), device=device, generator=g)
+    ys = torch.nn.functional.one_hot(torch.randint(0, 10, (n_img,), device=device, generator=g), 10).float()
+    net = Net(LENET, ctx, seed=2)
+    net.set_math(args.math)
+    dp = DataParallel(net)
+    steps = max(10, args.steps)
+
+    def bench_train(global_batch, key):
+        local = global_batch // world
+        nb = n_img // global_batch
+        state = {"i": 0}
+
+        def step():
+            b = state["i"] % nb
+            state["i"] += 1
+            lo = b * global_batch + rank * local
+            dp.train_step(xs[lo:lo + local], ys[lo:lo + local], "entropy", "compat")
+
+        cnt = [0]
+        ms = time_steps(torch, step, steps, args.warmup, dist_on, counter=lambda: ctx.launches, count_out=cnt)
+        ms = max_over_ranks(torch, ms, dist_on, device)
+        per = ms / steps
+        byts = lenet_step_bytes(local)
+        out[key] = {
+            "value": global_batch * steps / (ms * 1e-3), "unit": "images/s", "ms_per_step": per, "global_batch": global_batch,
+            "per_gpu_batch": local, "optimizer": "Adagrad(1e-4) (what the reference runs)", "gpu_launches_per_step": cnt[0] / steps,
+            "math": "tf32 tcgen05" if args.math == 1 else "fp32 simt",
+            "roofline": {"bound": "hbm", "achieved": byts / (per * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": byts / (per * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts,
+                         "tflops": LENET_FLOP_PER_IMG * local / (per * 1e-3) / 1e12},
+        }
+
+    if world == 1:
+        bench_train(256, "train")                     # C3: batch 256
+        bench_train(2048, "train_b2048")              # C4's single-device reference point
+    else:
+        bench_train(2048, "train")                    # C4: global batch 2048 over the ranks (strong)
+        bench_train(256 * world, "train_weak")        # 256 per GPU (weak)
+
+    # e2e train step: host (pinned) batch in, loss out, every step
+    if world == 1:
+        xb = xs[:256].cpu().pin_memory()
+        yb = ys[:256].cpu().pin_memory()
+        xd, yd = torch.empty_like(xs[:256]), torch.empty_like(ys[:256])
+        lh = torch.zeros(1).pin_memory()
+
+        def e2e():
+            xd.copy_(xb, non_blocking=True)
+            yd.copy_(yb, non_blocking=True)
+            loss, _ = net.train_step(xd, yd, "entropy", "compat")
+            lh.copy_(loss, non_blocking=True)
+
+        ms = time_steps(torch, e2e, steps, 3, False)
+        out["train"]["e2e"] = {"value": 256 * steps / (ms * 1e-3), "unit": "images/s",
+                               "h2d_bytes_per_step": 256 * (784 + 10) * 4, "d2h_bytes_per_step": 4}
+
+    # inference: sess.run(argmax) (construct_inference.py:335-342), batched
+    for nb_, key in ((4096, "predict"), (99, "predict_c1_99_pictures"), (1, "predict_single")):
+        xb = xs[:nb_]
+
+        def pstep():
+            net.predict(xb)
+
+        ms = time_steps(torch, pstep, steps, 3, dist_on)
+        ms = max_over_ranks(torch, ms, dist_on, device)
+        out[key] = {"value": world * nb_ * steps / (ms * 1e-3), "unit": "images/s", "ms_per_batch": ms / steps, "batch": nb_}
+    return out
+
+
 def run_ours(args, rank, local_rank, world):
     import torch
     from cloud_server_b200.context import Context
@@ -321,11 +411,7 @@ def run_ours(args, rank, local_rank, world):
     }
 
     # ---- CNN train / predict sub-benchmarks (filled in when the net library is present)
-    try:
-        from cloud_server_b200 import bench_net
-        line.update(bench_net.run(ctx, args, rank, world, device, peaks, dist_on))
-    except ImportError:
-        pass
+    line.update(run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on))
 
     # ---- CPU baseline on this box's host cores (rank 0, N == 1 only), bounded sample
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -353,6 +439,7 @@ def main():
     ap.add_argument("--e2e-batch", type=int, default=1024, help="uploads per e2e step (host pinned)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--math", type=int, default=0, help="CNN math: 0 fp32 SIMT, 1 TF32 tcgen05")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
