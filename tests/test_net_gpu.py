@@ -102,19 +102,35 @@ def test_train_steps_post_step_weights(ctx, opt, lr):
     delta_ref = w - flat
     delta_got = got - flat
     if opt == "adam":
-        # Adam's m/(sqrt(v)+eps) is ~sign(g): parameters whose gradient is rounding noise (|g| below
-        # 1e-5 of the largest) move by +-lr in a direction fp32 summation order decides; they are
-        # excluded from the update comparison (their weights still agree to lr).
-        params = ref.unflatten(flat)
-        logits, cache = ref.forward(x, params, keep=True)
-        g0 = ref.flatten(ref.backward(ref.loss_and_grad(logits, y, "entropy")[1], params, cache))
-        keep = np.abs(g0) > 1e-4 * np.abs(g0).max()
-        assert keep.mean() > 0.5
-        assert rel_err(delta_got[keep], delta_ref[keep]) < 2e-3, opt
-        assert np.abs(got - w).max() <= 3 * 3 * lr
+        # Adam's m/(sqrt(v)+eps) is ~sign(g): where the gradient is rounding noise the step direction
+        # is decided by fp32 summation order, so the 3-step comparison is on the loss trajectory and
+        # a bound of the drift; the update arithmetic itself is pinned in test_optimizer_arithmetic.
+        assert np.abs(got - w).max() <= 2 * 3 * lr * 1.01
+        assert np.median(np.abs(delta_got - delta_ref)) < 1e-3 * np.abs(delta_ref).max()
     else:
         assert rel_err(delta_got, delta_ref) < 1e-3, opt          # the update itself, not just the weights
         assert rel_err(got, w) < 1e-5
+
+
+@pytest.mark.parametrize("opt,lr", [("adagrad", 0.05), ("sgd", 0.05), ("adam", 0.01)])
+def test_optimizer_arithmetic(ctx, opt, lr):
+    """ApplyAdagrad / ApplyGradientDescent / ApplyAdam on an injected gradient vector, 3 steps."""
+    from cloud_server_b200.net import Net
+    net = Net({"middle_layer": [{"layer": "connect", "hidden": 32}]}, ctx)
+    rng = np.random.default_rng(9)
+    w = net.get_params().copy()
+    o = {"adagrad": tfref.Adagrad(w.size, lr), "sgd": tfref.SGD(w.size, lr), "adam": tfref.Adam(w.size, lr)}[opt]
+    for step in range(3):
+        g = (rng.standard_normal(w.size) * 10.0 ** rng.integers(-6, 1, w.size)).astype(np.float32)
+        net.grads.copy_(torch.from_numpy(g).cuda())
+        net.apply(opt, lr)
+        o.apply(w, g)
+        assert rel_err(net.get_params(), w) < 2e-6, (opt, step)
+    st = net.get_state({"adagrad": 0, "sgd": 1, "adam": 2}[opt])
+    if opt == "adagrad":
+        assert rel_err(st, o.acc) < 1e-6
+    if opt == "adam":
+        assert rel_err(st[:w.size], o.m) < 1e-5 and rel_err(st[w.size:], o.v) < 1e-5
 
 
 def test_config_errors_and_defaults(ctx):
