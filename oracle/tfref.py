@@ -361,8 +361,9 @@ class Adam:
     def apply(self, w, g):
         self.t += 1
         lr_t = self.dt(self.lr * math.sqrt(1 - self.b2 ** self.t) / (1 - self.b1 ** self.t))
-        self.m += (g - self.m) * self.dt(1 - self.b1)
-        self.v += (g * g - self.v) * self.dt(1 - self.b2)
+        # TF's ApplyAdam evaluates (1 - beta) in the variable dtype: float32(1) - float32(0.999)
+        self.m += (g - self.m) * (self.dt(1) - self.dt(self.b1))
+        self.v += (g * g - self.v) * (self.dt(1) - self.dt(self.b2))
         w -= lr_t * self.m / (np.sqrt(self.v) + self.dt(self.eps))
 
 
