@@ -180,6 +180,25 @@ int nc_net_state_slots(nc_net* net, int opt);
 int nc_net_get_state(nc_net* net, int opt, float* host_state);
 int nc_net_set_state(nc_net* net, int opt, const float* host_state, int64_t global_step);
 
+/* ---- dense layer without any allocation -------------------------------------------------
+ * No counterpart in the reference: this entry point exists for hosts of the library that must not
+ * allocate device memory while serving -- a process whose own pool already owns all of HBM, a
+ * latency-critical request thread (cudaMalloc locks and may synchronise the whole device), or a
+ * tenant whose memory budget is audited.  It computes y[m][n] = x[m][k] . w[k][n] (+ bias[n]) --
+ * the arithmetic of one `connect` / output layer -- with the same deterministic split-K scheme as
+ * nc_net_forward, but keeps the partial sums in a fixed 4 MiB array inside the library image
+ * instead of a cudaMalloc'ed workspace.  It calls no cudaMalloc / cudaFree / allocating routine.
+ *   limit:   m * n <= 1 048 576 outputs (NC_EINVAL beyond that; split the batch or use nc_net_forward)
+ *   cost:    every GPU that loads the library holds those 4 MiB until the process exits
+ *   sharing: all calls on a device use the same array; it keeps the previous call's partial sums
+ *            (never read: every partial is written before it is summed, nothing needs zeroing).
+ *            Calls whose kernels overlap on the GPU (other streams / threads) race: serialise them.
+ *   set-up:  the first call on a device looks up the array's device address (no allocation);
+ *            make that first call before any stream capture on that device.
+ * x, w, bias (nullable), y are device pointers, row-major float32. */
+int nc_dense_forward_noalloc(nc_ctx* ctx, const float* x, const float* w, const float* bias,
+                             int m, int k, int n, float* y, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
