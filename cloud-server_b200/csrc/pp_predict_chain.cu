@@ -16,6 +16,7 @@
 //   phase 4  threshold / canvas (compat: the reference's in-place 220 write + IndexError)
 #include "nc_internal.h"
 #include <string.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -47,6 +48,215 @@ __device__ __forceinline__ int dp4a_us(unsigned a, unsigned b_signed, int c) {
 
 __device__ __forceinline__ int clip8(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
 
+// phases 3 + 4, shared by both kernels: vertical pass over s_temp[h][20], then the threshold /
+// canvas logic of construct_inference.py:317-330
+__device__ __forceinline__ void finish_picture(const PredHdr& hdr, const unsigned char* s_temp, unsigned char* s_small,
+                                               unsigned char* s_canvas, int* s_err, const int* __restrict__ g_kky, int compat,
+                                               float* __restrict__ out_f32, uint8_t* __restrict__ out_small20,
+                                               int* __restrict__ status, int nthreads) {
+    const int tid = threadIdx.x;
+    // ---------------- phase 3: vertical pass (ImagingResampleVertical_8bpc)
+    for (int o = tid; o < kOut * kOut; o += nthreads) {
+        const int yy = o / kOut, xx = o - yy * kOut;
+        const int y0 = hdr.ymin[yy], cnt = hdr.ycnt[yy];
+        const int* kk = g_kky + yy * hdr.ksize_y;
+        unsigned acc = 1u << 21;
+        for (int i = 0; i < cnt; ++i) acc += (unsigned)s_temp[(y0 + i) * kOut + xx] * (unsigned)__ldg(kk + i);
+        s_small[o] = (unsigned char)clip8((int)acc >> 22);
+    }
+    for (int i = tid; i < 784; i += nthreads) s_canvas[i] = 0;
+    if (tid == 0) *s_err = 0;
+    __syncthreads();
+
+    if (out_small20)
+        for (int o = tid; o < kOut * kOut; o += nthreads) out_small20[(long long)blockIdx.x * 400 + o] = s_small[o];
+
+    // ---------------- phase 4: construct_inference.py:317-330
+    if (!compat) {
+        for (int o = tid; o < kOut * kOut; o += nthreads) {
+            const int i = o / kOut, j = o - i * kOut;
+            if (s_small[o] > 150) s_canvas[(i + 4) * 28 + (j + 4)] = 1;
+        }
+    } else if (tid == 0) {
+        // sequential: the `elif arr[i][j] > 100: arr[bizar+i][bizar+j] = 220` statement feeds
+        // later iterations of the same scan and raises IndexError past row/column 15
+        int err = 0;
+        for (int i = 0; i < kOut && !err; ++i)
+            for (int j = 0; j < kOut; ++j) {
+                const int v = s_small[i * kOut + j];
+                if (v > 150) {
+                    s_canvas[(i + 4) * 28 + (j + 4)] = 1;
+                } else if (v > 100) {
+                    if (i + 4 >= kOut || j + 4 >= kOut) { err = 1; break; }
+                    s_small[(i + 4) * kOut + (j + 4)] = 220;
+                }
+            }
+        *s_err = err;
+    }
+    __syncthreads();
+    const int err = *s_err;
+    if (tid == 0 && status) status[blockIdx.x] = err;
+    const float v254 = (float)(254.0 / 255.0);
+    for (int i = tid; i < 784; i += nthreads)
+        out_f32[(long long)blockIdx.x * 784 + i] = (!err && s_canvas[i]) ? v254 : 0.0f;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// TMA-staged variant (C == 3, rows 16-byte aligned): raw rows arrive in shared memory through
+// cp.async.bulk (one bulk copy per 8-row stage, double buffered, mbarrier completion), so no warp
+// ever waits on a global load; rgb2l reads the staged bytes with conflict-free LDS.128 and uses
+// dp2a (16-bit coefficient pairs x pixel bytes): 8 dp2a + 3 prmt per 4 pixels.
+// ---------------------------------------------------------------------------------------------
+constexpr int kStageRows = 8;
+constexpr int kBlockRows = 16;    // gray block consumed by one horizontal pass (2 stages)
+
+__device__ __forceinline__ unsigned dp2a_lo(unsigned coef16x2, unsigned px, unsigned c) {
+    unsigned d;
+    asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(coef16x2), "r"(px), "r"(c));
+    return d;
+}
+__device__ __forceinline__ unsigned dp2a_hi(unsigned coef16x2, unsigned px, unsigned c) {
+    unsigned d;
+    asm("dp2a.hi.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(coef16x2), "r"(px), "r"(c));
+    return d;
+}
+// 12 stream bytes (4 pixels) -> 4 gray bytes packed in one word
+__device__ __forceinline__ unsigned gray4(unsigned w0, unsigned w1, unsigned w2, unsigned A01, unsigned A2_, unsigned A_0,
+                                          unsigned A12) {
+    const unsigned s0 = dp2a_hi(A2_, w0, dp2a_lo(A01, w0, 0x8000u));     // bytes 0,1,2 of w0
+    const unsigned s1 = dp2a_lo(A12, w1, dp2a_hi(A_0, w0, 0x8000u));     // byte 3 of w0, bytes 0,1 of w1
+    const unsigned s2 = dp2a_lo(A2_, w2, dp2a_hi(A01, w1, 0x8000u));     // bytes 2,3 of w1, byte 0 of w2
+    const unsigned s3 = dp2a_hi(A12, w2, dp2a_lo(A_0, w2, 0x8000u));     // bytes 1,2,3 of w2
+    // L = sum >> 16 = byte 2 of each sum (sum < 2^24)
+    const unsigned t01 = __byte_perm(s0, s1, 0x0062), t23 = __byte_perm(s2, s3, 0x0062);
+    return __byte_perm(t01, t23, 0x5410);
+}
+
+__device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t}\n" ::"r"(bar_addr), "r"(parity) : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads)
+predict_chain_tma_kernel(const uint8_t* __restrict__ src, long long img_stride, int h, int w,
+                         const PredHdr* __restrict__ g_hdr, const uint4* __restrict__ g_groups,
+                         const int* __restrict__ g_kky, unsigned A01, unsigned A2_, unsigned A_0, unsigned A12,
+                         int compat, float* __restrict__ out_f32, uint8_t* __restrict__ out_small20,
+                         int* __restrict__ status, int wq, unsigned ipr, unsigned ipr_magic) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ PredHdr hdr;
+    __shared__ unsigned char s_small[kOut * kOut];
+    __shared__ unsigned char s_canvas[784];
+    __shared__ int s_err;
+    __shared__ __align__(8) unsigned long long s_bar[2];
+
+    const int tid = threadIdx.x;
+    for (int i = tid; i < (int)(sizeof(PredHdr) / 4); i += kThreads) ((int*)&hdr)[i] = ((const int*)g_hdr)[i];
+    const unsigned row_bytes = (unsigned)w * 3u;
+    const unsigned stage_bytes = kStageRows * row_bytes;
+    unsigned char* raw = smem;                                            // 2 stages of raw rows
+    __syncthreads();
+    uint4* s_groups = reinterpret_cast<uint4*>(smem + 2 * stage_bytes);
+    unsigned* s_gbuf = reinterpret_cast<unsigned*>(smem + 2 * stage_bytes + (size_t)hdr.total_groups * 16);
+    unsigned char* s_temp = reinterpret_cast<unsigned char*>(s_gbuf + (size_t)kBlockRows * wq);
+
+    const uint8_t* base = src + (long long)blockIdx.x * img_stride;
+    const int nstages = (h + kStageRows - 1) / kStageRows;
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&s_bar[0]);
+    const unsigned raw0 = (unsigned)__cvta_generic_to_shared(raw);
+
+    auto issue = [&](int s) {      // one elected thread: arm the barrier, start the bulk copy of stage s
+        const int r0 = s * kStageRows;
+        const unsigned bytes = (unsigned)min(kStageRows, h - r0) * row_bytes;
+        const unsigned bar = bar0 + 8u * (s & 1);
+        const unsigned dst = raw0 + (s & 1) * stage_bytes;
+        const uint8_t* gsrc = base + (long long)r0 * row_bytes;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(gsrc), "r"(bytes), "r"(bar) : "memory");
+    };
+
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        issue(0);
+        if (nstages > 1) issue(1);
+    }
+    for (int i = tid; i < hdr.total_groups; i += kThreads) s_groups[i] = g_groups[i];
+    for (int i = tid; i < kBlockRows * wq; i += kThreads) s_gbuf[i] = 0u;
+    __syncthreads();
+
+    // horizontal-pass task of this thread: (row pair, output column, half of the taps)
+    const int half = tid & 1, pr = (tid >> 1) & 7, xx = tid >> 4;
+    const int ng = hdr.ng[xx], gh = (ng + 1) >> 1;
+    const int g_begin = half ? gh : 0, g_end = half ? ng : gh;
+    const unsigned* ra0 = s_gbuf + (size_t)(2 * pr) * wq + (hdr.a0[xx] >> 2);
+    const uint4* wg = s_groups + hdr.goff[xx];
+
+    for (int s = 0; s < nstages; ++s) {
+        const int r0 = s * kStageRows;
+        const int rows = min(kStageRows, h - r0);
+        mbar_wait(bar0 + 8u * (s & 1), (unsigned)((s >> 1) & 1));
+        // ---------------- phase 1: staged bytes -> rgb2l -> gray block rows (s&1)*8 ..
+        const unsigned char* rbuf = raw + (size_t)(s & 1) * stage_bytes;
+        unsigned* gdst = s_gbuf + (size_t)((s & 1) * kStageRows) * wq;
+        const unsigned items = (unsigned)rows * ipr;                      // ipr = 16-pixel items per row
+        for (unsigned it = tid; it < items; it += kThreads) {
+            const unsigned rl = ipr_magic ? __umulhi(it, ipr_magic) : it;
+            const unsigned g16 = it - rl * ipr;
+            const uint4* p = reinterpret_cast<const uint4*>(rbuf + (size_t)rl * row_bytes + (size_t)g16 * 48);
+            const uint4 q0 = p[0], q1 = p[1], q2 = p[2];
+            uint2 o0, o1;
+            o0.x = gray4(q0.x, q0.y, q0.z, A01, A2_, A_0, A12);
+            o0.y = gray4(q0.w, q1.x, q1.y, A01, A2_, A_0, A12);
+            o1.x = gray4(q1.z, q1.w, q2.x, A01, A2_, A_0, A12);
+            o1.y = gray4(q2.y, q2.z, q2.w, A01, A2_, A_0, A12);
+            uint2* d = reinterpret_cast<uint2*>(gdst + (size_t)rl * wq + g16 * 4);   // wq even: 8-byte aligned
+            d[0] = o0;
+            d[1] = o1;
+        }
+        __syncthreads();          // raw stage consumed, gray rows visible
+        if (tid == 0 && s + 2 < nstages) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic reads before async writes
+            issue(s + 2);
+        }
+        if ((s & 1) || s == nstages - 1) {
+            // ---------------- phase 2: horizontal pass over the 16-row gray block
+            const int b0 = (s & ~1) * kStageRows;                 // first picture row of this block
+            const int brow = min(kBlockRows, h - b0);
+            const unsigned* ra = ra0;
+            const unsigned* rb = ra0 + wq;
+            unsigned s0a = 0, s1a = 0, s0b = 0, s1b = 0;
+            int s2a = 0, s2b = 0;
+#pragma unroll 4
+            for (int i = g_begin; i < g_end; ++i) {
+                const uint4 k = wg[i];
+                const unsigned pa = ra[i], pb = rb[i];
+                s0a = dp4a_uu(pa, k.x, s0a); s1a = dp4a_uu(pa, k.y, s1a); s2a = dp4a_us(pa, k.z, s2a);
+                s0b = dp4a_uu(pb, k.x, s0b); s1b = dp4a_uu(pb, k.y, s1b); s2b = dp4a_us(pb, k.z, s2b);
+            }
+            unsigned va = s0a + (s1a << 8) + ((unsigned)s2a << 16);
+            unsigned vb = s0b + (s1b << 8) + ((unsigned)s2b << 16);
+            va += __shfl_xor_sync(0xffffffffu, va, 1);
+            vb += __shfl_xor_sync(0xffffffffu, vb, 1);
+            const int row = 2 * pr + half;
+            if (row < brow) {
+                const unsigned v = half ? vb : va;
+                s_temp[(b0 + row) * kOut + xx] = (unsigned char)clip8((int)(v + (1u << 21)) >> 22);
+            }
+            __syncthreads();      // gray block free for the next two stages
+        }
+    }
+    finish_picture(hdr, s_temp, s_small, s_canvas, &s_err, g_kky, compat, out_f32, out_small20, status, kThreads);
+}
+
 template <int C>
 __global__ void __launch_bounds__(kThreads)
 predict_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h, int w,
@@ -55,7 +265,7 @@ predict_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int 
                      int r_coef, int g_coef, int b_coef,   // applied to stream bytes 0,1,2
                      int compat, float* __restrict__ out_f32, uint8_t* __restrict__ out_small20,
                      int* __restrict__ status, int rb, int wq, unsigned wq_src, unsigned wq_magic) {
-    extern __shared__ __align__(16) unsigned char smem[];
+    extern __shared__ __align__(128) unsigned char smem[];
     __shared__ PredHdr hdr;
     __shared__ unsigned char s_small[kOut * kOut];
     __shared__ unsigned char s_canvas[784];
@@ -161,50 +371,7 @@ predict_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int 
         __syncthreads();
     }
 
-    // ---------------- phase 3: vertical pass (ImagingResampleVertical_8bpc)
-    for (int o = tid; o < kOut * kOut; o += kThreads) {
-        const int yy = o / kOut, xx = o - yy * kOut;
-        const int y0 = hdr.ymin[yy], cnt = hdr.ycnt[yy];
-        const int* kk = g_kky + yy * hdr.ksize_y;
-        unsigned acc = 1u << 21;
-        for (int i = 0; i < cnt; ++i) acc += (unsigned)s_temp[(y0 + i) * kOut + xx] * (unsigned)__ldg(kk + i);
-        s_small[o] = (unsigned char)clip8((int)acc >> 22);
-    }
-    for (int i = tid; i < 784; i += kThreads) s_canvas[i] = 0;
-    if (tid == 0) s_err = 0;
-    __syncthreads();
-
-    if (out_small20)
-        for (int o = tid; o < kOut * kOut; o += kThreads) out_small20[(long long)blockIdx.x * 400 + o] = s_small[o];
-
-    // ---------------- phase 4: construct_inference.py:317-330
-    if (!compat) {
-        for (int o = tid; o < kOut * kOut; o += kThreads) {
-            const int i = o / kOut, j = o - i * kOut;
-            if (s_small[o] > 150) s_canvas[(i + 4) * 28 + (j + 4)] = 1;
-        }
-    } else if (tid == 0) {
-        // sequential: the `elif arr[i][j] > 100: arr[bizar+i][bizar+j] = 220` statement feeds
-        // later iterations of the same scan and raises IndexError past row/column 15
-        int err = 0;
-        for (int i = 0; i < kOut && !err; ++i)
-            for (int j = 0; j < kOut; ++j) {
-                const int v = s_small[i * kOut + j];
-                if (v > 150) {
-                    s_canvas[(i + 4) * 28 + (j + 4)] = 1;
-                } else if (v > 100) {
-                    if (i + 4 >= kOut || j + 4 >= kOut) { err = 1; break; }
-                    s_small[(i + 4) * kOut + (j + 4)] = 220;
-                }
-            }
-        s_err = err;
-    }
-    __syncthreads();
-    const int err = s_err;
-    if (tid == 0 && status) status[blockIdx.x] = err;
-    const float v254 = (float)(254.0 / 255.0);
-    for (int i = tid; i < 784; i += kThreads)
-        out_f32[(long long)blockIdx.x * 784 + i] = (!err && s_canvas[i]) ? v254 : 0.0f;
+    finish_picture(hdr, s_temp, s_small, s_canvas, &s_err, g_kky, compat, out_f32, out_small20, status, kThreads);
 }
 
 struct PredTabDev {
@@ -323,6 +490,25 @@ extern "C" int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h
     plane(8, gc.hi);
     const unsigned magic = wq_src == 1 ? 0u : (unsigned)((0x100000000ull + (unsigned)wq_src - 1) / (unsigned)wq_src);
     cudaStream_t st = (cudaStream_t)stream;
+    // TMA-staged kernel: 3 channels, rows and pictures 16-byte aligned, the plan fits shared memory
+    if (c == 3 && (w % 16) == 0 && (reinterpret_cast<uintptr_t>(src) % 16) == 0 && (img_stride % 16) == 0 && h >= 16 &&
+        !getenv("NC_PREDICT_NO_TMA")) {
+        const int wq2 = w / 4 + 2;                 // even, = 2 mod 4: 8-byte stores, row pairs on distinct banks
+        const size_t stage = (size_t)8 * w * 3;
+        const size_t smem2 = 2 * stage + (size_t)tabs.hdr.total_groups * 16 + (size_t)16 * wq2 * 4 + ((size_t)h * kOut + 15) / 16 * 16;
+        if (smem2 <= 220 * 1024) {
+            const unsigned A01 = (unsigned)c0 | ((unsigned)c1 << 16), A2_ = (unsigned)c2, A_0 = (unsigned)c0 << 16,
+                           A12 = (unsigned)c1 | ((unsigned)c2 << 16);
+            const unsigned ipr = (unsigned)w / 16;
+            const unsigned ipr_magic = ipr == 1 ? 0u : (unsigned)((0x100000000ull + ipr - 1) / ipr);
+            NC_CUDA(ctx, cudaFuncSetAttribute(predict_chain_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+            predict_chain_tma_kernel<<<n, kThreads, smem2, st>>>(src, img_stride, h, w, tabs.d_hdr, tabs.d_groups, tabs.d_kky,
+                                                                  A01, A2_, A_0, A12, compat, out_f32, out_small20, status,
+                                                                  wq2, ipr, ipr_magic);
+            NC_LAUNCH_CHECK(ctx);
+            return NC_OK;
+        }
+    }
     if (c == 3) {
         NC_CUDA(ctx, cudaFuncSetAttribute(predict_chain_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         predict_chain_kernel<3><<<n, kThreads, smem, st>>>(src, img_stride, h, w, tabs.d_hdr, tabs.d_groups, tabs.d_kky,

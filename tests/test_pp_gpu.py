@@ -179,6 +179,22 @@ def test_predict_chain_random_shapes_vs_oracle(ctx):
                     assert int(status[i]) == 1
 
 
+def test_predict_chain_both_kernels_agree(ctx, monkeypatch):
+    """The TMA-staged kernel (aligned 3-channel pictures) and the generic kernel give identical bytes."""
+    rng = np.random.default_rng(33)
+    for (h, w) in [(16, 16), (40, 64), (97, 160), (768, 1024), (333, 1008)]:
+        imgs = dev(rng.integers(0, 256, (3, h, w, 3), np.uint8))
+        monkeypatch.delenv("NC_PREDICT_NO_TMA", raising=False)
+        o1, s1, m1 = ctx.predict_chain(imgs, compat=True, want_small20=True)
+        monkeypatch.setenv("NC_PREDICT_NO_TMA", "1")
+        o2, s2, m2 = ctx.predict_chain(imgs, compat=True, want_small20=True)
+        monkeypatch.delenv("NC_PREDICT_NO_TMA", raising=False)
+        assert torch.equal(m1, m2), (h, w)
+        assert torch.equal(o1, o2) and torch.equal(s1, s2)
+        es = R.pil_resize_bicubic_l(R.pil_rgb2l(imgs[1].cpu().numpy()))
+        assert np.array_equal(m1[1].cpu().numpy(), es), (h, w)
+
+
 def test_predict_chain_full_size_properties(ctx):
     rng = np.random.default_rng(32)
     n = 48
