@@ -12,6 +12,8 @@
 // (float32 for the first 80 interleaved elements of a row -- OpenCV's 128-bit SIMD body -- and
 // integer for the tail, see oracle/pp_restate.py:cv_resize_cubic_u8); stage 3 gray + normalise.
 #include "nc_internal.h"
+#include <stdlib.h>
+#include <string.h>
 
 namespace {
 
@@ -123,6 +125,116 @@ train_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h,
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Row-streaming variant.  At 1024 -> 28 the 4-tap groups of a source row are 110 B apart, so DRAM
+// (64 B bursts) already moves the whole 112 source rows of a picture (measured: 344 KB / picture =
+// 112 x 3072 B).  This kernel therefore streams exactly those rows: each warp owns 4 of the 28
+// output rows; for an output row it bulk-copies the <= 4 consecutive source rows (one
+// cp.async.bulk, 12 KB at 1024 x 3) into its private shared-memory stage, waits on its mbarrier,
+// and each lane computes one output pixel (16 taps x 3 channels, vertical pass, gray) from shared
+// memory.  Same arithmetic, same bytes out; DRAM pages are read sequentially and there is no
+// per-byte global load left.  Works on device memory and on pinned host memory (zero copy).
+// ---------------------------------------------------------------------------------------------
+constexpr int kRowWarps = 7;                 // 28 output rows / 7 warps = 4 rows per warp
+constexpr int kRowThreads = kRowWarps * 32;
+
+__global__ void __launch_bounds__(kRowThreads)
+train_chain_rows_kernel(const uint8_t* __restrict__ src, long long img_stride, int h, int w,
+                        const __grid_constant__ TrainTabs tabs, uint8_t* __restrict__ out_u8,
+                        float* __restrict__ out_f32, unsigned stage_bytes) {
+    constexpr int C = 3, E = 28 * C, NSIMD = (E / 8) * 8;
+    extern __shared__ __align__(128) unsigned char stage_mem[];
+    __shared__ int s_xofs[28][4];
+    __shared__ int s_xcoef[28][4];
+    __shared__ __align__(8) unsigned long long s_bar[kRowWarps];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < 112; i += kRowThreads) {
+        s_xofs[i >> 2][i & 3] = tabs.x.ofs[i >> 2][i & 3] * C;
+        s_xcoef[i >> 2][i & 3] = tabs.x.coef[i >> 2][i & 3];
+    }
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
+    unsigned char* stage = stage_mem + (size_t)warp * stage_bytes;
+    const unsigned stage_addr = (unsigned)__cvta_generic_to_shared(stage);
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const uint8_t* base = src + (long long)blockIdx.x * img_stride;
+    const unsigned row_bytes = (unsigned)w * C;
+    const float inv255 = (float)(1.0 / 255.0);
+    const float scale = 1.0f / (2048.0f * 2048.0f);
+
+    for (int j = 0; j < 4; ++j) {
+        const int dy = warp * 4 + j;
+        const int r_lo = tabs.y.ofs[dy][0], r_hi = tabs.y.ofs[dy][3];     // clamped, non-decreasing
+        if (lane == 0) {
+            const unsigned bytes = (unsigned)(r_hi - r_lo + 1) * row_bytes;
+            if (j > 0) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(stage_addr), "l"(base + (long long)r_lo * row_bytes), "r"(bytes), "r"(bar) : "memory");
+        }
+        // wait for the bytes of this output row (phase parity j & 1)
+        {
+            const unsigned parity = (unsigned)(j & 1);
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "W_LOOP:\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                "@p bra W_DONE;\n\t"
+                "bra W_LOOP;\n\t"
+                "W_DONE:\n\t}\n" ::"r"(bar), "r"(parity) : "memory");
+        }
+        if (lane < 28) {
+            const int dx = lane;
+            int S[4][C];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const unsigned char* rp = stage + (size_t)(tabs.y.ofs[dy][k] - r_lo) * row_bytes;
+                int acc[C] = {0, 0, 0};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const unsigned char* p = rp + s_xofs[dx][t];
+                    const int a = s_xcoef[dx][t];
+#pragma unroll
+                    for (int c = 0; c < C; ++c) acc[c] += (int)p[c] * a;
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) S[k][c] = acc[c];
+            }
+            const int b0 = tabs.y.coef[dy][0], b1 = tabs.y.coef[dy][1], b2 = tabs.y.coef[dy][2], b3 = tabs.y.coef[dy][3];
+            const float f0 = __fmul_rn((float)b0, scale), f1 = __fmul_rn((float)b1, scale);
+            const float f2 = __fmul_rn((float)b2, scale), f3 = __fmul_rn((float)b3, scale);
+            int col[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const int e = dx * C + c;
+                int v;
+                if (e < NSIMD) {
+                    float t = __fmul_rn(__int2float_rn(S[3][c]), f3);
+                    t = __fadd_rn(__fmul_rn(__int2float_rn(S[2][c]), f2), t);
+                    t = __fadd_rn(__fmul_rn(__int2float_rn(S[1][c]), f1), t);
+                    t = __fadd_rn(__fmul_rn(__int2float_rn(S[0][c]), f0), t);
+                    v = __float2int_rn(t);
+                } else {
+                    const int sum = S[0][c] * b0 + S[1][c] * b1 + S[2][c] * b2 + S[3][c] * b3;
+                    v = (sum + (1 << 21)) >> 22;
+                }
+                col[c] = v < 0 ? 0 : (v > 255 ? 255 : v);
+            }
+            const int g = (3735 * col[0] + 19235 * col[1] + 9798 * col[2] + (1 << 14)) >> 15;
+            const long long o = (long long)blockIdx.x * 784 + dy * 28 + dx;
+            if (out_u8) out_u8[o] = (uint8_t)g;
+            if (out_f32) out_f32[o] = __fmul_rn((float)g, inv255);
+        }
+        __syncwarp();     // every lane is done with the stage before lane 0 overwrites it
+    }
+}
+
 }  // namespace
 
 static int launch_train_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
@@ -134,6 +246,18 @@ static int launch_train_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int
         nc_cv_cubic_axis(h, 28, &tabs.y);
     } else {
         memset(&tabs, 0, sizeof(tabs));
+    }
+    // row-streaming kernel: 3 channels, 16-byte aligned rows, source rows close enough together that
+    // DRAM would fetch them whole anyway (tap spacing <= 192 B), and the 7 stages fit shared memory
+    const long long row_bytes = (long long)w * c;
+    if (c == 3 && !identity && (row_bytes % 16) == 0 && (reinterpret_cast<uintptr_t>(src) % 16) == 0 && (img_stride % 16) == 0 &&
+        h >= 4 && row_bytes * 4 * kRowWarps <= 200 * 1024 && row_bytes <= 28 * 192 && !getenv("NC_TRAIN_NO_ROWS")) {
+        const unsigned stage_bytes = (unsigned)(row_bytes * 4);
+        const size_t smem = (size_t)stage_bytes * kRowWarps;
+        NC_CUDA(ctx, cudaFuncSetAttribute(train_chain_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        train_chain_rows_kernel<<<n, kRowThreads, smem, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, stage_bytes);
+        NC_LAUNCH_CHECK(ctx);
+        return NC_OK;
     }
     if (c == 3)
         train_chain_kernel<3><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity);

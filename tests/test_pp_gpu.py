@@ -106,9 +106,24 @@ def test_train_chain_full_size_batch_properties(ctx):
     assert e8.shape[0] == 0 and ef.shape[0] == 0
 
 
+def test_train_chain_both_kernels_agree(ctx, monkeypatch):
+    """Row-streaming (TMA) kernel and tap-gather kernel: identical bytes; both equal the oracle."""
+    rng = np.random.default_rng(25)
+    for (h, w) in [(32, 32), (29, 48), (100, 160), (768, 1024), (1080, 1920), (480, 640), (5, 1776)]:
+        imgs = dev(rng.integers(0, 256, (3, h, w, 3), np.uint8))
+        monkeypatch.delenv("NC_TRAIN_NO_ROWS", raising=False)
+        a8, af = ctx.resize_gray_norm(imgs)
+        monkeypatch.setenv("NC_TRAIN_NO_ROWS", "1")
+        b8, bf = ctx.resize_gray_norm(imgs)
+        monkeypatch.delenv("NC_TRAIN_NO_ROWS", raising=False)
+        assert torch.equal(a8, b8) and torch.equal(af, bf), (h, w)
+        e8, ef = R.train_chain(imgs[2].cpu().numpy())
+        assert np.array_equal(a8[2].cpu().numpy(), e8), (h, w)
+
+
 def test_train_chain_host_buffers(ctx):
     rng = np.random.default_rng(24)
-    imgs = rng.integers(0, 256, (5, 200, 300, 3), np.uint8)
+    imgs = rng.integers(0, 256, (5, 200, 304, 3), np.uint8)      # 16-byte rows: row-streaming kernel over PCIe
     want = np.stack([R.train_chain(i)[0] for i in imgs])
     pinned = torch.from_numpy(imgs).pin_memory()
     u8, _ = ctx.resize_gray_norm(pinned)
@@ -118,6 +133,10 @@ def test_train_chain_host_buffers(ctx):
     u8b, _ = ctx.resize_gray_norm(pageable)
     torch.cuda.synchronize()
     assert np.array_equal(u8b.cpu().numpy(), want)
+    odd = rng.integers(0, 256, (3, 77, 301, 3), np.uint8)        # unaligned rows: tap-gather kernel over PCIe
+    u8c, _ = ctx.resize_gray_norm(torch.from_numpy(odd).pin_memory())
+    torch.cuda.synchronize()
+    assert np.array_equal(u8c.cpu().numpy(), np.stack([R.train_chain(i)[0] for i in odd]))
 
 
 def test_train_chain_bad_arguments(ctx):
