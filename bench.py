@@ -106,52 +106,60 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the same cv2 calls the reference makes, on the host cores
 # ------------------------------------------------------------------------------------------
-def cpu_train_chain_throughput(seconds, threads, sample_n=128):
-    """oracle/cvref.train_chain (cv2.resize INTER_CUBIC -> BGR2GRAY -> *1/255, the calls of
-    apps/preprocess/preprocess.py:29,40 + construct_distribute.py:503-504) over a bounded sample."""
-    from concurrent.futures import ThreadPoolExecutor
-    from oracle import cvref
+_CPU_SAMPLE = None
+
+
+def _cpu_init(sample_n):
+    """worker initialiser: every process builds the same bounded sample once"""
+    global _CPU_SAMPLE
     import cv2
-    cv2.setNumThreads(1)   # parallelism comes from one picture per worker thread
-    rng = np.random.default_rng(0)
-    sample = rng.integers(0, 256, (sample_n, H, W, C), np.uint8)
+    cv2.setNumThreads(1)   # parallelism comes from one picture per worker process
+    _CPU_SAMPLE = np.random.default_rng(0).integers(0, 256, (sample_n, H, W, C), np.uint8)
 
-    def work(i):
-        cvref.train_chain(sample[i % sample_n])
-        return 1
 
-    done = 0
-    t0 = time.perf_counter()
-    with ThreadPoolExecutor(threads) as ex:
+def _cpu_work(i):
+    """One picture through the reference's own library calls, in memory: cv2.resize INTER_CUBIC ->
+    BGR2GRAY -> *1/255 (preprocess.py:29,40; construct_distribute.py:503-504) and PIL convert('L') ->
+    resize((20,20)) -> threshold/canvas -> /255 (construct_inference.py:312-330)."""
+    from oracle import cvref
+    img = _CPU_SAMPLE[i % len(_CPU_SAMPLE)]
+    cvref.train_chain(img)
+    cvref.predict_chain(img[:, :, ::-1], compat=False)
+    return 1
+
+
+def _cpu_pool(procs, sample_n):
+    import multiprocessing as mp
+    return mp.get_context("fork").Pool(procs, initializer=_cpu_init, initargs=(sample_n,))
+
+
+def cpu_baseline_throughput(seconds, procs, sample_n=16):
+    with _cpu_pool(procs, sample_n) as pool:
+        pool.map(_cpu_work, range(procs))          # warm-up: sample built, libraries loaded
+        done = 0
+        t0 = time.perf_counter()
         while True:
-            done += sum(ex.map(work, range(done, done + sample_n)))
+            done += sum(pool.map(_cpu_work, range(done, done + 8 * procs), chunksize=2))
             dt = time.perf_counter() - t0
             if dt >= seconds:
                 break
     return done / dt, done, dt
 
 
+WORKLOAD = ("C2 batch preprocess: %d synthetic 1024x768x3 uint8 uploads per GPU through the whole preprocess half -> "
+            "28x28 float32: train-side chain (cv2-exact cubic resize -> gray -> *1/255) and predict-side chain "
+            "(PIL-exact L -> antialiased bicubic 20x20 -> threshold -> canvas -> /255)")
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    per_step = 128
-    from concurrent.futures import ThreadPoolExecutor
-    from oracle import cvref
-    import cv2
-    cv2.setNumThreads(1)
-    rng = np.random.default_rng(0)
-    sample = rng.integers(0, 256, (per_step, H, W, C), np.uint8)
-    reps = 8   # one step = 8 passes over the 128-picture sample = 1024 pictures
-
-    def work(i):
-        cvref.train_chain(sample[i % per_step])
-        return 1
-
-    with ThreadPoolExecutor(threads) as ex:
+    per_step = 256
+    with _cpu_pool(threads, 16) as pool:
         def step():
-            return sum(ex.map(work, range(per_step * reps)))
-        for _ in range(args.warmup):
+            return sum(pool.map(_cpu_work, range(per_step), chunksize=2))
+        for _ in range(min(args.warmup, 1)):
             step()
         t0 = time.perf_counter()
         n = 0
@@ -163,12 +171,11 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "images/sec", "value": val, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C2 batch preprocess: 1024x768x3 uint8 uploads -> 28x28 float32 (train-side chain)",
-                   "pictures_per_step": per_step * reps},
+        "config": {"workload": WORKLOAD % per_step, "pictures_per_step": per_step},
         "cpu_baseline": {"value": val, "unit": "images/s", "cores": threads, "kind": "port",
-                         "sample": "%d distinct 1024x768x3 pictures cycled, %d per step; the reference's own cv2 calls "
-                                   "(resize INTER_CUBIC, BGR2GRAY, *1/255) in memory, IPP off, one picture per thread"
-                                   % (per_step, per_step * reps)},
+                         "sample": "16 distinct 1024x768x3 pictures per worker cycled, %d per step; the reference's own cv2 / "
+                                   "Pillow calls for both chains, in memory (no JPEG), IPP off, one worker process per core"
+                                   % per_step},
         "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -315,100 +322,96 @@ def run_ours(args, rank, local_rank, world):
     g = torch.Generator(device=device)
     g.manual_seed(1234 + rank)
     batch = torch.randint(0, 256, (n, H, W, C), dtype=torch.uint8, device=device, generator=g)
-    out_u8 = torch.empty((n, 28, 28), dtype=torch.uint8, device=device)
-    out_f32 = torch.empty((n, 784), dtype=torch.float32, device=device)
+    outs = (torch.empty((n, 28, 28), dtype=torch.uint8, device=device),
+            torch.empty((n, 784), dtype=torch.float32, device=device),
+            torch.empty((n, 784), dtype=torch.float32, device=device))
 
-    def step():
-        ctx.resize_gray_norm(batch, out_u8=out_u8, out_f32=out_f32)
+    def step():            # one pass of the preprocess half over the batch: 2 kernel launches
+        ctx.preprocess_uploads(batch, channel_order="BGR", out=outs)
+
+    def step_train():
+        ctx.resize_gray_norm(batch, out_u8=outs[0], out_f32=outs[1])
+
+    def step_pred():
+        ctx.predict_chain(batch, channel_order="BGR", out=outs[2])
 
     sampler = ClockSampler(local_rank)
     sampler.start()
     cnt = [0]
     ms = time_steps(torch, step, args.steps, args.warmup, dist_on, counter=lambda: ctx.launches, count_out=cnt)
     launches = cnt[0]
-    # keep the same kernel running ~0.5 s more so the NVML sampler sees clocks under this load
+    # keep the same kernels running ~0.5 s more so the NVML sampler sees clocks under this load
     t_end = time.perf_counter() + 0.5
     while time.perf_counter() < t_end:
-        for _ in range(20):
+        for _ in range(5):
             step()
         torch.cuda.synchronize()
     sampler.stop()
     ms_max = max_over_ranks(torch, ms, dist_on, device)
     value = world * n * args.steps / (ms_max * 1e-3)
-    kern_ms = ms / args.steps
-    achieved = ALG_BYTES_TRAIN_CHAIN * n / (kern_ms * 1e-3) / 1e9
+    # each kernel alone, same inputs (per-launch duration for the rooflines)
+    ms_t = time_steps(torch, step_train, args.steps, 3, dist_on) / args.steps
+    ms_p = time_steps(torch, step_pred, args.steps, 3, dist_on) / args.steps
+    ach_t = ALG_BYTES_TRAIN_CHAIN * n / (ms_t * 1e-3) / 1e9
+    ach_p = ALG_BYTES_PREDICT_CHAIN * n / (ms_p * 1e-3) / 1e9
+    tr_t, tr_p = traffic.get("train_chain_rows_kernel"), traffic.get("predict_chain_tma_kernel")
+    peak = peaks["hbm_gbs"]
 
     line = {
         "metric": "images/sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "C2 batch preprocess: %d synthetic 1024x768x3 uint8 uploads per GPU -> 28x28 float32 "
-                               "(train-side chain: cv2-exact cubic resize -> gray -> *1/255)" % n,
-                   "pictures_per_gpu": n, "parallelism": "replicas x%d (no collective)" % world,
+        "config": {"workload": WORKLOAD % n, "pictures_per_gpu": n, "parallelism": "replicas x%d (no collective)" % world,
                    "l2": "inputs (%.2f GB) larger than L2" % (n * H * W * C / 1e9)},
         "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / peaks["hbm_gbs"], "traffic": traffic.get("train_chain_kernel"),
-                     "kernel": "train_chain_kernel<3>", "peak_source": peak_src + " (burst copy bandwidth)",
-                     "algorithmic_bytes_per_picture": ALG_BYTES_TRAIN_CHAIN,
-                     "note": "4x4-tap gather: DRAM moves whole sectors, see traffic and DESIGN.md"},
+        "roofline": {"bound": "hbm", "achieved": ach_p, "peak": peak, "unit": "GB/s", "frac": ach_p / peak,
+                     "traffic": tr_p * n if tr_p else None, "kernel": "predict_chain_tma_kernel (dominant: %.0f%% of the step)"
+                     % (100 * ms_p / (ms_p + ms_t)), "peak_source": peak_src + " (burst copy bandwidth)",
+                     "algorithmic_bytes_per_launch": ALG_BYTES_PREDICT_CHAIN * n, "launch_ms": ms_p},
+        "train_side_chain": {"value": world * n / (ms_t * 1e-3), "unit": "images/s", "launch_ms": ms_t,
+                             "roofline": {"bound": "hbm", "achieved": ach_t, "peak": peak, "unit": "GB/s", "frac": ach_t / peak,
+                                          "traffic": tr_t * n if tr_t else None, "kernel": "train_chain_rows_kernel",
+                                          "algorithmic_bytes_per_launch": ALG_BYTES_TRAIN_CHAIN * n,
+                                          "dram_frac": (tr_t * n / (ms_t * 1e-3) / 1e9 / peak) if tr_t else None,
+                                          "note": "4x4-tap resize: DRAM moves the 112 source rows whole (64 B bursts, taps "
+                                                  "110 B apart), 8.3x the algorithmic bytes; dram_frac = ncu traffic / time / peak"}},
+        "predict_side_chain": {"value": world * n / (ms_p * 1e-3), "unit": "images/s", "launch_ms": ms_p},
         "clocks": sampler.summary(),
     }
 
-    # ---- e2e: host (pinned) uploads through the public API, result read back to the host
-    if rank == 0 or dist_on:
-        n_e = min(n, args.e2e_batch)
-        host = torch.empty((n_e, H, W, C), dtype=torch.uint8).pin_memory()
-        host.copy_(batch[:n_e])
-        res_host = torch.empty((n_e, 784), dtype=torch.float32).pin_memory()
-        dev_stage = torch.empty((n_e, H, W, C), dtype=torch.uint8, device=device)
-        o8 = out_u8[:n_e]
-        of = out_f32[:n_e]
+    # ---- e2e: pinned host uploads through the public API (chunked H2D overlapped with the kernels),
+    #      all three results read back to the host
+    n_e = min(n, args.e2e_batch)
+    host = torch.empty((n_e, H, W, C), dtype=torch.uint8).pin_memory()
+    host.copy_(batch[:n_e])
+    res_host = [torch.empty(o[:n_e].shape, dtype=o.dtype).pin_memory() for o in outs]
+    outs_e = tuple(o[:n_e] for o in outs)
 
-        def e2e_zero_copy():
-            ctx.resize_gray_norm(host, out_u8=o8, out_f32=of)       # kernel gathers taps over PCIe
-            res_host.copy_(of, non_blocking=True)
+    def e2e_step():
+        r = ctx.preprocess_uploads(host, channel_order="BGR", out=outs_e)
+        for hbuf, dbuf in zip(res_host, r):
+            hbuf.copy_(dbuf, non_blocking=True)
 
-        def e2e_staged():
-            dev_stage.copy_(host, non_blocking=True)                # full H2D copy, then the kernel
-            ctx.resize_gray_norm(dev_stage, out_u8=o8, out_f32=of)
-            res_host.copy_(of, non_blocking=True)
+    ks = max(3, min(args.steps, 10))
+    ms_e = max_over_ranks(torch, time_steps(torch, e2e_step, ks, 3, dist_on), dist_on, device)
+    torch.cuda.synchronize()
+    assert all(torch.equal(hb, db.cpu()) for hb, db in zip(res_host, outs_e))
 
-        ks = max(3, min(args.steps, 10))
-        ms_z = max_over_ranks(torch, time_steps(torch, e2e_zero_copy, ks, 3, dist_on), dist_on, device)
-        ms_s = max_over_ranks(torch, time_steps(torch, e2e_staged, ks, 3, dist_on), dist_on, device)
-        torch.cuda.synchronize()
-        assert torch.equal(res_host, of.cpu())
-        v_z = world * n_e * ks / (ms_z * 1e-3)
-        v_s = world * n_e * ks / (ms_s * 1e-3)
-        best_zero = v_z >= v_s
-        line["e2e"] = {
-            "value": max(v_z, v_s), "unit": "images/s",
-            "h2d_bytes_per_step": int(n_e * 28 * 28 * 16 * 3) if best_zero else int(n_e * H * W * C),
-            "d2h_bytes_per_step": int(n_e * 784 * 4),
-            "mode": "zero-copy tap gather from pinned host memory" if best_zero else "staged full H2D copy",
-            "zero_copy_images_s": v_z, "staged_copy_images_s": v_s, "pictures_per_step": n_e,
-            "note": "h2d bytes for zero-copy = taps read (compulsory bytes; PCIe moves whole sectors)",
-        }
-        del host, dev_stage
+    # train-side chain alone, zero copy: the kernel bulk-copies only the source rows it needs over PCIe
+    def e2e_train_only():
+        ctx.resize_gray_norm(host, out_u8=outs_e[0], out_f32=outs_e[1])
+        res_host[1].copy_(outs_e[1], non_blocking=True)
 
-    # ---- predict-side chain: the streaming kernel (reads every byte of every upload)
-    pred_out = None
-
-    def pstep():
-        nonlocal pred_out
-        pred_out = ctx.predict_chain(batch, channel_order="BGR")
-
-    ksp = max(3, min(args.steps, 10))
-    msp = time_steps(torch, pstep, ksp, 3, dist_on)
-    msp_max = max_over_ranks(torch, msp, dist_on, device)
-    ach_p = ALG_BYTES_PREDICT_CHAIN * n / (msp / ksp * 1e-3) / 1e9
-    line["predict_chain"] = {
-        "value": world * n * ksp / (msp_max * 1e-3), "unit": "images/s", "ms_per_step": msp_max / ksp,
-        "roofline": {"bound": "hbm", "achieved": ach_p, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": ach_p / peaks["hbm_gbs"], "traffic": traffic.get("predict_chain_kernel"),
-                     "kernel": "predict_chain_kernel<3>", "algorithmic_bytes_per_picture": ALG_BYTES_PREDICT_CHAIN},
+    ms_z = max_over_ranks(torch, time_steps(torch, e2e_train_only, ks, 3, dist_on), dist_on, device)
+    line["e2e"] = {
+        "value": world * n_e * ks / (ms_e * 1e-3), "unit": "images/s", "h2d_bytes_per_step": int(n_e * H * W * C),
+        "d2h_bytes_per_step": int(n_e * (784 + 3136 + 3136)), "pictures_per_step": n_e,
+        "mode": "pinned host batch -> 256-picture chunks, H2D on a copy stream overlapped with both kernels -> D2H of all outputs",
     }
+    line["train_side_chain"]["e2e"] = {
+        "value": world * n_e * ks / (ms_z * 1e-3), "unit": "images/s", "h2d_bytes_per_step": int(n_e * 112 * W * C),
+        "d2h_bytes_per_step": int(n_e * 3136), "mode": "zero copy: cp.async.bulk of the 112 needed rows straight from pinned host memory"}
+    del host
 
     # ---- CNN train / predict sub-benchmarks (filled in when the net library is present)
     line.update(run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on))
@@ -416,12 +419,12 @@ def run_ours(args, rank, local_rank, world):
     # ---- CPU baseline on this box's host cores (rank 0, N == 1 only), bounded sample
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        v, done, dt = cpu_train_chain_throughput(args.cpu_seconds, threads)
+        v, done, dt = cpu_baseline_throughput(args.cpu_seconds, threads)
         line["cpu_baseline"] = {
             "value": v, "unit": "images/s", "cores": threads, "kind": "port",
-            "sample": "128 distinct 1024x768x3 pictures cycled for %.1f s (%d pictures); the reference's own cv2 "
-                      "calls (resize INTER_CUBIC, BGR2GRAY, *1/255; preprocess.py:29,40) in memory, IPP off, "
-                      "one picture per thread" % (dt, done)}
+            "sample": "16 distinct 1024x768x3 pictures per worker cycled for %.1f s (%d pictures); the reference's own cv2 / "
+                      "Pillow calls for both chains (preprocess.py:29,40; construct_inference.py:312-330) in memory, IPP off, "
+                      "one worker process per core" % (dt, done)}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist_on:
@@ -437,7 +440,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=4096, help="uploads per GPU (C2: 4096)")
     ap.add_argument("--e2e-batch", type=int, default=1024, help="uploads per e2e step (host pinned)")
-    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--math", type=int, default=0, help="CNN math: 0 fp32 SIMT, 1 TF32 tcgen05")
     args = ap.parse_args()

@@ -78,7 +78,7 @@ class Context:
         return out_u8, out_f32
 
     # ---------------------------------------------------------------- predict-side chain (P5)
-    def predict_chain(self, src, channel_order="RGB", compat=False, want_small20=False):
+    def predict_chain(self, src, channel_order="RGB", compat=False, want_small20=False, out=None, status=None):
         """src: uint8 CUDA tensor [N,H,W,3] or [N,H,W] ('L').  Returns (f32[N,784], status[N] int32
         (1 where the reference raises IndexError; only meaningful with compat), small20 | None).
         Stands in for construct_inference.py:312-330."""
@@ -88,8 +88,10 @@ class Context:
             src = src.unsqueeze(-1)
         n, h, w, c = src.shape
         stride = src.stride(0) if n > 1 else h * w * c
-        out = torch.empty((n, 784), dtype=torch.float32, device=self.tdev)
-        status = torch.zeros((n,), dtype=torch.int32, device=self.tdev)
+        if out is None:
+            out = torch.empty((n, 784), dtype=torch.float32, device=self.tdev)
+        if status is None:
+            status = torch.zeros((n,), dtype=torch.int32, device=self.tdev)
         small = torch.empty((n, 20, 20), dtype=torch.uint8, device=self.tdev) if want_small20 else None
         order = {"RGB": 0, "BGR": 1}[channel_order]
         rc = _lib.lib().nc_pp_predict_chain(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, stride, order,
@@ -98,6 +100,51 @@ class Context:
                                             C.c_void_p(status.data_ptr()), self._stream())
         _lib.check(self.handle, rc)
         return out, status, small
+
+    # ---------------------------------------------------------------- both chains over one batch
+    def preprocess_uploads(self, src, channel_order="BGR", chunk=256, out=None):
+        """The whole preprocess half for a batch of decoded uploads [N,H,W,3] uint8: the train-side
+        chain (P2-P4) and the predict-side chain (P5).  Returns device tensors
+        (u8[N,28,28], f32_train[N,784], f32_predict[N,784]).
+
+        src on the GPU: two launches.  src in (pinned) host memory: the batch is streamed through two
+        device staging buffers of `chunk` pictures -- H2D copies on a side stream overlap the kernels of
+        the previous chunk, so the end-to-end rate is the PCIe rate."""
+        if src.dtype != torch.uint8 or src.dim() != 4:
+            raise ValueError("src must be uint8 [N,H,W,C]")
+        n, h, w, c = src.shape
+        if out is None:
+            out = (torch.empty((n, 28, 28), dtype=torch.uint8, device=self.tdev),
+                   torch.empty((n, 784), dtype=torch.float32, device=self.tdev),
+                   torch.empty((n, 784), dtype=torch.float32, device=self.tdev))
+        u8, f32, pred = out
+        if src.is_cuda:
+            self.resize_gray_norm(src, out_u8=u8, out_f32=f32)
+            self.predict_chain(src, channel_order=channel_order, out=pred)
+            return out
+        key = (chunk, h, w, c)
+        st = getattr(self, "_stage", None)
+        if st is None or st["key"] != key:
+            st = {"key": key, "buf": [torch.empty((chunk, h, w, c), dtype=torch.uint8, device=self.tdev) for _ in range(2)],
+                  "ready": [torch.cuda.Event() for _ in range(2)], "free": [torch.cuda.Event() for _ in range(2)],
+                  "copy": torch.cuda.Stream(device=self.tdev)}
+            self._stage = st
+        main = torch.cuda.current_stream(self.tdev)
+        for e in st["free"]:
+            e.record(main)
+        for i, lo in enumerate(range(0, n, chunk)):
+            hi = min(n, lo + chunk)
+            b = i & 1
+            st["copy"].wait_event(st["free"][b])
+            with torch.cuda.stream(st["copy"]):
+                st["buf"][b][:hi - lo].copy_(src[lo:hi], non_blocking=True)
+                st["ready"][b].record(st["copy"])
+            main.wait_event(st["ready"][b])
+            d = st["buf"][b][:hi - lo]
+            self.resize_gray_norm(d, out_u8=u8[lo:hi], out_f32=f32[lo:hi])
+            self.predict_chain(d, channel_order=channel_order, out=pred[lo:hi])
+            st["free"][b].record(main)
+        return out
 
     # ---------------------------------------------------------------- the 14 ops (P6-P19)
     def op(self, op_id, imgs, v1=None, v2=None, draws=None, out=None):

@@ -20,7 +20,7 @@ timeout 600 python bench.py --steps 3 --warmup 3 --batch 1024 --e2e-batch 64 --n
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
     python bench.py --steps 3 --warmup 3 --batch 1024 --e2e-batch 64 --no-cpu-baseline > gpurun_out/${tag}_ncu_list.log 2>&1
 if [ -n "$kre" ]; then
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$kre -s 4 -c 2 -f -o gpurun_out/${tag}_prof \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$kre -s 6 -c 4 -f -o gpurun_out/${tag}_prof \
     python bench.py --steps 3 --warmup 3 --batch 1024 --e2e-batch 64 --no-cpu-baseline > gpurun_out/${tag}_ncu_full.log 2>&1
 fi
 echo done
