@@ -24,6 +24,7 @@ _SIGS = {
     "nc_launch_count": (C.c_int64, [C.c_void_p]),
     "nc_pp_resize_gray_norm": (C.c_int, [C.c_void_p, c_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int,
                                          c_u8p, c_f32p, C.c_void_p]),
+    "nc_pp_resize_cubic": (C.c_int, [C.c_void_p, c_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, c_u8p, C.c_void_p]),
     "nc_pp_resize_gray_norm_host": (C.c_int, [C.c_void_p, c_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int,
                                               c_u8p, c_f32p, C.POINTER(C.c_int), C.c_void_p]),
     "nc_pp_predict_chain": (C.c_int, [C.c_void_p, c_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int,

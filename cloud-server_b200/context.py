@@ -77,6 +77,19 @@ class Context:
         _lib.check(self.handle, rc)
         return out_u8, out_f32
 
+    def resize_cubic(self, src):
+        """uint8 CUDA [N,H,W,C] -> uint8 [N,28,28,C]: cv2.resize(.., (28,28), INTER_CUBIC) alone
+        (what preprocess.resize writes back, apps/preprocess/preprocess.py:29-30)."""
+        if src.dtype != torch.uint8 or not src.is_cuda or src.dim() != 4:
+            raise ValueError("src must be a uint8 CUDA tensor [N,H,W,C]")
+        n, h, w, c = src.shape
+        src = src.contiguous()
+        out = torch.empty((n, 28, 28, c), dtype=torch.uint8, device=self.tdev)
+        rc = _lib.lib().nc_pp_resize_cubic(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, h * w * c, 0,
+                                           C.c_void_p(out.data_ptr()), self._stream())
+        _lib.check(self.handle, rc)
+        return out
+
     # ---------------------------------------------------------------- predict-side chain (P5)
     def predict_chain(self, src, channel_order="RGB", compat=False, want_small20=False, out=None, status=None):
         """src: uint8 CUDA tensor [N,H,W,3] or [N,H,W] ('L').  Returns (f32[N,784], status[N] int32

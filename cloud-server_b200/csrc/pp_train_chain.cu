@@ -27,7 +27,7 @@ template <int C>
 __global__ void __launch_bounds__(kThreads)
 train_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h, int w,
                    const __grid_constant__ TrainTabs tabs, uint8_t* __restrict__ out_u8,
-                   float* __restrict__ out_f32, int identity) {
+                   float* __restrict__ out_f32, int identity, uint8_t* __restrict__ out_color) {
     constexpr int E = 28 * C;               // interleaved elements per output row
     constexpr int NSIMD = (E / 8) * 8;      // OpenCV v_int16x8 body
     __shared__ int hp[112][E];
@@ -103,6 +103,11 @@ train_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h,
         __syncthreads();
     }
 
+    if (out_color) {   // the resized picture itself (what preprocess.resize writes back, preprocess.py:29-30)
+        for (int idx = tid; idx < 28 * E; idx += kThreads)
+            out_color[(long long)blockIdx.x * 28 * E + idx] = identity ? __ldg(base + idx) : (&col[0][0])[idx];
+        if (!out_u8 && !out_f32) return;
+    }
     // ---- stage 3: BGR2GRAY (cv2 4.13: 15-bit coefficients) and float32 normalise
     const float inv255 = (float)(1.0 / 255.0);
     for (int idx = tid; idx < 784; idx += kThreads) {
@@ -238,7 +243,8 @@ train_chain_rows_kernel(const uint8_t* __restrict__ src, long long img_stride, i
 }  // namespace
 
 static int launch_train_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
-                              int64_t img_stride, uint8_t* out_u8, float* out_f32, cudaStream_t st) {
+                              int64_t img_stride, uint8_t* out_u8, float* out_f32, cudaStream_t st,
+                              uint8_t* out_color = nullptr) {
     TrainTabs tabs;
     const int identity = (h == 28 && w == 28) ? 1 : 0;
     if (!identity) {
@@ -250,7 +256,7 @@ static int launch_train_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int
     // row-streaming kernel: 3 channels, 16-byte aligned rows, source rows close enough together that
     // DRAM would fetch them whole anyway (tap spacing <= 192 B), and the 7 stages fit shared memory
     const long long row_bytes = (long long)w * c;
-    if (c == 3 && !identity && (row_bytes % 16) == 0 && (reinterpret_cast<uintptr_t>(src) % 16) == 0 && (img_stride % 16) == 0 &&
+    if (c == 3 && !identity && !out_color && (row_bytes % 16) == 0 && (reinterpret_cast<uintptr_t>(src) % 16) == 0 && (img_stride % 16) == 0 &&
         h >= 4 && row_bytes * 4 * kRowWarps <= 200 * 1024 && row_bytes <= 28 * 192 && !getenv("NC_TRAIN_NO_ROWS")) {
         const unsigned stage_bytes = (unsigned)(row_bytes * 4);
         const size_t smem = (size_t)stage_bytes * kRowWarps;
@@ -260,9 +266,9 @@ static int launch_train_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int
         return NC_OK;
     }
     if (c == 3)
-        train_chain_kernel<3><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity);
+        train_chain_kernel<3><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity, out_color);
     else
-        train_chain_kernel<1><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity);
+        train_chain_kernel<1><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity, out_color);
     NC_LAUNCH_CHECK(ctx);
     return NC_OK;
 }
@@ -312,4 +318,13 @@ extern "C" int nc_pp_resize_gray_norm_host(nc_ctx* ctx, const uint8_t* host_src,
     NC_CUDA(ctx, cudaMemcpyAsync(ctx->ws, host_src, bytes, cudaMemcpyHostToDevice, st));
     if (staged) *staged = 1;
     return launch_train_chain(ctx, (const uint8_t*)ctx->ws, n, h, w, c, img_stride, out_u8, out_f32, st);
+}
+
+extern "C" int nc_pp_resize_cubic(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c, int64_t img_stride,
+                                  int mode, uint8_t* out, void* stream) {
+    int rc = check_train_args(ctx, src, n, h, w, c, img_stride, mode, out, out);
+    if (rc != NC_OK) return rc;
+    if (n == 0) return NC_OK;
+    NC_CUDA(ctx, cudaSetDevice(ctx->device));
+    return launch_train_chain(ctx, src, n, h, w, c, img_stride, nullptr, nullptr, (cudaStream_t)stream, out);
 }

@@ -64,6 +64,11 @@ int nc_pp_resize_gray_norm(nc_ctx* ctx, const uint8_t* src, int n, int h, int w,
                            int64_t img_stride, int mode, uint8_t* out_u8, float* out_f32,
                            void* stream);
 
+/* The resize alone: out[n][28][28][c] = cv2.resize(src[i], (28,28), interpolation=cv2.INTER_CUBIC)
+ * (apps/preprocess/preprocess.py:29), the picture preprocess.resize writes back to disk (:30). */
+int nc_pp_resize_cubic(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c, int64_t img_stride,
+                       int mode, uint8_t* out, void* stream);
+
 /* Same chain with the source in HOST memory (what the REST view has after decoding).  If
  * host_src is pinned (cudaHostAlloc / cudaHostRegister) the kernel gathers the 4x4 taps it
  * needs straight over PCIe; pageable memory is staged through the ctx workspace.  Outputs are

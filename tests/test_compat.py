@@ -1,0 +1,167 @@
+"""Drop-in surface of the reference: names, signatures, flags, file formats.  CPU part:
+host logic only.  GPU part (marked): the shims run end to end on temp copies of bundled pictures."""
+import inspect
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import golden
+from oracle import tfref
+
+REF_NAMES = ["copied_name", "resize", "flip_up_down", "flip_left_right", "transpose_image", "adjust_brightness_contrast",
+             "random_brightness_contrast", "mean_filter", "gaussian_blur", "median_filter", "nl_denoise_gray",
+             "add_salt_pepper_noise", "equalize_hist", "clahe", "erode", "dilate"]
+
+
+def test_preprocess_module_surface():
+    from cloud_server_b200.compat.apps.preprocess import preprocess as pp
+    for n in REF_NAMES:
+        assert hasattr(pp, n), n
+    assert list(inspect.signature(pp.resize).parameters) == ["dir"]
+    for n in REF_NAMES[2:]:
+        assert len(inspect.signature(getattr(pp, n)).parameters) == 4, n
+    assert pp.copied_name("/a/b/test1.jpg") == "/a/b/test1_copy.jpg"
+
+
+def test_train_script_flags_match_reference_command_line():
+    from cloud_server_b200.compat import construct_distribute as cd
+    # the exact string cmd.py:63-69 builds
+    cfg = '{"iter":"1000","learning_rate":"0.01","loss_name":"entropy","optimizer_name":"GradientDescentOptimizer",' \
+          '"net_type":"CNN","net_config":{"middle_layer":[{"layer":"conv","filter":[2,2,10]}],"output_layer":{}}}'
+    argv = ["--mode=train", "--ps_hosts=127.0.0.1:2222", "--worker_hosts=127.0.0.1:2223", "--job_name=ps", "--task_index=0",
+            "--config=" + cfg, "--ratio=0.800000"]
+    f = cd.build_flags(argv)
+    assert f.job_name == "ps" and f.ratio == "0.800000" and json.loads(f.config)["iter"] == "1000"
+    assert cd.main(argv) == 0                      # the ps job is a no-op that returns
+    f2 = cd.build_flags([])
+    assert (f2.model_name, f2.save_path, f2.result, f2.iter) == ("model", "./train_model/", "./result.txt", 2000)
+    from cloud_server_b200.compat import construct_inference as ci
+    g = ci.build_flags(["--config=" + cfg, "--filename=infer/x.jpg"])
+    assert (g.model_name, g.save_path, g.result) == ("model", "./train_model/", "result.json")
+
+
+def test_dataset_matches_oracle_dataset():
+    from cloud_server_b200.compat.construct_distribute import DataSet
+    imgs = (np.arange(23 * 784).reshape(23, 28, 28, 1) % 251).astype(np.uint8)
+    labs = np.eye(10)[np.arange(23) % 10]
+    np.random.seed(5)
+    a = DataSet(imgs, labs)
+    b = tfref.DataSet(imgs, labs, rs=np.random.RandomState(5))
+    for _ in range(9):
+        xa, ya = a.next_batch(5)
+        xb, yb = b.next_batch(5)
+        assert np.array_equal(xa, xb) and np.array_equal(ya, yb)
+    assert a.epochs_completed == 1 and a.num_examples == 23
+
+
+def test_graph_builder_equals_json_interpreter():
+    from cloud_server_b200.compat import graph as G
+    x = G.placeholder()
+    h = G.conv2d(x, [5, 5, 32], isBias=True)
+    h = G.active(h, "relu")
+    h = G.max_pool(h)
+    h = G.connect_layer(h, 64)
+    cfg = G.net_config_of(h)
+    layers, params = tfref.parse_layers(cfg)
+    assert [l["kind"] for l in layers] == ["conv", "active", "pool", "connect", "connect"]
+    assert h.get_shape() == (None, 64)
+    via_json = G.cnn(tfref.API_EXAMPLE, G.placeholder())
+    l2, p2 = tfref.parse_layers(G.net_config_of(via_json))
+    l3, p3 = tfref.parse_layers(tfref.API_EXAMPLE)
+    assert [p[1] for p in p2] == [p[1] for p in p3]
+    with pytest.raises(AssertionError):
+        G.active(x, "tanh")
+    assert G.loss_function("hinge", None) is None
+    assert G.optimizer_function("GradientDescentOptimizer", "0.01") == ("sgd", 0.01)
+    assert G.optimizer_function("AdamOptimizer", 0.5)[0] == "adagrad"      # the reference's else-branch (:310-311)
+
+
+# ------------------------------------------------------------------------------------------ GPU
+@pytest.mark.gpu
+def test_preprocess_shim_files(ctx, tmp_path):
+    import cv2
+    from cloud_server_b200.compat.apps.preprocess import preprocess as pp
+    from oracle import cvref
+    pics = golden("pics.npz")
+    big = np.random.default_rng(1).integers(0, 256, (96, 128, 3), np.uint8)
+    p = str(tmp_path / "u.jpg")
+    cv2.imwrite(p, big)
+    decoded = cv2.imread(p)
+    pp.resize(p)
+    want = cv2.resize(decoded, (28, 28), interpolation=cv2.INTER_CUBIC)
+    q = str(tmp_path / "w.jpg")
+    cv2.imwrite(q, want)
+    assert np.array_equal(cv2.imread(p), cv2.imread(q))            # same pixels into the same encoder
+    for name, v1, v2 in [("flip_up_down", None, None), ("mean_filter", 3, None), ("erode", 3, None), ("equalize_hist", None, None),
+                         ("adjust_brightness_contrast", 1.5, 30), ("clahe", None, None), ("gaussian_blur", 5, None)]:
+        f = str(tmp_path / ("%s.jpg" % name))
+        cv2.imwrite(f, pics["gray_cv"][3])
+        src = cv2.imread(f, 0)
+        getattr(pp, name)(f, True, v1, v2)
+        assert os.path.exists(pp.copied_name(f))
+        ref = str(tmp_path / "ref.jpg")
+        cv2.imwrite(ref, cvref.op(name, src, v1, v2))
+        assert np.array_equal(cv2.imread(pp.copied_name(f), 0), cv2.imread(ref, 0)), name
+        assert np.array_equal(cv2.imread(f, 0), src)               # overlap=True leaves the original alone
+    with pytest.raises(OverflowError):
+        pp.adjust_brightness_contrast(f, False, 300, 0)
+
+
+@pytest.mark.gpu
+def test_train_and_inference_scripts_end_to_end(ctx, tmp_path, monkeypatch):
+    import cv2
+    from cloud_server_b200.compat import construct_distribute as cd, construct_inference as ci
+    pics = golden("pics.npz")
+    monkeypatch.chdir(tmp_path)
+    os.mkdir("data")
+    tags = {}
+    for i, (name, lab) in enumerate(zip(pics["names"], pics["labels"])):
+        cv2.imwrite(os.path.join("data", str(name)), pics["gray_cv"][i])
+        tags[str(name)] = str(int(lab))
+    json.dump(tags, open("tag.json", "w"))
+    config = {"iter": "120", "learning_rate": "0.01", "loss_name": "entropy", "optimizer_name": "GradientDescentOptimizer",
+              "net_type": "CNN", "net_config": {"middle_layer": [{"layer": "conv", "filter": [3, 3, 8], "isBias": "True"},
+                                                                 {"layer": "active", "active_func": "relu"}, {"layer": "pool"},
+                                                                 {"layer": "connect", "hidden": 64}, {"layer": "active", "active_func": "relu"}],
+                                        "output_layer": {}}}
+    argv = ["--mode=train", "--ps_hosts=a:1", "--worker_hosts=b:2", "--job_name=worker", "--task_index=0",
+            "--config=" + json.dumps(config), "--ratio=0.800000", "--data_dir=.", "--save_path=./train_model/",
+            "--honor_config", "--seed=3"]
+    assert cd.main(argv) == 0
+    # result.txt parses with the consumer's own logic (apps/runtime/views.py:55-70)
+    lines = open("result.txt").read().split("\n")
+    steps = [l for l in lines if l.startswith("step:")]
+    assert len(steps) == 2 and re.fullmatch(r"step:\d+,accuracy:\d\.\d{6},duration:\d+\.\d{6}", steps[0])
+    assert steps[0].startswith("step:0,") and steps[1].startswith("step:100,")
+    final = [l for l in lines if l.startswith("final_accuracy:")]
+    assert len(final) == 1 and 0.0 <= float(final[0].split(":")[1]) <= 1.0
+    assert cd.get_model("./train_model/", "model") == 120
+    assert os.path.exists("./train_model/model.ckpt-120.meta")
+    # SGD at 0.01 for 120 steps on 79 pictures learns something: accuracy on the train split rises
+    acc0 = float(steps[0].split(",")[1].split(":")[1])
+    acc1 = float(steps[1].split(",")[1].split(":")[1])
+    assert acc1 >= acc0
+    # inference script: compat mode raises where the reference raises, --intended predicts a digit
+    name = str(pics["names"][0])
+    iargv = ["--config=" + json.dumps(config), "--filename=" + os.path.join("data", name)]
+    from PIL import Image
+    from oracle import pp_restate as R
+    try:
+        R.predict_chain(np.asarray(Image.open(os.path.join("data", name))), compat=True)
+        ref_raises = False
+    except IndexError:
+        ref_raises = True
+    if ref_raises:
+        with pytest.raises(IndexError):
+            ci.main(iargv)
+    else:
+        assert ci.main(iargv) == 0
+    assert ci.main(iargv + ["--intended"]) == 0
+    out = json.load(open("result.json"))
+    assert out["result"] == "success" and out["message"] in list("0123456789")
+    with pytest.raises(ValueError):
+        ci.main(["--config=" + json.dumps(config), "--filename=x.jpg", "--save_path=./nowhere/"] if os.path.isdir("./nowhere/") else
+                ["--config=" + json.dumps(config), "--filename=x.jpg", "--model_name=absent"])
