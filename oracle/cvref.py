@@ -14,6 +14,11 @@ try:  # the GPU box has the same image; gate anyway
     import cv2
 
     cv2.ipp.setUseIPP(False)
+    # OpenCV's useIPP flag is thread-local and its row-stripe parallel_for_ is not bit-reproducible
+    # across thread counts (observed: GaussianBlur k=5 on a 28x28 picture differs in 13 pixels with a
+    # 24-thread pool, never with 1 thread).  The reference ran on a 1-vCPU node (API.md:428-431), so
+    # the canonical, deterministic target is single-threaded OpenCV.
+    cv2.setNumThreads(1)
 except Exception:  # pragma: no cover
     cv2 = None
 try:

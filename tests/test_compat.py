@@ -103,8 +103,13 @@ def test_preprocess_shim_files(ctx, tmp_path):
         getattr(pp, name)(f, True, v1, v2)
         assert os.path.exists(pp.copied_name(f))
         ref = str(tmp_path / "ref.jpg")
-        cv2.imwrite(ref, cvref.op(name, src, v1, v2))
-        assert np.array_equal(cv2.imread(pp.copied_name(f), 0), cv2.imread(ref, 0)), name
+        want_arr = cvref.op(name, src, v1, v2)
+        cv2.imwrite(ref, want_arr)
+        from oracle import pp_restate as R
+        ora = getattr(R, name)(src) if v1 is None else (getattr(R, name)(src, v1) if v2 is None else getattr(R, name)(src, v1, v2))
+        got, want = cv2.imread(pp.copied_name(f), 0), cv2.imread(ref, 0)
+        assert np.array_equal(got, want), (name, "file diff", int((got != want).sum()), "cv2 vs oracle", int((want_arr != ora).sum()),
+                                           "threads", cv2.getNumThreads())
         assert np.array_equal(cv2.imread(f, 0), src)               # overlap=True leaves the original alone
     with pytest.raises(OverflowError):
         pp.adjust_brightness_contrast(f, False, 300, 0)
