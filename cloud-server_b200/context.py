@@ -181,6 +181,19 @@ class Context:
         _lib.check(self.handle, rc)
         return out
 
+    def matmul(self, a, b, bias=None, trans_a=False, trans_b=False, precision=0):
+        """tf.matmul(a, b) + bias on the TF32 tcgen05 path (construct_distribute.py:182, :264)."""
+        a, b = a.contiguous(), b.contiguous()
+        m, k = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
+        n = b.shape[0] if trans_b else b.shape[1]
+        out = torch.empty((m, n), dtype=torch.float32, device=self.tdev)
+        rc = _lib.lib().nc_matmul(self.handle, C.c_void_p(a.data_ptr()), C.c_void_p(b.data_ptr()),
+                                  C.c_void_p(bias.data_ptr()) if bias is not None else None, m, k, n,
+                                  1 if trans_a else 0, 1 if trans_b else 0, int(precision), C.c_void_p(out.data_ptr()),
+                                  self._stream())
+        _lib.check(self.handle, rc)
+        return out
+
     def normalise(self, imgs_u8):
         imgs_u8 = imgs_u8.contiguous()
         n = imgs_u8.shape[0]

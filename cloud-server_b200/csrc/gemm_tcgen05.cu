@@ -1,0 +1,397 @@
+// TF32 tensor-core GEMM for sm_100a: tcgen05.mma with the accumulator in TMEM, operands staged in
+// shared memory by TMA (cp.async.bulk.tensor, 128-byte swizzle), mbarrier producer/consumer pipeline.
+//
+//   C[M][N] = opA(A) . opB(B) (+ bias[N]) (+ activation)           fp32 in, TF32 multiply, fp32 accumulate
+//
+// It carries the dense contractions of the CNN path -- tf.matmul(x, w) + b of connect_layer() and the
+// output layer (apps/construction/util/construct_distribute.py:182, :264) and their two gradients --
+// straight from the natural row-major buffers: both operands may be "K-major" (reduction dimension
+// contiguous) or "MN-major" (the other dimension contiguous), selected in the UMMA instruction
+// descriptor, so no transposed copies of weights or activations are ever made:
+//   forward   Y[n][out]  = X[n][in] . W[in][out]          A K-major, B MN-major
+//   dgrad     dX[n][in]  = dY[n][out] . W[in][out]^T      A K-major, B K-major
+//   wgrad     dW[in][out] = X[n][in]^T . dY[n][out]       A MN-major, B MN-major (reduction over the batch)
+//
+// Tile: 128 x BN x 32 (BN = 64 or 128), 4 stages, one CTA per output tile and K slice (deterministic
+// split-K through a workspace, summed in slice order).  Warp roles: warp 0 = TMA producer (one
+// elected lane), warp 1 = MMA issuer (one lane) and TMEM allocator, warps 2-5 = epilogue
+// (tcgen05.ld 32 lanes x 32 columns per warp -> bias / activation -> global).
+#include "nc_internal.h"
+#include "tc_gemm.h"
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+namespace {
+
+constexpr int BM = 128, BK = 32;          // BK * 4 B = 128 B = one swizzle-128B row
+constexpr int STAGES = 3;
+constexpr int kThreads = 192;             // 6 warps
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+
+// shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start>>4 [0,14), LBO>>4 [16,30),
+// SBO>>4 [32,46), version=1 [46,48), layout SWIZZLE_128B = 2 [61,64)
+__device__ __forceinline__ unsigned long long umma_desc(unsigned saddr, unsigned lbo_bytes, unsigned sbo_bytes,
+                                                        unsigned long long layout_type = 2) {
+    unsigned long long d = 0;
+    d |= (unsigned long long)((saddr >> 4) & 0x3FFF);
+    d |= (unsigned long long)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (unsigned long long)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= 1ull << 46;
+    d |= layout_type << 61;
+    return d;
+}
+
+// X3 = true: "3xTF32" -- every fp32 operand is split into hi = rna_tf32(x) and lo = rna_tf32(x - hi) and
+// the product is accumulated as hi.hi + lo.hi + hi.lo (three MMAs per k step), which restores fp32-class
+// accuracy (error ~2^-21 per product) on the TF32 tensor pipe.  X3 = false: one rounded TF32 product.
+__device__ __forceinline__ void umma_tf32(unsigned tmem, unsigned long long da, unsigned long long db, unsigned idesc,
+                                          unsigned accum) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
+        ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(accum) : "memory");
+}
+
+template <int BN, bool A_MN, bool B_MN, bool X3>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ C,
+                 const float* __restrict__ bias, int M, int N, int K, int kb_per_slice, int act, float slope,
+                 float* __restrict__ partial) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    constexpr unsigned A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
+    constexpr unsigned HI_BYTES = A_BYTES + B_BYTES;                 // TMA destination (hi parts after conversion)
+    constexpr unsigned STAGE_BYTES = X3 ? 2 * HI_BYTES : HI_BYTES;   // [A_hi | B_hi | A_lo | B_lo]
+    // 1024-byte aligned stage buffers (swizzle atoms are 8 rows x 128 B)
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[STAGES], s_tmem_full;
+    __shared__ unsigned s_tmem_base;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int nkb_total = (K + BK - 1) / BK;
+    const int kb0 = blockIdx.z * kb_per_slice;
+    const int nkb = min(kb_per_slice, nkb_total - kb0);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(smem_u32(&s_full[s]), 1);
+            mbar_init(smem_u32(&s_empty[s]), 1);
+            mbar_init(smem_u32(&s_ready[s]), 4);       // one arrive per converter warp
+        }
+        mbar_init(smem_u32(&s_tmem_full), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {   // TMEM: BN fp32 accumulator columns (power of two >= 32)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem_base)), "r"((unsigned)BN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = s_tmem_base;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % STAGES;
+                const unsigned ph = (unsigned)(i / STAGES) & 1u;
+                mbar_wait(smem_u32(&s_empty[s]), ph ^ 1u);
+                const unsigned full = smem_u32(&s_full[s]);
+                mbar_expect_tx(full, A_BYTES + B_BYTES);
+                const unsigned sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                const unsigned sb = sa + A_BYTES;
+                const int k0 = (kb0 + i) * BK;
+                if (!A_MN) {
+                    tma_load_2d(sa, &tmA, k0, m0, full);                       // [M][K]: box 32 k x 128 rows
+                } else {
+#pragma unroll
+                    for (int c = 0; c < BM / 32; ++c) tma_load_2d(sa + c * 4096, &tmA, m0 + c * 32, k0, full);   // [K][M]: box 32 m x 32 k-rows
+                }
+                if (!B_MN) {
+                    tma_load_2d(sb, &tmB, k0, n0, full);                       // [N][K]: box 32 k x BN rows
+                } else {
+#pragma unroll
+                    for (int c = 0; c < BN / 32; ++c) tma_load_2d(sb + c * 4096, &tmB, n0 + c * 32, k0, full);   // [K][N]
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32, A = B = TF32, majors, N >> 3, M >> 4
+            const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                                   ((unsigned)(BN >> 3) << 17) | ((unsigned)(BM >> 4) << 24);
+            for (int i = 0; i < nkb; ++i) {
+                const int s = i % STAGES;
+                const unsigned ph = (unsigned)(i / STAGES) & 1u;
+                mbar_wait(smem_u32(&s_ready[s]), ph);      // operands landed AND rounded to TF32
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const unsigned sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                const unsigned sb = sa + A_BYTES;
+#pragma unroll
+                for (int kk = 0; kk < BK / 8; ++kk) {       // UMMA_K = 8 for tf32 (32 bytes)
+                    // K-major (SWIZZLE_128B): rows of 128 B, 8-row atoms 1024 B apart (SBO); advance 32 B inside the atom.
+                    // MN-major 32-bit operands need the 32-byte-granular swizzle (SWIZZLE_128B_BASE32B, type 1;
+                    // TMA: SWIZZLE_128B_ATOM_32B): each k is a 128 B row of 32 mn, 4 k-rows = one 512 B atom (SBO),
+                    // 32-mn chunks 4096 B apart (LBO); one MMA (K = 8) covers two atoms = 1024 B.
+                    const unsigned long long da = A_MN ? umma_desc(sa + kk * 1024, 4096, 512, 1) : umma_desc(sa + kk * 32, 16, 1024);
+                    const unsigned long long db = B_MN ? umma_desc(sb + kk * 1024, 4096, 512, 1) : umma_desc(sb + kk * 32, 16, 1024);
+                    const unsigned accum = (i > 0 || kk > 0) ? 1u : 0u;
+                    if (X3) {
+                        // lo parts live HI_BYTES further on in the stage: same layout, same descriptors + offset
+                        const unsigned long long off = (unsigned long long)(HI_BYTES >> 4);
+                        umma_tf32(tmem, da + off, db, idesc, accum);         // lo(A) . hi(B)
+                        umma_tf32(tmem, da, db + off, idesc, 1u);            // hi(A) . lo(B)
+                        umma_tf32(tmem, da, db, idesc, 1u);                  // hi(A) . hi(B)
+                    } else {
+                        umma_tf32(tmem, da, db, idesc, accum);
+                    }
+                }
+                // frees the smem stage once these MMAs have read it
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_empty[s])) : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_tmem_full)) : "memory");
+        }
+    } else {
+        // ===================== epilogue: warps 2..5 own TMEM lanes 32*(warp%4) .. +32 =====================
+        const int q = warp & 3;
+        const int row = m0 + q * 32 + lane;
+        // During the main loop these four warps round the staged fp32 operands to TF32 (round to nearest,
+        // ties away: cvt.rna) in place.  kind::tf32 otherwise TRUNCATES the 13 low mantissa bits, a
+        // one-sided error of ~1e-3 per product that does not average out over the dot product.
+        for (int i = 0; i < nkb; ++i) {
+            const int s = i % STAGES;
+            const unsigned ph = (unsigned)(i / STAGES) & 1u;
+            mbar_wait(smem_u32(&s_full[s]), ph);
+            uint4* p = reinterpret_cast<uint4*>(smem + (size_t)s * STAGE_BYTES);
+#pragma unroll 4
+            for (int j = (warp - 2) * 32 + lane; j < (int)(HI_BYTES / 16); j += 128) {
+                const uint4 v = p[j];
+                uint4 hi;
+                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi.x) : "f"(__uint_as_float(v.x)));
+                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi.y) : "f"(__uint_as_float(v.y)));
+                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi.z) : "f"(__uint_as_float(v.z)));
+                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi.w) : "f"(__uint_as_float(v.w)));
+                p[j] = hi;
+                if (X3) {
+                    uint4 lo;
+                    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo.x) : "f"(__uint_as_float(v.x) - __uint_as_float(hi.x)));
+                    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo.y) : "f"(__uint_as_float(v.y) - __uint_as_float(hi.y)));
+                    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo.z) : "f"(__uint_as_float(v.z) - __uint_as_float(hi.z)));
+                    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo.w) : "f"(__uint_as_float(v.w) - __uint_as_float(hi.w)));
+                    p[j + HI_BYTES / 16] = lo;
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core (async proxy) reads
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[s])) : "memory");
+        }
+        if (nkb > 0) {
+            mbar_wait(smem_u32(&s_tmem_full), 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+        float* out = partial ? partial + (size_t)blockIdx.z * M * N : C;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            unsigned r[32];
+            if (nkb > 0) {
+                const unsigned taddr = tmem + ((unsigned)(q * 32) << 16) + (unsigned)c0;
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                      "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                      "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                      "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                    : "r"(taddr));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) r[j] = 0u;
+            }
+            if (row < M) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int col = n0 + c0 + j;
+                    if (col < N) {
+                        float v = __uint_as_float(r[j]);
+                        if (!partial) {
+                            if (bias) v += __ldg(bias + col);
+                            if (act == 1) v = fmaxf(v, 0.0f);
+                            else if (act == 2) v = 1.0f / (1.0f + expf(-v));
+                            else if (act == 3) v = fmaxf(v, slope * v);
+                        }
+                        out[(size_t)row * N + col] = v;
+                    }
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((unsigned)BN));
+    }
+}
+
+__global__ void tc_reduce_kernel(float* __restrict__ dst, const float* __restrict__ ws, int splits, long long count,
+                                 const float* __restrict__ bias, int ncols, int act, float slope) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        float s = 0.0f;
+        for (int k = 0; k < splits; ++k) s += ws[(long long)k * count + i];
+        if (bias) s += __ldg(bias + (int)(i % ncols));
+        if (act == 1) s = fmaxf(s, 0.0f);
+        else if (act == 2) s = 1.0f / (1.0f + expf(-s));
+        else if (act == 3) s = fmaxf(s, slope * s);
+        dst[i] = s;
+    }
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+
+int get_encode(nc_ctx* ctx) {
+    if (g_encode) return NC_OK;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+    if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
+        cudaGetLastError();
+        return nc_set_error(ctx, NC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    }
+    g_encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+    return NC_OK;
+}
+
+// row-major fp32 matrix [rows][cols] (ld = cols), box = 32 columns x box_rows rows, 128-byte swizzle, zero OOB fill
+int make_map(nc_ctx* ctx, CUtensorMap* map, const float* base, long long rows, long long cols, int box_rows,
+             bool mn_major = false) {
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)cols * sizeof(float)};
+    cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return nc_set_error(ctx, NC_ECUDA, "cuTensorMapEncodeTiled failed (%d) for %lld x %lld", (int)r, rows, cols);
+    return NC_OK;
+}
+
+template <int BN, bool A_MN, bool B_MN, bool X3>
+int launch(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, float* C, const float* bias, int M, int N, int K,
+           int kbps, int splits, int act, float slope, float* partial, cudaStream_t st) {
+    const size_t smem = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) * (X3 ? 2 : 1) + 1024;
+    auto kfn = gemm_tf32_kernel<BN, A_MN, B_MN, X3>;
+    NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);
+    kfn<<<grid, kThreads, smem, st>>>(ma, mb, C, bias, M, N, K, kbps, act, slope, partial);
+    NC_LAUNCH_CHECK(ctx);
+    return NC_OK;
+}
+
+}  // namespace
+
+bool nc_tc_gemm_supported(const float* A, const float* B, int M, int N, int K, bool a_mn, bool b_mn) {
+    // TMA needs 16-byte aligned bases and row pitches
+    const long long lda = a_mn ? M : K, ldb = b_mn ? N : K;
+    if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return false;
+    if ((lda & 3) || (ldb & 3)) return false;
+    return M >= 1 && N >= 8 && K >= 8;
+}
+
+size_t nc_tc_gemm_workspace(int sm_count, int M, int N, int K, int* splits_out, int* kbps_out) {
+    const int BN = N <= 64 ? 64 : 128;
+    const long long tiles = (long long)((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+    const int nkb = (K + BK - 1) / BK;
+    int splits = 1;
+    if (tiles < sm_count && nkb >= 8) {
+        splits = (int)((sm_count + tiles - 1) / tiles);
+        if (splits > nkb / 4) splits = nkb / 4;
+        if (splits < 1) splits = 1;
+    }
+    int kbps = (nkb + splits - 1) / splits;
+    splits = (nkb + kbps - 1) / kbps;
+    if (splits_out) *splits_out = splits;
+    if (kbps_out) *kbps_out = kbps;
+    return splits > 1 ? (size_t)splits * M * N * sizeof(float) : 0;
+}
+
+int nc_tc_gemm(nc_ctx* ctx, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
+               bool b_mn, int act, float slope, float* ws, size_t ws_bytes, cudaStream_t st, bool x3) {
+    int rc = get_encode(ctx);
+    if (rc != NC_OK) return rc;
+    if (!nc_tc_gemm_supported(A, B, M, N, K, a_mn, b_mn)) return nc_set_error(ctx, NC_EUNSUPPORTED, "tcgen05 GEMM: unaligned operands");
+    const int BN = N <= 64 ? 64 : 128;
+    int splits, kbps;
+    const size_t need = nc_tc_gemm_workspace(ctx->sm_count, M, N, K, &splits, &kbps);
+    if (need > ws_bytes) return nc_set_error(ctx, NC_EINVAL, "tcgen05 GEMM: workspace %zu < %zu", ws_bytes, need);
+    CUtensorMap ma, mb;
+    rc = a_mn ? make_map(ctx, &ma, A, K, M, 32, true) : make_map(ctx, &ma, A, M, K, BM);
+    if (rc != NC_OK) return rc;
+    rc = b_mn ? make_map(ctx, &mb, B, K, N, 32, true) : make_map(ctx, &mb, B, N, K, BN);
+    if (rc != NC_OK) return rc;
+    float* partial = splits > 1 ? ws : nullptr;
+#define NC_TC_LAUNCH(BN_, AM, BMJ)                                                                                          \
+    rc = x3 ? launch<BN_, AM, BMJ, true>(ctx, ma, mb, C, bias, M, N, K, kbps, splits, act, slope, partial, st)                \
+            : launch<BN_, AM, BMJ, false>(ctx, ma, mb, C, bias, M, N, K, kbps, splits, act, slope, partial, st)
+    if (BN == 64) {
+        if (!a_mn && !b_mn) NC_TC_LAUNCH(64, false, false);
+        else if (!a_mn && b_mn) NC_TC_LAUNCH(64, false, true);
+        else if (a_mn && !b_mn) NC_TC_LAUNCH(64, true, false);
+        else NC_TC_LAUNCH(64, true, true);
+    } else {
+        if (!a_mn && !b_mn) NC_TC_LAUNCH(128, false, false);
+        else if (!a_mn && b_mn) NC_TC_LAUNCH(128, false, true);
+        else if (a_mn && !b_mn) NC_TC_LAUNCH(128, true, false);
+        else NC_TC_LAUNCH(128, true, true);
+    }
+#undef NC_TC_LAUNCH
+    if (rc != NC_OK) return rc;
+    if (splits > 1) {
+        const long long count = (long long)M * N;
+        long long blocks = (count + 255) / 256;
+        if (blocks > (long long)ctx->sm_count * 8) blocks = (long long)ctx->sm_count * 8;
+        tc_reduce_kernel<<<(int)blocks, 256, 0, st>>>(C, ws, splits, count, bias, N, act, slope);
+        NC_LAUNCH_CHECK(ctx);
+    }
+    return NC_OK;
+}
+
+// tf.matmul(a, b) (+ bias): construct_distribute.py:182, :264
+extern "C" int nc_matmul(nc_ctx* ctx, const float* a, const float* b, const float* bias, int m, int k, int n, int trans_a,
+                         int trans_b, int precision, float* out, void* stream) {
+    if (!ctx) return nc_set_error(nullptr, NC_EINVAL, "ctx is NULL");
+    if (!a || !b || !out || m <= 0 || k <= 0 || n <= 0) return nc_set_error(ctx, NC_EINVAL, "bad arguments");
+    NC_CUDA(ctx, cudaSetDevice(ctx->device));
+    // row-major a: [m][k] (or [k][m] if trans_a), b: [k][n] (or [n][k] if trans_b)
+    const bool a_mn = trans_a != 0, b_mn = trans_b == 0;
+    size_t need = nc_tc_gemm_workspace(ctx->sm_count, m, n, k, nullptr, nullptr);
+    if (need) { int rc = nc_ws_reserve(ctx, need); if (rc != NC_OK) return rc; }
+    return nc_tc_gemm(ctx, a, b, out, bias, m, n, k, a_mn, b_mn, 0, 0.0f, (float*)ctx->ws, ctx->ws_bytes, (cudaStream_t)stream,
+                      precision != 1);
+}

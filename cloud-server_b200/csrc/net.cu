@@ -9,6 +9,7 @@
 // flat fp32 buffer, gradients and optimizer state in matching flat buffers.
 #include "nc_internal.h"
 #include "net_kernels.cuh"
+#include "tc_gemm.h"
 #include <cmath>
 #include <cstring>
 #include <cstdlib>
@@ -388,7 +389,7 @@ extern "C" int nc_net_get_params(nc_net* net, float* host_params) {
 }
 extern "C" int nc_net_set_math(nc_net* net, int math) {
     if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
-    if (math != 0 && math != 1) return net_err(net, NC_EINVAL, "math must be 0 (fp32 SIMT) or 1 (TF32 tensor cores)");
+    if (math < 0 || math > 2) return net_err(net, NC_EINVAL, "math must be 0 (fp32 SIMT), 1 (3xTF32 tensor cores) or 2 (1xTF32 tensor cores)");
     net->math = math;
     return NC_OK;
 }
@@ -472,6 +473,21 @@ static int run_colsum(nc_net* net, const float* y, int rows, int cols, float* ou
     return NC_OK;
 }
 
+// dense contraction on the tensor cores (math 1) when TMA can address the operands; else SIMT
+static int tc_try(nc_net* net, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
+                  bool b_mn, cudaStream_t st, bool* done) {
+    *done = false;
+    if (net->math == 0 || !nc_tc_gemm_supported(A, B, M, N, K, a_mn, b_mn)) return NC_OK;
+    const size_t need = nc_tc_gemm_workspace(net->ctx->sm_count, M, N, K, nullptr, nullptr);
+    int rc = reserve_ws(net, need);
+    if (rc != NC_OK) return rc;
+    const int64_t before = net->ctx->launches;
+    rc = nc_tc_gemm(net->ctx, A, B, C, bias, M, N, K, a_mn, b_mn, 0, 0.0f, net->ws, net->ws_bytes, st, net->math == 1);
+    (void)before;
+    if (rc == NC_OK) *done = true;
+    return rc;
+}
+
 static ConvGeom geom(const Layer& L) { return ConvGeom{L.ih, L.iw, L.ic, L.oh, L.ow, L.oc, L.fh, L.fw, L.sh, L.sw, L.pt, L.pl}; }
 static PoolGeom pgeom(const Layer& L) { return PoolGeom{L.ih, L.iw, L.ic, L.oh, L.ow, L.fh, L.fw, L.sh, L.sw, L.pt, L.pl}; }
 
@@ -496,7 +512,10 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st) {
         }
         case L_CONNECT: {
             const int M = n, N = L.oc, K = (int)L.in_size;
-            rc = run_gemm<true, true>(net, M, N, K, RowMajor{in, K}, RowMajor{W, N}, out, Bp, st);
+            bool done;
+            rc = tc_try(net, in, W, out, Bp, M, N, K, false, true, st, &done);       // Y = X . W[in][out] + b
+            if (rc != NC_OK) return rc;
+            if (!done) rc = run_gemm<true, true>(net, M, N, K, RowMajor{in, K}, RowMajor{W, N}, out, Bp, st);
             if (rc != NC_OK) return rc;
             break;
         }
@@ -586,13 +605,18 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         switch (L.kind) {
         case L_CONNECT: {
             const int M = n, N = L.oc, K = (int)L.in_size;
-            // dW[K][N] = X^T[K][M] * dY[M][N]
-            rc = run_gemm<false, true>(net, K, N, M, ColMajor{in, K}, RowMajor{d, N}, dW, nullptr, st);
+            // dW[K][N] = X^T[K][M] * dY[M][N]   (reduction over the batch: both operands MN-major)
+            bool done;
+            rc = tc_try(net, in, d, dW, nullptr, K, N, M, true, true, st, &done);
+            if (rc != NC_OK) return rc;
+            if (!done) rc = run_gemm<false, true>(net, K, N, M, ColMajor{in, K}, RowMajor{d, N}, dW, nullptr, st);
             if (rc != NC_OK) return rc;
             rc = run_colsum(net, d, M, N, dB, st);
             if (rc != NC_OK) return rc;
-            if (need_dx) {   // dX[M][K] = dY[M][N] * W^T[N][K]
-                rc = run_gemm<true, false>(net, M, K, N, RowMajor{d, N}, ColMajor{W, N}, dn, nullptr, st);
+            if (need_dx) {   // dX[M][K] = dY[M][N] * W^T[N][K]   (W[in][out] is already the K-major B operand)
+                rc = tc_try(net, d, W, dn, nullptr, M, K, N, false, false, st, &done);
+                if (rc != NC_OK) return rc;
+                if (!done) rc = run_gemm<true, false>(net, M, K, N, RowMajor{d, N}, ColMajor{W, N}, dn, nullptr, st);
                 if (rc != NC_OK) return rc;
             }
             break;

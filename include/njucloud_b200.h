@@ -156,8 +156,8 @@ float* nc_net_params(nc_net* net);
 float* nc_net_grads(nc_net* net);
 int nc_net_set_params(nc_net* net, const float* host_params);   /* synchronous H2D */
 int nc_net_get_params(nc_net* net, float* host_params);         /* synchronous D2H */
-/* math: 0 = fp32 SIMT everywhere, 1 = TF32 tcgen05 tensor-core tiles for conv/dense with fp32
- * accumulate (default) */
+/* math: 0 = fp32 SIMT everywhere; 1 = tcgen05 tensor-core tiles in 3xTF32 (fp32-class accuracy);
+ * 2 = tcgen05 tiles with one round-to-nearest TF32 product (logits within ~2e-3 relative). */
 int nc_net_set_math(nc_net* net, int math);
 
 /* logits[n][classes] = net(x[n][in_h*in_w*in_c])   -- sess.run(y_conv / argmax)
@@ -184,6 +184,16 @@ int64_t nc_net_global_step(nc_net* net);
 int nc_net_state_slots(nc_net* net, int opt);
 int nc_net_get_state(nc_net* net, int opt, float* host_state);
 int nc_net_set_state(nc_net* net, int opt, const float* host_state, int64_t global_step);
+
+/* tf.matmul(a, b) (+ bias) as used by connect_layer() and the output layer
+ * (construct_distribute.py:182, :264) on the TF32 tensor-core path (tcgen05.mma, fp32 accumulate):
+ * out[m][n] = op(a) . op(b) + bias[n];  a is [m][k] ([k][m] if trans_a), b is [k][n] ([n][k] if
+ * trans_b), all row-major float32 device buffers, 16-byte aligned with row pitches that are
+ * multiples of 4 floats (NC_EUNSUPPORTED otherwise).  bias may be NULL.
+ * precision 0 = 3xTF32 (operands split into hi + lo TF32 parts, three MMAs per k step: fp32-class
+ * accuracy, ~1e-6 relative), 1 = one round-to-nearest TF32 product (~1e-3 relative). */
+int nc_matmul(nc_ctx* ctx, const float* a, const float* b, const float* bias, int m, int k, int n,
+              int trans_a, int trans_b, int precision, float* out, void* stream);
 
 /* ---- dense layer without any allocation -------------------------------------------------
  * No counterpart in the reference: this entry point exists for hosts of the library that must not

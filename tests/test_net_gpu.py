@@ -133,6 +133,33 @@ def test_optimizer_arithmetic(ctx, opt, lr):
         assert rel_err(st[:w.size], o.m) < 1e-5 and rel_err(st[w.size:], o.v) < 1e-5
 
 
+@pytest.mark.parametrize("name", ["lenet", "dense_only", "deep", "api_example"])
+@pytest.mark.parametrize("math,tol", [(1, 1e-4), (2, 8e-3)])
+def test_tensor_core_math_within_tolerance(ctx, name, math, tol):
+    """math 1 (tcgen05 tiles, 3xTF32, fp32 accumulate): logits, loss, gradients and post-step weights
+    within 1e-4 relative of the fp32 oracle -- well inside north_star's 1e-3.  math 2 (one rounded TF32
+    product, 10 mantissa bits per operand): stated tolerance 8e-3."""
+    ref, net, flat, x, y = make(name, ctx, seed=4)
+    net.set_math(math)
+    params = ref.unflatten(flat)
+    logits, cache = ref.forward(x, params, keep=True)
+    got = net.forward(torch.from_numpy(x).cuda()).cpu().numpy()
+    assert rel_err(got, logits) < tol, (name, rel_err(got, logits))
+    lref, dz = ref.loss_and_grad(logits, y, "entropy")
+    gref = ref.flatten(ref.backward(dz, params, cache))
+    lgot, _ = net.backward(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), "entropy")
+    assert abs(float(lgot.item()) - lref) < tol * max(1.0, abs(lref))
+    g = net.grads.cpu().numpy()
+    gmax = float(np.abs(gref).max())
+    for (off, size, shape), spec in zip(net.tensors, ref.param_specs):
+        err = float(np.abs(g[off:off + size].astype(np.float64) - gref[off:off + size]).max())
+        assert err < 2 * tol * max(float(np.abs(gref[off:off + size]).max()), 1e-2 * gmax), (name, spec[0], err)
+    w = flat.copy()
+    tfref.train_step(ref, w, x, y, tfref.SGD(w.size, 0.05))
+    net.apply("sgd", 0.05)
+    assert rel_err(net.get_params() - flat, w - flat) < 2 * tol
+
+
 def test_config_errors_and_defaults(ctx):
     from cloud_server_b200.net import Net
     with pytest.raises(ValueError):
