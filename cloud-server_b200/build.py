@@ -1,6 +1,7 @@
 """In-tree build of libnjucloud_b200.so with nvcc for sm_100a (no torch extension machinery:
 the library has a plain C ABI and links only the CUDA runtime)."""
 import glob
+import hashlib
 import os
 import subprocess
 
@@ -30,13 +31,27 @@ def _stale(out, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def _digest(deps):
+    """Content hash of every source the library is built from (mtimes do not survive being copied
+    to another machine; contents do)."""
+    h = hashlib.sha256()
+    for d in sorted(deps):
+        h.update(os.path.basename(d).encode())
+        with open(d, "rb") as f:
+            h.update(f.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
 def build_library(force=False, verbose=False):
     """Compile every CUDA/C++ source under csrc/ into lib/libnjucloud_b200.so (sm_100a)."""
     os.makedirs(LIBDIR, exist_ok=True)
     out = library_path()
     deps = sources() + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
         glob.glob(os.path.join(os.path.dirname(_HERE), "include", "*.h"))
-    if not force and not _stale(out, deps):
+    manifest = os.path.join(LIBDIR, "build_manifest.txt")
+    digest = _digest(deps)
+    if not force and os.path.exists(out) and os.path.exists(manifest) and open(manifest).read().strip() == digest:
         return out
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     # compile objects in parallel, then link
@@ -63,4 +78,6 @@ def build_library(force=False, verbose=False):
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout)
+    with open(manifest, "w") as f:
+        f.write(digest + "\n")
     return out

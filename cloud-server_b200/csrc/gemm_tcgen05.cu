@@ -18,8 +18,7 @@
 // (tcgen05.ld 32 lanes x 32 columns per warp -> bias / activation -> global).
 #include "nc_internal.h"
 #include "tc_gemm.h"
-#include <cuda.h>
-#include <cudaTypedefs.h>
+#include "tc_common.cuh"
 
 namespace {
 
@@ -27,53 +26,9 @@ constexpr int BM = 128, BK = 32;          // BK * 4 B = 128 B = one swizzle-128B
 constexpr int STAGES = 3;
 constexpr int kThreads = 192;             // 6 warps
 
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
-    unsigned ok;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-    } while (!ok);
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
-}
-
-// shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start>>4 [0,14), LBO>>4 [16,30),
-// SBO>>4 [32,46), version=1 [46,48), layout SWIZZLE_128B = 2 [61,64)
-__device__ __forceinline__ unsigned long long umma_desc(unsigned saddr, unsigned lbo_bytes, unsigned sbo_bytes,
-                                                        unsigned long long layout_type = 2) {
-    unsigned long long d = 0;
-    d |= (unsigned long long)((saddr >> 4) & 0x3FFF);
-    d |= (unsigned long long)((lbo_bytes >> 4) & 0x3FFF) << 16;
-    d |= (unsigned long long)((sbo_bytes >> 4) & 0x3FFF) << 32;
-    d |= 1ull << 46;
-    d |= layout_type << 61;
-    return d;
-}
-
 // X3 = true: "3xTF32" -- every fp32 operand is split into hi = rna_tf32(x) and lo = rna_tf32(x - hi) and
 // the product is accumulated as hi.hi + lo.hi + hi.lo (three MMAs per k step), which restores fp32-class
 // accuracy (error ~2^-21 per product) on the TF32 tensor pipe.  X3 = false: one rounded TF32 product.
-__device__ __forceinline__ void umma_tf32(unsigned tmem, unsigned long long da, unsigned long long db, unsigned idesc,
-                                          unsigned accum) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
-        ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(accum) : "memory");
-}
-
 template <int BN, bool A_MN, bool B_MN, bool X3>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ C,
@@ -270,36 +225,6 @@ __global__ void tc_reduce_kernel(float* __restrict__ dst, const float* __restric
         else if (act == 3) s = fmaxf(s, slope * s);
         dst[i] = s;
     }
-}
-
-PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
-
-int get_encode(nc_ctx* ctx) {
-    if (g_encode) return NC_OK;
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
-    if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
-        cudaGetLastError();
-        return nc_set_error(ctx, NC_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
-    }
-    g_encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
-    return NC_OK;
-}
-
-// row-major fp32 matrix [rows][cols] (ld = cols), box = 32 columns x box_rows rows, 128-byte swizzle, zero OOB fill
-int make_map(nc_ctx* ctx, CUtensorMap* map, const float* base, long long rows, long long cols, int box_rows,
-             bool mn_major = false) {
-    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)cols * sizeof(float)};
-    cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
-                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return nc_set_error(ctx, NC_ECUDA, "cuTensorMapEncodeTiled failed (%d) for %lld x %lld", (int)r, rows, cols);
-    return NC_OK;
 }
 
 template <int BN, bool A_MN, bool B_MN, bool X3>

@@ -488,6 +488,23 @@ static int tc_try(nc_net* net, const float* A, const float* B, float* C, const f
     return rc;
 }
 
+static ConvGeom geom(const Layer& L);
+// convolution on the tensor cores when the reduced channel count is a multiple of 32
+static int tc_conv_try(nc_net* net, int mode, const Layer& L, int n, const float* src, const float* wmat, float* out,
+                       const float* bias, cudaStream_t st, bool* done) {
+    *done = false;
+    const ConvGeom g = geom(L);
+    if (net->math == 0 || !nc_tc_conv_supported(mode, g, src, wmat)) return NC_OK;
+    int M, N, K;
+    nc_tc_conv_dims(mode, g, n, &M, &N, &K);
+    const size_t need = nc_tc_gemm_workspace(net->ctx->sm_count, M, N, K, nullptr, nullptr);
+    int rc = reserve_ws(net, need);
+    if (rc != NC_OK) return rc;
+    rc = nc_tc_conv(net->ctx, mode, g, n, src, wmat, out, bias, net->ws, net->ws_bytes, st, net->math == 1);
+    if (rc == NC_OK) *done = true;
+    return rc;
+}
+
 static ConvGeom geom(const Layer& L) { return ConvGeom{L.ih, L.iw, L.ic, L.oh, L.ow, L.oc, L.fh, L.fw, L.sh, L.sw, L.pt, L.pl}; }
 static PoolGeom pgeom(const Layer& L) { return PoolGeom{L.ih, L.iw, L.ic, L.oh, L.ow, L.fh, L.fw, L.sh, L.sw, L.pt, L.pl}; }
 
@@ -506,7 +523,10 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st) {
         switch (L.kind) {
         case L_CONV: {
             const int M = n * L.oh * L.ow, N = L.oc, K = L.fh * L.fw * L.ic;
-            rc = run_gemm<true, true>(net, M, N, K, Im2col{in, geom(L)}, RowMajor{W, N}, out, Bp, st);
+            bool done;
+            rc = tc_conv_try(net, 0, L, n, in, W, out, Bp, st, &done);
+            if (rc != NC_OK) return rc;
+            if (!done) rc = run_gemm<true, true>(net, M, N, K, Im2col{in, geom(L)}, RowMajor{W, N}, out, Bp, st);
             if (rc != NC_OK) return rc;
             break;
         }
@@ -623,12 +643,17 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         }
         case L_CONV: {
             const int M = n * L.oh * L.ow, N = L.oc, K = L.fh * L.fw * L.ic;
-            rc = run_gemm<false, true>(net, K, N, M, Im2colT{Im2col{in, geom(L)}}, RowMajor{d, N}, dW, nullptr, st);
+            bool done;
+            rc = tc_conv_try(net, 2, L, n, in, d, dW, nullptr, st, &done);
+            if (rc != NC_OK) return rc;
+            if (!done) rc = run_gemm<false, true>(net, K, N, M, Im2colT{Im2col{in, geom(L)}}, RowMajor{d, N}, dW, nullptr, st);
             if (rc != NC_OK) return rc;
             if (dB) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
             if (need_dx) {
                 const int Mi = n * L.ih * L.iw, Ki = L.fh * L.fw * L.oc;
-                rc = run_gemm<true, false>(net, Mi, L.ic, Ki, DgradA{d, geom(L)}, DgradB{W, geom(L)}, dn, nullptr, st);
+                rc = tc_conv_try(net, 1, L, n, d, W, dn, nullptr, st, &done);
+                if (rc != NC_OK) return rc;
+                if (!done) rc = run_gemm<true, false>(net, Mi, L.ic, Ki, DgradA{d, geom(L)}, DgradB{W, geom(L)}, dn, nullptr, st);
                 if (rc != NC_OK) return rc;
             }
             break;

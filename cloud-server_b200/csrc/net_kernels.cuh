@@ -5,6 +5,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "tc_gemm.h"
 
 namespace nck {
 
@@ -20,9 +21,6 @@ struct ColMajor {           // element (r, c) stored at p[c*ld + r]   (a transpo
     __device__ __forceinline__ float operator()(int r, int c) const { return __ldg(p + (long long)c * ld + r); }
 };
 
-struct ConvGeom {
-    int ih, iw, ic, oh, ow, oc, fh, fw, sh, sw, pt, pl;
-};
 
 // im2col view of the NHWC input: row m = (n, oy, ox), col k = (i, j, c)
 struct Im2col {

@@ -9,3 +9,16 @@ bool nc_tc_gemm_supported(const float* A, const float* B, int M, int N, int K, b
 size_t nc_tc_gemm_workspace(int sm_count, int M, int N, int K, int* splits_out, int* kbps_out);
 int nc_tc_gemm(nc_ctx* ctx, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
                bool b_mn, int act, float slope, float* ws, size_t ws_bytes, cudaStream_t st, bool x3);
+
+namespace nck {
+struct ConvGeom {
+    int ih, iw, ic, oh, ow, oc, fh, fw, sh, sw, pt, pl;
+};
+}  // namespace nck
+
+// implicit-GEMM convolution on the tensor cores (conv_tcgen05.cu).  mode: 0 forward (src = x, wmat = W,
+// out = y), 1 dgrad (src = dy, wmat = W, out = dx), 2 wgrad (src = x, wmat = dy, out = dW)
+bool nc_tc_conv_supported(int mode, const nck::ConvGeom& g, const float* src, const float* wmat);
+void nc_tc_conv_dims(int mode, const nck::ConvGeom& g, int batch, int* M, int* N, int* K);
+int nc_tc_conv(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, const float* src, const float* wmat, float* out,
+               const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3);
