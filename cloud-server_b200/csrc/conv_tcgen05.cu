@@ -20,7 +20,8 @@
 
 namespace {
 
-constexpr int BM = 128, BK = 32, STAGES = 3, kThreads = 192;
+constexpr int BM = 128, BK = 32, STAGES = 2, kThreads = 320;   // warps: 0 TMA, 1 MMA, 2..9 gather/round/epilogue
+constexpr int kGatherThreads = 256;
 enum { CM_FWD = 0, CM_DGRAD = 1, CM_WGRAD = 2 };
 
 struct ConvArgs {
@@ -35,51 +36,65 @@ __device__ __forceinline__ unsigned rna(float v) {
     return r;
 }
 
-// address of the 128-byte source row for A-tile row `t` of k block `kb` (nullptr = zero row)
+// Per-thread iterator over the 128-byte source rows of ONE A-tile row across consecutive k blocks.
+// All divisions happen once in init(); advancing to the next k block is a few adds and compares.
 template <int MODE>
-__device__ __forceinline__ const float* gather_row(const ConvArgs& a, int t, int m0, int kb, int M, int K) {
-    const nck::ConvGeom& g = a.g;
-    if (MODE == CM_FWD) {
-        const int m = m0 + t;
-        if (m >= M) return nullptr;
-        const int cpb = g.ic >> 5;                        // 32-channel blocks per tap
-        const int tap = kb / cpb, cb = kb - tap * cpb;
-        const int i = tap / g.fw, j = tap - i * g.fw;
-        const int ox = m % g.ow; const int q = m / g.ow; const int oy = q % g.oh, n = q / g.oh;
-        const int y = oy * g.sh - g.pt + i, x = ox * g.sw - g.pl + j;
-        if (y < 0 || y >= g.ih || x < 0 || x >= g.iw) return nullptr;
-        return a.src + (((long long)n * g.ih + y) * g.iw + x) * g.ic + cb * 32;
-    } else if (MODE == CM_DGRAD) {
-        const int m = m0 + t;
-        if (m >= M) return nullptr;
-        const int cpb = g.oc >> 5;
-        const int tap = kb / cpb, cb = kb - tap * cpb;
-        const int i = tap / g.fw, j = tap - i * g.fw;
-        const int x = m % g.iw; const int q = m / g.iw; const int y = q % g.ih, n = q / g.ih;
-        const int ny = y + g.pt - i, nx = x + g.pl - j;
-        if (ny < 0 || nx < 0 || ny % g.sh || nx % g.sw) return nullptr;
-        const int oy = ny / g.sh, ox = nx / g.sw;
-        if (oy >= g.oh || ox >= g.ow) return nullptr;
-        return a.src + (((long long)n * g.oh + oy) * g.ow + ox) * g.oc + cb * 32;
-    } else {
-        // wgrad: tile row t = (32-row chunk of dW rows, k-row); k = output position
-        const int chunk = t >> 5, krow = t & 31;
-        const int mc = (m0 >> 5) + chunk;                 // which 32-channel block of which tap
-        if (mc * 32 >= M) return nullptr;
-        const int p = kb * 32 + krow;                     // output position (n, oy, ox)
-        if (p >= K) return nullptr;
-        const int cpb = g.ic >> 5;
-        const int tap = mc / cpb, cb = mc - tap * cpb;
-        const int i = tap / g.fw, j = tap - i * g.fw;
-        const int ox = p % g.ow; const int q = p / g.ow; const int oy = q % g.oh, n = q / g.oh;
-        const int y = oy * g.sh - g.pt + i, x = ox * g.sw - g.pl + j;
-        if (y < 0 || y >= g.ih || x < 0 || x >= g.iw) return nullptr;
-        return a.src + (((long long)n * g.ih + y) * g.iw + x) * g.ic + cb * 32;
+struct RowIter {
+    int n, y, x;          // fwd: (n, oy, ox) of the output row; dgrad: (n, y, x) of the input row; wgrad: running output position
+    int i, j, cb, cpb;    // filter tap and 32-channel block (fwd/dgrad: advance with kb; wgrad: fixed per tile row)
+    int p;                // wgrad: running output position index
+    bool valid;           // the tile row exists at all
+
+    __device__ __forceinline__ void init(const ConvArgs& a, int row, int m0, int kb, int M) {
+        const nck::ConvGeom& g = a.g;
+        if (MODE == CM_WGRAD) {
+            const int chunk = row >> 5, krow = row & 31;
+            const int mc = (m0 >> 5) + chunk;
+            valid = mc * 32 < M;
+            cpb = g.ic >> 5;
+            const int tap = mc / cpb;
+            cb = mc - tap * cpb; i = tap / g.fw; j = tap - i * g.fw;
+            p = kb * 32 + krow;
+            x = p % g.ow; const int q = p / g.ow; y = q % g.oh; n = q / g.oh;
+        } else {
+            const int m = m0 + row;
+            valid = m < M;
+            const int w = MODE == CM_FWD ? g.ow : g.iw, h = MODE == CM_FWD ? g.oh : g.ih;
+            x = m % w; const int q = m / w; y = q % h; n = q / h;
+            cpb = (MODE == CM_FWD ? g.ic : g.oc) >> 5;
+            const int tap = kb / cpb;
+            cb = kb - tap * cpb; i = tap / g.fw; j = tap - i * g.fw;
+            p = 0;
+        }
     }
-}
+    __device__ __forceinline__ const float* ptr(const ConvArgs& a, int K) const {
+        const nck::ConvGeom& g = a.g;
+        if (!valid) return nullptr;
+        if (MODE == CM_DGRAD) {
+            const int ny = y + g.pt - i, nx = x + g.pl - j;
+            if (ny < 0 || nx < 0 || ny % g.sh || nx % g.sw) return nullptr;
+            const int oy = ny / g.sh, ox = nx / g.sw;
+            if (oy >= g.oh || ox >= g.ow) return nullptr;
+            return a.src + (((long long)n * g.oh + oy) * g.ow + ox) * g.oc + cb * 32;
+        }
+        if (MODE == CM_WGRAD && p >= K) return nullptr;
+        const int yy = y * g.sh - g.pt + i, xx = x * g.sw - g.pl + j;
+        if (yy < 0 || yy >= g.ih || xx < 0 || xx >= g.iw) return nullptr;
+        return a.src + (((long long)n * g.ih + yy) * g.iw + xx) * g.ic + cb * 32;
+    }
+    __device__ __forceinline__ void next(const ConvArgs& a) {
+        const nck::ConvGeom& g = a.g;
+        if (MODE == CM_WGRAD) {
+            p += 32; x += 32;
+            while (x >= g.ow) { x -= g.ow; if (++y == g.oh) { y = 0; ++n; } }
+        } else {
+            if (++cb == cpb) { cb = 0; if (++j == g.fw) { j = 0; ++i; } }
+        }
+    }
+};
 
 template <int BN, int MODE, bool X3>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ CUtensorMap tmB, float* __restrict__ C,
                  const float* __restrict__ bias, int M, int N, int K, int kb_per_slice, float* __restrict__ partial) {
     constexpr bool A_MN = MODE == CM_WGRAD;      // gathered rows are k-rows of an MN-major tile
@@ -102,7 +117,7 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(smem_u32(&s_full[s]), 1);
             mbar_init(smem_u32(&s_empty[s]), 1);
-            mbar_init(smem_u32(&s_ready[s]), 4);
+            mbar_init(smem_u32(&s_ready[s]), kGatherThreads / 32);
         }
         mbar_init(smem_u32(&s_tmem_full), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -170,35 +185,40 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
         }
     } else {
         // ===================== gather + round (main loop), then epilogue =====================
-        const int t = threadIdx.x - 64;              // 0..127: the A-tile row this thread owns
+        const int t2 = threadIdx.x - 64;             // 0..255: two threads per A-tile row
+        const int t = t2 >> 1, half = t2 & 1;        // row, and which four 16-byte chunks of it
         const int q = warp & 3;
-        uint4 cur[8];
+        RowIter<MODE> it;
+        it.init(args, t, m0, kb0, M);
+        uint4 cur[4];
         {
-            const float* p = nkb > 0 ? gather_row<MODE>(args, t, m0, kb0, M, K) : nullptr;
+            const float* p = nkb > 0 ? it.ptr(args, K) : nullptr;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) cur[c] = p ? __ldg(reinterpret_cast<const uint4*>(p) + c) : make_uint4(0, 0, 0, 0);
+            for (int c = 0; c < 4; ++c) cur[c] = p ? __ldg(reinterpret_cast<const uint4*>(p) + half * 4 + c) : make_uint4(0, 0, 0, 0);
         }
         for (int i = 0; i < nkb; ++i) {
             const int s = i % STAGES;
             const unsigned ph = (unsigned)(i / STAGES) & 1u;
-            // prefetch the next k block's row while this one is rounded and stored
-            uint4 nxt[8];
+            // prefetch the next k block's half row while this one is rounded and stored
+            uint4 nxt[4];
+            it.next(args);
             {
-                const float* p = (i + 1 < nkb) ? gather_row<MODE>(args, t, m0, kb0 + i + 1, M, K) : nullptr;
+                const float* p = (i + 1 < nkb) ? it.ptr(args, K) : nullptr;
 #pragma unroll
-                for (int c = 0; c < 8; ++c) nxt[c] = p ? __ldg(reinterpret_cast<const uint4*>(p) + c) : make_uint4(0, 0, 0, 0);
+                for (int c = 0; c < 4; ++c) nxt[c] = p ? __ldg(reinterpret_cast<const uint4*>(p) + half * 4 + c) : make_uint4(0, 0, 0, 0);
             }
             mbar_wait(smem_u32(&s_full[s]), ph);       // B landed => the stage is free and B can be rounded
             unsigned char* st = smem + (size_t)s * STAGE_BYTES;
-            // ---- A row -> swizzled UMMA layout
+            // ---- A half row -> swizzled UMMA layout
             unsigned char* arow;
             if (!A_MN) arow = st + t * 128;                                  // K-major: row t, 16-byte chunks XOR (t & 7)
             else arow = st + (t >> 5) * 4096 + (t & 31) * 128;               // MN-major: chunk t/32, k-row t%32, 32-byte units XOR (krow & 3)
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
+            for (int cc = 0; cc < 4; ++cc) {
+                const int c = half * 4 + cc;
                 const unsigned off = !A_MN ? ((unsigned)(c ^ (t & 7)) << 4)
                                            : ((((unsigned)(c >> 1) ^ (unsigned)(t & 3)) << 5) | ((unsigned)(c & 1) << 4));
-                const uint4 v = cur[c];
+                const uint4 v = cur[cc];
                 uint4 hi = make_uint4(rna(__uint_as_float(v.x)), rna(__uint_as_float(v.y)), rna(__uint_as_float(v.z)), rna(__uint_as_float(v.w)));
                 *reinterpret_cast<uint4*>(arow + off) = hi;
                 if (X3) {
@@ -210,21 +230,21 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
             // ---- B tile (TMA, raw fp32) -> rounded in place (+ lo copy)
             uint4* pb = reinterpret_cast<uint4*>(st + A_BYTES);
 #pragma unroll 2
-            for (int j = t; j < (int)(B_BYTES / 16); j += 128) {
-                const uint4 v = pb[j];
+            for (int jj = t2; jj < (int)(B_BYTES / 16); jj += kGatherThreads) {
+                const uint4 v = pb[jj];
                 uint4 hi = make_uint4(rna(__uint_as_float(v.x)), rna(__uint_as_float(v.y)), rna(__uint_as_float(v.z)), rna(__uint_as_float(v.w)));
-                pb[j] = hi;
+                pb[jj] = hi;
                 if (X3) {
                     uint4 lo = make_uint4(rna(__uint_as_float(v.x) - __uint_as_float(hi.x)), rna(__uint_as_float(v.y) - __uint_as_float(hi.y)),
                                           rna(__uint_as_float(v.z) - __uint_as_float(hi.z)), rna(__uint_as_float(v.w) - __uint_as_float(hi.w)));
-                    pb[j + HI_BYTES / 16] = lo;
+                    pb[jj + HI_BYTES / 16] = lo;
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[s])) : "memory");
 #pragma unroll
-            for (int c = 0; c < 8; ++c) cur[c] = nxt[c];
+            for (int c = 0; c < 4; ++c) cur[c] = nxt[c];
         }
         // ---- epilogue
         const int row = m0 + q * 32 + lane;
@@ -233,8 +253,9 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
         float* out = partial ? partial + (size_t)blockIdx.z * M * N : C;
+        // warps 2-5 take the even 32-column chunks, warps 6-9 the odd ones (each warp reads its own TMEM lane quarter)
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = (warp >= 6 ? 32 : 0); c0 < BN; c0 += 64) {
             unsigned r[32];
             if (nkb > 0) {
                 const unsigned taddr = tmem + ((unsigned)(q * 32) << 16) + (unsigned)c0;
@@ -253,13 +274,27 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
                 for (int j = 0; j < 32; ++j) r[j] = 0u;
             }
             if (row < M) {
+                float* po = out + (size_t)row * N + n0 + c0;
+                if (n0 + c0 + 32 <= N && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(po) & 15) == 0 &&
+                    (partial || !bias || (reinterpret_cast<uintptr_t>(bias) & 15) == 0)) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int col = n0 + c0 + j;
-                    if (col < N) {
-                        float v = __uint_as_float(r[j]);
-                        if (!partial && bias) v += __ldg(bias + col);
-                        out[(size_t)row * N + col] = v;
+                    for (int j = 0; j < 32; j += 4) {
+                        float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                        if (!partial && bias) {
+                            const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n0 + c0 + j));
+                            v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+                        }
+                        *reinterpret_cast<float4*>(po + j) = v;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int col = n0 + c0 + j;
+                        if (col < N) {
+                            float v = __uint_as_float(r[j]);
+                            if (!partial && bias) v += __ldg(bias + col);
+                            po[j] = v;
+                        }
                     }
                 }
             }

@@ -526,6 +526,13 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st) {
             bool done;
             rc = tc_conv_try(net, 0, L, n, in, W, out, Bp, st, &done);
             if (rc != NC_OK) return rc;
+            const size_t smallc_smem = (size_t)K * ((N + 31) / 32 * 32) * sizeof(float);
+            if (!done && L.ic <= 4 && smallc_smem <= 48 * 1024) {     // first layer: direct convolution
+                const long long total = (long long)M * ((N + 31) / 32);
+                conv_smallc_fwd_kernel<<<grid_for(total, sms), 256, smallc_smem, st>>>(in, W, Bp, out, geom(L), M);
+                NET_LAUNCH(net);
+                done = true;
+            }
             if (!done) rc = run_gemm<true, true>(net, M, N, K, Im2col{in, geom(L)}, RowMajor{W, N}, out, Bp, st);
             if (rc != NC_OK) return rc;
             break;
@@ -646,9 +653,28 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             bool done;
             rc = tc_conv_try(net, 2, L, n, in, d, dW, nullptr, st, &done);
             if (rc != NC_OK) return rc;
+            bool bias_done = false;
+            if (!done && L.ic <= 4 && K <= 32) {
+                // first layer: weight AND bias gradient in one pass over dY, per-CTA partials summed in fixed order
+                const int blocks = sms * 4;
+                rc = reserve_ws(net, (size_t)blocks * (K + 1) * N * sizeof(float));
+                if (rc != NC_OK) return rc;
+                float* pw = net->ws;
+                float* pb = net->ws + (size_t)blocks * K * N;
+                conv_smallc_wgrad_kernel<<<blocks, 256, 0, st>>>(in, d, pw, pb, geom(L), M);
+                NET_LAUNCH(net);
+                reduce_partials_kernel<<<grid_for((long long)K * N, sms), 256, 0, st>>>(dW, pw, blocks, (long long)K * N, nullptr, N);
+                NET_LAUNCH(net);
+                if (dB) {
+                    reduce_partials_kernel<<<1, 256, 0, st>>>(dB, pb, blocks, N, nullptr, N);
+                    NET_LAUNCH(net);
+                }
+                done = true;
+                bias_done = true;
+            }
             if (!done) rc = run_gemm<false, true>(net, K, N, M, Im2colT{Im2col{in, geom(L)}}, RowMajor{d, N}, dW, nullptr, st);
             if (rc != NC_OK) return rc;
-            if (dB) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
+            if (dB && !bias_done) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
             if (need_dx) {
                 const int Mi = n * L.ih * L.iw, Ki = L.fh * L.fw * L.oc;
                 rc = tc_conv_try(net, 1, L, n, d, W, dn, nullptr, st, &done);
@@ -660,8 +686,10 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         }
         case L_POOL:
             if (need_dx) {
-                const long long total_in = (long long)n * L.in_size;
-                maxpool_bwd_kernel<<<grid_for(total_in, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_in);
+                const long long total_in = (long long)n * L.in_size, total_out = (long long)n * L.out_size;
+                const bool tiled = L.fh == L.sh && L.fw == L.sw && L.pt == 0 && L.pl == 0 && L.oh * L.sh >= L.ih && L.ow * L.sw >= L.iw;
+                if (tiled) maxpool_bwd_tiled_kernel<<<grid_for(total_out, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_out);
+                else maxpool_bwd_kernel<<<grid_for(total_in, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_in);
                 NET_LAUNCH(net);
             }
             break;

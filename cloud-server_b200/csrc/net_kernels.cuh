@@ -173,6 +173,110 @@ __global__ void colsum_partial_kernel(const float* __restrict__ y, int rows, int
 }
 
 // ---------------------------------------------------------------------------------------------
+// direct convolution for few input channels (the first layer: Cin = 1 or 3).  An im2col GEMM with
+// K = fh*fw*Cin = 25 wastes a 64x64x16 tile; here one thread owns one output position and 32 output
+// channels (weights broadcast from shared memory), and the weight gradient keeps one output channel per
+// lane with fh*fw*Cin accumulators in registers, reduced per CTA and then across CTAs in fixed order.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+conv_smallc_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                       float* __restrict__ y, ConvGeom g, long long M) {
+    extern __shared__ float s_w[];                       // [fh*fw*ic][ocp], rows zero-padded to a multiple of 32
+    const int T = g.fh * g.fw * g.ic;
+    const int ocb = (g.oc + 31) >> 5, ocp = ocb * 32;
+    for (int i = threadIdx.x; i < T * ocp; i += blockDim.x) {
+        const int r = i / ocp, o = i - r * ocp;
+        s_w[i] = o < g.oc ? __ldg(w + r * g.oc + o) : 0.0f;
+    }
+    __syncthreads();
+    const long long total = M * ocb;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const int ob = (int)(idx % ocb);
+        const long long m = idx / ocb;
+        const int ox = (int)(m % g.ow); const long long q = m / g.ow; const int oy = (int)(q % g.oh); const int n = (int)(q / g.oh);
+        float acc[32];
+#pragma unroll
+        for (int o = 0; o < 32; ++o) acc[o] = 0.0f;
+        for (int i = 0; i < g.fh; ++i) {
+            const int yy = oy * g.sh - g.pt + i;
+            if (yy < 0 || yy >= g.ih) continue;
+            for (int j = 0; j < g.fw; ++j) {
+                const int xx = ox * g.sw - g.pl + j;
+                if (xx < 0 || xx >= g.iw) continue;
+                const float* px = x + (((long long)n * g.ih + yy) * g.iw + xx) * g.ic;
+                const float* pw = s_w + (size_t)((i * g.fw + j) * g.ic) * ocp + ob * 32;
+                for (int c = 0; c < g.ic; ++c) {
+                    const float v = __ldg(px + c);
+#pragma unroll
+                    for (int o = 0; o < 32; ++o) acc[o] = fmaf(v, pw[c * ocp + o], acc[o]);
+                }
+            }
+        }
+        float* py = y + m * g.oc + ob * 32;
+#pragma unroll
+        for (int o = 0; o < 32; ++o)
+            if (ob * 32 + o < g.oc) py[o] = acc[o] + (bias ? __ldg(bias + ob * 32 + o) : 0.0f);
+    }
+}
+
+// partial_w[block][T*oc], partial_b[block][oc]; T = fh*fw*ic <= 32
+__global__ void __launch_bounds__(256)
+conv_smallc_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partial_w,
+                         float* __restrict__ partial_b, ConvGeom g, long long M) {
+    __shared__ float s_red[8][33];
+    __shared__ int s_tdy[32], s_tdx[32], s_tc[32];
+    const int T = g.fh * g.fw * g.ic;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+    if (threadIdx.x < 32) {
+        const int t = threadIdx.x < T ? threadIdx.x : 0;
+        const int c = t % g.ic, ij = t / g.ic;
+        s_tdy[threadIdx.x] = ij / g.fw; s_tdx[threadIdx.x] = ij % g.fw; s_tc[threadIdx.x] = c;
+    }
+    __syncthreads();
+    const int ocb = (g.oc + 31) >> 5;
+    for (int ob = 0; ob < ocb; ++ob) {
+        const int co = ob * 32 + lane;
+        float acc[32];
+#pragma unroll
+        for (int t = 0; t < 32; ++t) acc[t] = 0.0f;
+        float accb = 0.0f;
+        for (long long m = (long long)blockIdx.x * nwarp + warp; m < M; m += (long long)gridDim.x * nwarp) {
+            const float gv = co < g.oc ? __ldg(dy + m * g.oc + co) : 0.0f;
+            accb += gv;
+            const int ox = (int)(m % g.ow); const long long q = m / g.ow; const int oy = (int)(q % g.oh); const int n = (int)(q / g.oh);
+            const int y0 = oy * g.sh - g.pt, x0 = ox * g.sw - g.pl;
+            const float* xb = x + (long long)n * g.ih * g.iw * g.ic;
+#pragma unroll
+            for (int t = 0; t < 32; ++t) {            // t is a compile-time register index; T is uniform
+                if (t < T) {
+                    const int yy = y0 + s_tdy[t], xx = x0 + s_tdx[t];
+                    const bool ok = yy >= 0 && yy < g.ih && xx >= 0 && xx < g.iw;
+                    const float v = ok ? __ldg(xb + ((long long)yy * g.iw + xx) * g.ic + s_tc[t]) : 0.0f;
+                    acc[t] = fmaf(v, gv, acc[t]);
+                }
+            }
+        }
+        // reduce the warps of this CTA in fixed order, one tap at a time
+        for (int t = 0; t <= T; ++t) {
+            float v = accb;
+            if (t < T) {
+#pragma unroll
+                for (int u = 0; u < 32; ++u) if (u == t) v = acc[u];
+            }
+            __syncthreads();
+            s_red[warp][lane] = v;
+            __syncthreads();
+            if (warp == 0 && co < g.oc) {
+                float sum = 0.0f;
+                for (int k = 0; k < nwarp; ++k) sum += s_red[k][lane];
+                if (t < T) partial_w[(size_t)blockIdx.x * T * g.oc + (size_t)t * g.oc + co] = sum;
+                else partial_b[(size_t)blockIdx.x * g.oc + co] = sum;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // pooling  (tf.nn.max_pool, construct_distribute.py:121-130)
 // ---------------------------------------------------------------------------------------------
 struct PoolGeom { int ih, iw, c, oh, ow, kh, kw, sh, sw, pt, pl; };
@@ -225,6 +329,29 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* 
             }
         }
         dx[idx] = s;
+    }
+}
+
+// scatter form for windows that tile the input exactly (kernel == stride, no padding): one thread per
+// window writes its kh*kw input positions (dy at the argmax, 0 elsewhere) -- no searching, coalesced in c
+__global__ void maxpool_bwd_tiled_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ arg, float* __restrict__ dx,
+                                         PoolGeom g, long long total_out) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total_out; idx += stride) {
+        const int c = idx % g.c; long long t = idx / g.c;
+        const int ox = t % g.ow; t /= g.ow;
+        const int oy = t % g.oh; const int n = (int)(t / g.oh);
+        const float gv = __ldg(dy + idx);
+        const int a = arg[idx];
+        for (int i = 0; i < g.kh; ++i) {
+            const int yy = oy * g.sh + i;
+            if (yy >= g.ih) continue;
+            for (int j = 0; j < g.kw; ++j) {
+                const int xx = ox * g.sw + j;
+                if (xx >= g.iw) continue;
+                dx[(((long long)n * g.ih + yy) * g.iw + xx) * g.c + c] = (a == i * g.kw + j) ? gv : 0.0f;
+            }
+        }
     }
 }
 
