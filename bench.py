@@ -261,7 +261,7 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
         out[key] = {
             "value": global_batch * steps / (ms * 1e-3), "unit": "images/s", "ms_per_step": per, "global_batch": global_batch,
             "per_gpu_batch": local, "optimizer": "Adagrad(1e-4) (what the reference runs)", "gpu_launches_per_step": cnt[0] / steps,
-            "math": {0: "fp32 simt", 1: "tcgen05 3xTF32 (fp32-class accuracy)", 2: "tcgen05 1xTF32"}[args.math],
+            "math": {0: "fp32 simt", 1: "tcgen05 3xTF32 (fp32-class accuracy)", 2: "tcgen05 1xTF32", 3: "tcgen05 3xTF32 forward + 1xTF32 gradients"}[args.math],
             "roofline": {"bound": "hbm", "achieved": byts / (per * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": byts / (per * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts,
                          "tflops": LENET_FLOP_PER_IMG * local / (per * 1e-3) / 1e12},
@@ -290,6 +290,33 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
         ms = time_steps(torch, e2e, steps, 3, False)
         out["train"]["e2e"] = {"value": 256 * steps / (ms * 1e-3), "unit": "images/s",
                                "h2d_bytes_per_step": 256 * (784 + 10) * 4, "d2h_bytes_per_step": 4}
+
+    # C5: the user-constructed deeper CNN (4 conv + 3 dense) on 32x32x3, global batch 512 over the ranks
+    from cloud_server_b200.configs import DEEPNET
+    n5 = 8192
+    x5 = torch.rand((n5, 32 * 32 * 3), device=device, generator=g)
+    y5 = torch.nn.functional.one_hot(torch.randint(0, 10, (n5,), device=device, generator=g), 10).float()
+    net5 = Net(DEEPNET, ctx, 32, 32, 3, seed=3)
+    net5.set_math(args.math)
+    dp5 = DataParallel(net5)
+    gb5 = 512
+    loc5 = gb5 // world
+    st5 = {"i": 0}
+
+    def step5():
+        b = st5["i"] % (n5 // gb5)
+        st5["i"] += 1
+        lo = b * gb5 + rank * loc5
+        dp5.train_step(x5[lo:lo + loc5], y5[lo:lo + loc5], "entropy", "compat")
+
+    ms5 = max_over_ranks(torch, time_steps(torch, step5, steps, args.warmup, dist_on), dist_on, device)
+    byts5 = 4 * loc5 * (2 * 114442 + 2 * 111370) + 32 * 2297130          # SURVEY 8(d) C5 formula
+    out["train_c5_deepnet"] = {
+        "value": gb5 * steps / (ms5 * 1e-3), "unit": "images/s", "ms_per_step": ms5 / steps, "global_batch": gb5,
+        "per_gpu_batch": loc5, "input": "32x32x3", "params": net5.param_count,
+        "roofline": {"bound": "hbm", "achieved": byts5 / (ms5 / steps * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": byts5 / (ms5 / steps * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts5,
+                     "tflops": 158.5e6 * loc5 / (ms5 / steps * 1e-3) / 1e12}}
 
     # inference: sess.run(argmax) (construct_inference.py:335-342), batched
     for nb_, key in ((4096, "predict"), (99, "predict_c1_99_pictures"), (1, "predict_single")):
@@ -442,7 +469,7 @@ def main():
     ap.add_argument("--e2e-batch", type=int, default=1024, help="uploads per e2e step (host pinned)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--math", type=int, default=1, help="CNN math: 0 fp32 SIMT, 1 tcgen05 3xTF32 (default), 2 tcgen05 1xTF32")
+    ap.add_argument("--math", type=int, default=3, help="CNN math: 0 fp32 SIMT, 1 tcgen05 3xTF32, 2 tcgen05 1xTF32, 3 (default) 3xTF32 forward + 1xTF32 gradients")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))

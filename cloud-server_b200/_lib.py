@@ -35,6 +35,7 @@ _SIGS = {
     "nc_pp_pil_table": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "nc_pp_gaussian_q8": (C.c_int, [C.c_int, C.c_void_p]),
     "nc_pp_normalise": (C.c_int, [C.c_void_p, c_u8p, C.c_int64, c_f32p, C.c_void_p]),
+    "nc_gather_rows": (C.c_int, [C.c_void_p, c_f32p, C.c_int64, C.c_int, C.c_void_p, C.c_int, c_f32p, C.c_void_p]),
     "nc_matmul": (C.c_int, [C.c_void_p, c_f32p, c_f32p, c_f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_f32p, C.c_void_p]),
     "nc_dense_forward_noalloc": (C.c_int, [C.c_void_p, c_f32p, c_f32p, c_f32p, C.c_int, C.c_int, C.c_int, c_f32p, C.c_void_p]),
     "nc_net_create": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64,

@@ -20,7 +20,9 @@
 
 namespace {
 
-constexpr int BM = 128, BK = 32, STAGES = 2, kThreads = 320;   // warps: 0 TMA, 1 MMA, 2..9 gather/round/epilogue
+constexpr int BM = 128, BK = 32, STAGES = 2, BRING = 2, kThreads = 320;   // warps: 0 TMA, 1 MMA, 2..9 gather/round/epilogue
+// STAGES = operand stages the MMA reads (rounded hi/lo tiles); BRING = raw fp32 B tiles in flight from TMA.  Keeping the TMA
+// ring separate takes the B load latency out of the stage-reuse chain (MMA done -> gather/round -> MMA).
 constexpr int kGatherThreads = 256;
 enum { CM_FWD = 0, CM_DGRAD = 1, CM_WGRAD = 2 };
 
@@ -30,11 +32,11 @@ struct ConvArgs {
     int batch;
 };
 
-__device__ __forceinline__ unsigned rna(float v) {
-    unsigned r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-    return r;
-}
+// round-to-nearest (ties away) to TF32 in two integer ops: add half an ulp of the 10-bit mantissa and clear
+// the 13 low bits (cvt.rna.tf32.f32 expands to a ~5 instruction inf/nan-safe sequence; operands here are finite).
+__device__ __forceinline__ unsigned rna(float v) { return (__float_as_uint(v) + 0x1000u) & 0xFFFFE000u; }
+// the lo part is only TRUNCATED by the tensor core (error 2^-21 relative to x): no rounding needed
+__device__ __forceinline__ unsigned lo_part(float v, unsigned hi) { return __float_as_uint(v - __uint_as_float(hi)); }
 
 // Per-thread iterator over the 128-byte source rows of ONE A-tile row across consecutive k blocks.
 // All divisions happen once in init(); advancing to the next k block is a few adds and compares.
@@ -104,7 +106,8 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
     constexpr unsigned HI_BYTES = A_BYTES + B_BYTES;
     constexpr unsigned STAGE_BYTES = X3 ? 2 * HI_BYTES : HI_BYTES;
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[STAGES], s_tmem_full;
+    __shared__ __align__(8) unsigned long long s_full[BRING], s_bempty[BRING], s_empty[STAGES], s_ready[STAGES], s_tmem_full;
+    unsigned char* braw = smem + (size_t)STAGES * STAGE_BYTES;       // raw B ring
     __shared__ unsigned s_tmem_base;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -114,8 +117,11 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
     const int nkb = min(kb_per_slice, nkb_total - kb0);
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) {
+        for (int s = 0; s < BRING; ++s) {
             mbar_init(smem_u32(&s_full[s]), 1);
+            mbar_init(smem_u32(&s_bempty[s]), kGatherThreads / 32);
+        }
+        for (int s = 0; s < STAGES; ++s) {
             mbar_init(smem_u32(&s_empty[s]), 1);
             mbar_init(smem_u32(&s_ready[s]), kGatherThreads / 32);
         }
@@ -135,12 +141,12 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
         // ===================== TMA producer: B tiles only =====================
         if (lane == 0) {
             for (int i = 0; i < nkb; ++i) {
-                const int s = i % STAGES;
-                const unsigned ph = (unsigned)(i / STAGES) & 1u;
-                mbar_wait(smem_u32(&s_empty[s]), ph ^ 1u);
+                const int s = i % BRING;
+                const unsigned ph = (unsigned)(i / BRING) & 1u;
+                mbar_wait(smem_u32(&s_bempty[s]), ph ^ 1u);
                 const unsigned full = smem_u32(&s_full[s]);
                 mbar_expect_tx(full, B_BYTES);
-                const unsigned sb = smem_u32(smem + (size_t)s * STAGE_BYTES) + A_BYTES;
+                const unsigned sb = smem_u32(braw + (size_t)s * B_BYTES);
                 const int kb = kb0 + i;
                 if (MODE == CM_DGRAD) {
                     // W[tap][c][co]: rows tap*Cin + n0 .., columns cb*32 ..   (K-major: co is the reduction index)
@@ -190,24 +196,23 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
         const int q = warp & 3;
         RowIter<MODE> it;
         it.init(args, t, m0, kb0, M);
-        uint4 cur[4];
-        {
-            const float* p = nkb > 0 ? it.ptr(args, K) : nullptr;
+        // register ring: the half rows of k blocks i, i+1, i+2 are in flight / in registers (global latency
+        // is ~2 k-block periods; one block of look-ahead left long_scoreboard as the top stall)
+        uint4 cur[4], nx1[4], nx2[4];
+        auto load_row = [&](uint4 (&dst)[4], bool live) {
+            const float* p = live ? it.ptr(args, K) : nullptr;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) cur[c] = p ? __ldg(reinterpret_cast<const uint4*>(p) + half * 4 + c) : make_uint4(0, 0, 0, 0);
-        }
+            for (int c = 0; c < 4; ++c) dst[c] = p ? __ldg(reinterpret_cast<const uint4*>(p) + half * 4 + c) : make_uint4(0, 0, 0, 0);
+        };
+        load_row(cur, nkb > 0);
+        it.next(args);
+        load_row(nx1, nkb > 1);
         for (int i = 0; i < nkb; ++i) {
             const int s = i % STAGES;
             const unsigned ph = (unsigned)(i / STAGES) & 1u;
-            // prefetch the next k block's half row while this one is rounded and stored
-            uint4 nxt[4];
             it.next(args);
-            {
-                const float* p = (i + 1 < nkb) ? it.ptr(args, K) : nullptr;
-#pragma unroll
-                for (int c = 0; c < 4; ++c) nxt[c] = p ? __ldg(reinterpret_cast<const uint4*>(p) + half * 4 + c) : make_uint4(0, 0, 0, 0);
-            }
-            mbar_wait(smem_u32(&s_full[s]), ph);       // B landed => the stage is free and B can be rounded
+            load_row(nx2, i + 2 < nkb);
+            mbar_wait(smem_u32(&s_empty[s]), ph ^ 1u);  // the MMAs that read this operand stage two blocks ago are done
             unsigned char* st = smem + (size_t)s * STAGE_BYTES;
             // ---- A half row -> swizzled UMMA layout
             unsigned char* arow;
@@ -222,29 +227,35 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
                 uint4 hi = make_uint4(rna(__uint_as_float(v.x)), rna(__uint_as_float(v.y)), rna(__uint_as_float(v.z)), rna(__uint_as_float(v.w)));
                 *reinterpret_cast<uint4*>(arow + off) = hi;
                 if (X3) {
-                    uint4 lo = make_uint4(rna(__uint_as_float(v.x) - __uint_as_float(hi.x)), rna(__uint_as_float(v.y) - __uint_as_float(hi.y)),
-                                          rna(__uint_as_float(v.z) - __uint_as_float(hi.z)), rna(__uint_as_float(v.w) - __uint_as_float(hi.w)));
+                    uint4 lo = make_uint4(lo_part(__uint_as_float(v.x), hi.x), lo_part(__uint_as_float(v.y), hi.y),
+                                          lo_part(__uint_as_float(v.z), hi.z), lo_part(__uint_as_float(v.w), hi.w));
                     *reinterpret_cast<uint4*>(arow + HI_BYTES + off) = lo;
                 }
             }
-            // ---- B tile (TMA, raw fp32) -> rounded in place (+ lo copy)
+            // ---- B tile: raw fp32 from the TMA ring -> rounded hi (+ lo) in the operand stage
+            const int sbr = i % BRING;
+            mbar_wait(smem_u32(&s_full[sbr]), (unsigned)(i / BRING) & 1u);
+            const uint4* praw = reinterpret_cast<const uint4*>(braw + (size_t)sbr * B_BYTES);
             uint4* pb = reinterpret_cast<uint4*>(st + A_BYTES);
 #pragma unroll 2
             for (int jj = t2; jj < (int)(B_BYTES / 16); jj += kGatherThreads) {
-                const uint4 v = pb[jj];
+                const uint4 v = praw[jj];
                 uint4 hi = make_uint4(rna(__uint_as_float(v.x)), rna(__uint_as_float(v.y)), rna(__uint_as_float(v.z)), rna(__uint_as_float(v.w)));
                 pb[jj] = hi;
                 if (X3) {
-                    uint4 lo = make_uint4(rna(__uint_as_float(v.x) - __uint_as_float(hi.x)), rna(__uint_as_float(v.y) - __uint_as_float(hi.y)),
-                                          rna(__uint_as_float(v.z) - __uint_as_float(hi.z)), rna(__uint_as_float(v.w) - __uint_as_float(hi.w)));
+                    uint4 lo = make_uint4(lo_part(__uint_as_float(v.x), hi.x), lo_part(__uint_as_float(v.y), hi.y),
+                                          lo_part(__uint_as_float(v.z), hi.z), lo_part(__uint_as_float(v.w), hi.w));
                     pb[jj + HI_BYTES / 16] = lo;
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
-            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[s])) : "memory");
+            if (lane == 0) {
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[s])) : "memory");
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_bempty[sbr])) : "memory");
+            }
 #pragma unroll
-            for (int c = 0; c < 4; ++c) cur[c] = nxt[c];
+            for (int c = 0; c < 4; ++c) { cur[c] = nx1[c]; nx1[c] = nx2[c]; }
         }
         // ---- epilogue
         const int row = m0 + q * 32 + lane;
@@ -319,7 +330,7 @@ __global__ void conv_reduce_kernel(float* __restrict__ dst, const float* __restr
 template <int BN, int MODE, bool X3>
 int launch_conv(nc_ctx* ctx, const ConvArgs& a, const CUtensorMap& mb, float* C, const float* bias, int M, int N, int K,
                 int kbps, int splits, float* partial, cudaStream_t st) {
-    const size_t smem = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) * (X3 ? 2 : 1) + 1024;
+    const size_t smem = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) * (X3 ? 2 : 1) + (size_t)BRING * BN * BK * 4 + 1024;
     auto kfn = conv_tf32_kernel<BN, MODE, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);

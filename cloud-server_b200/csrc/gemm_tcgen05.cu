@@ -144,19 +144,17 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint4* p = reinterpret_cast<uint4*>(smem + (size_t)s * STAGE_BYTES);
 #pragma unroll 4
             for (int j = (warp - 2) * 32 + lane; j < (int)(HI_BYTES / 16); j += 128) {
+                // round to nearest TF32 = add half an ulp of the 10-bit mantissa, clear the 13 low bits (2 integer ops;
+                // cvt.rna.tf32.f32 expands to ~5).  The lo part is only truncated by the tensor core: no rounding needed.
                 const uint4 v = p[j];
-                uint4 hi;
-                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi.x) : "f"(__uint_as_float(v.x)));
-                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi.y) : "f"(__uint_as_float(v.y)));
-                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi.z) : "f"(__uint_as_float(v.z)));
-                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi.w) : "f"(__uint_as_float(v.w)));
+                const uint4 hi = make_uint4((v.x + 0x1000u) & 0xFFFFE000u, (v.y + 0x1000u) & 0xFFFFE000u,
+                                            (v.z + 0x1000u) & 0xFFFFE000u, (v.w + 0x1000u) & 0xFFFFE000u);
                 p[j] = hi;
                 if (X3) {
-                    uint4 lo;
-                    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo.x) : "f"(__uint_as_float(v.x) - __uint_as_float(hi.x)));
-                    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo.y) : "f"(__uint_as_float(v.y) - __uint_as_float(hi.y)));
-                    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo.z) : "f"(__uint_as_float(v.z) - __uint_as_float(hi.z)));
-                    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo.w) : "f"(__uint_as_float(v.w) - __uint_as_float(hi.w)));
+                    const uint4 lo = make_uint4(__float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x)),
+                                                __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y)),
+                                                __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z)),
+                                                __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w)));
                     p[j + HI_BYTES / 16] = lo;
                 }
             }
@@ -268,17 +266,25 @@ size_t nc_tc_gemm_workspace(int sm_count, int M, int N, int K, int* splits_out, 
 
 int nc_tc_gemm(nc_ctx* ctx, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
                bool b_mn, int act, float slope, float* ws, size_t ws_bytes, cudaStream_t st, bool x3) {
+    if (!nc_tc_gemm_supported(A, B, M, N, K, a_mn, b_mn)) return nc_set_error(ctx, NC_EUNSUPPORTED, "tcgen05 GEMM: unaligned operands");
+    return nc_tc_gemm_ex(ctx, A, B, C, bias, M, N, K, a_mn, b_mn, 0, 0, K, K, act, slope, ws, ws_bytes, st, x3);
+}
+
+// lda / ldb: row pitch in floats (0 = natural); ka / kb: how many of the K reduction rows/columns really exist
+// in A / B (TMA zero-fills the rest)
+int nc_tc_gemm_ex(nc_ctx* ctx, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
+                  bool b_mn, int lda, int ldb, int ka, int kb, int act, float slope, float* ws, size_t ws_bytes, cudaStream_t st,
+                  bool x3) {
     int rc = get_encode(ctx);
     if (rc != NC_OK) return rc;
-    if (!nc_tc_gemm_supported(A, B, M, N, K, a_mn, b_mn)) return nc_set_error(ctx, NC_EUNSUPPORTED, "tcgen05 GEMM: unaligned operands");
     const int BN = N <= 64 ? 64 : 128;
     int splits, kbps;
     const size_t need = nc_tc_gemm_workspace(ctx->sm_count, M, N, K, &splits, &kbps);
     if (need > ws_bytes) return nc_set_error(ctx, NC_EINVAL, "tcgen05 GEMM: workspace %zu < %zu", ws_bytes, need);
     CUtensorMap ma, mb;
-    rc = a_mn ? make_map(ctx, &ma, A, K, M, 32, true) : make_map(ctx, &ma, A, M, K, BM);
+    rc = a_mn ? make_map(ctx, &ma, A, ka, M, 32, true, lda) : make_map(ctx, &ma, A, M, ka, BM, false, lda);
     if (rc != NC_OK) return rc;
-    rc = b_mn ? make_map(ctx, &mb, B, K, N, 32, true) : make_map(ctx, &mb, B, N, K, BN);
+    rc = b_mn ? make_map(ctx, &mb, B, kb, N, 32, true, ldb) : make_map(ctx, &mb, B, N, kb, BN, false, ldb);
     if (rc != NC_OK) return rc;
     float* partial = splits > 1 ? ws : nullptr;
 #define NC_TC_LAUNCH(BN_, AM, BMJ)                                                                                          \

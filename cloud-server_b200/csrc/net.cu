@@ -140,6 +140,7 @@ struct nc_net {
     float* act = nullptr; unsigned char* aux = nullptr; float* stat = nullptr;
     float *dbuf0 = nullptr, *dbuf1 = nullptr;
     float* ws = nullptr; size_t ws_bytes = 0;              // split-K partial sums (scratch)
+    float* col = nullptr; size_t col_bytes = 0;            // im2col of the first (few-channel) conv layer, tensor path
     std::string err;
 };
 
@@ -317,7 +318,7 @@ static double trunc_normal(uint64_t& s) {
 static void free_net(nc_net* net) {
     if (!net) return;
     cudaFree(net->params); cudaFree(net->grads); cudaFree(net->st_adagrad); cudaFree(net->st_adam);
-    cudaFree(net->act); cudaFree(net->aux); cudaFree(net->stat); cudaFree(net->dbuf0); cudaFree(net->dbuf1); cudaFree(net->ws);
+    cudaFree(net->act); cudaFree(net->aux); cudaFree(net->stat); cudaFree(net->dbuf0); cudaFree(net->dbuf1); cudaFree(net->ws); cudaFree(net->col);
     delete net;
 }
 
@@ -389,7 +390,8 @@ extern "C" int nc_net_get_params(nc_net* net, float* host_params) {
 }
 extern "C" int nc_net_set_math(nc_net* net, int math) {
     if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
-    if (math < 0 || math > 2) return net_err(net, NC_EINVAL, "math must be 0 (fp32 SIMT), 1 (3xTF32 tensor cores) or 2 (1xTF32 tensor cores)");
+    if (math < 0 || math > 3)
+        return net_err(net, NC_EINVAL, "math must be 0 (fp32 SIMT), 1 (3xTF32), 2 (1xTF32) or 3 (3xTF32 forward, 1xTF32 gradients)");
     net->math = math;
     return NC_OK;
 }
@@ -458,9 +460,9 @@ static int run_gemm(nc_net* net, int M, int N, int K, AF A, BF B, float* C, cons
 }
 
 static int run_colsum(nc_net* net, const float* y, int rows, int cols, float* out, cudaStream_t st) {
-    int splits = (rows + 2047) / 2048;
+    int splits = (rows + 255) / 256;            // enough CTAs to stream dY at full bandwidth
     if (splits < 1) splits = 1;
-    if (splits > 256) splits = 256;
+    if (splits > 64) splits = 64;                // the final fixed-order sum over the splits is serial per column
     const int rps = (rows + splits - 1) / splits;
     splits = (rows + rps - 1) / rps;
     int rc = reserve_ws(net, (size_t)splits * cols * sizeof(float));
@@ -474,21 +476,48 @@ static int run_colsum(nc_net* net, const float* y, int rows, int cols, float* ou
 }
 
 // dense contraction on the tensor cores (math 1) when TMA can address the operands; else SIMT
+static inline bool x3_for(const nc_net* net, bool backward) { return net->math == 1 || (net->math == 3 && !backward); }
+
 static int tc_try(nc_net* net, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
-                  bool b_mn, cudaStream_t st, bool* done) {
+                  bool b_mn, cudaStream_t st, bool* done, bool backward = false) {
     *done = false;
     if (net->math == 0 || !nc_tc_gemm_supported(A, B, M, N, K, a_mn, b_mn)) return NC_OK;
     const size_t need = nc_tc_gemm_workspace(net->ctx->sm_count, M, N, K, nullptr, nullptr);
     int rc = reserve_ws(net, need);
     if (rc != NC_OK) return rc;
     const int64_t before = net->ctx->launches;
-    rc = nc_tc_gemm(net->ctx, A, B, C, bias, M, N, K, a_mn, b_mn, 0, 0.0f, net->ws, net->ws_bytes, st, net->math == 1);
+    rc = nc_tc_gemm(net->ctx, A, B, C, bias, M, N, K, a_mn, b_mn, 0, 0.0f, net->ws, net->ws_bytes, st, x3_for(net, backward));
     (void)before;
     if (rc == NC_OK) *done = true;
     return rc;
 }
 
 static ConvGeom geom(const Layer& L);
+static int grid_for(long long count, int sm);
+
+// first layer (few input channels) on the tensor cores: explicit im2col (K padded to a multiple of 32),
+// then forward = col . W and weight gradient = col^T . dY with the TMA-fed GEMM.  The im2col buffer is
+// kept from the forward pass for the backward pass of the same step.
+static bool smallc_tc_ok(nc_net* net, const Layer& L, const float* W, const float* other) {
+    const int K = L.fh * L.fw * L.ic;
+    return net->math != 0 && L.ic <= 4 && K <= 128 && (L.oc % 4) == 0 && L.oc >= 8 &&
+           (reinterpret_cast<uintptr_t>(W) & 15) == 0 && (reinterpret_cast<uintptr_t>(other) & 15) == 0;
+}
+static int smallc_im2col(nc_net* net, const Layer& L, int n, const float* x, cudaStream_t st, int* Kp_out) {
+    const int K = L.fh * L.fw * L.ic, Kp = (K + 31) / 32 * 32;
+    const long long M = (long long)n * L.oh * L.ow;
+    const size_t need = (size_t)M * Kp * sizeof(float);
+    if (need > net->col_bytes) {
+        cudaFree(net->col); net->col = nullptr; net->col_bytes = 0;
+        if (cudaMalloc(&net->col, need) != cudaSuccess) { cudaGetLastError(); return net_err(net, NC_ENOMEM, "im2col buffer of %zu bytes", need); }
+        net->col_bytes = need;
+    }
+    im2col_smallc_kernel<<<grid_for(M * (Kp / 4), net->ctx->sm_count), 256, 0, st>>>(x, net->col, geom(L), M, K, Kp);
+    NET_LAUNCH(net);
+    *Kp_out = Kp;
+    return NC_OK;
+}
+
 // convolution on the tensor cores when the reduced channel count is a multiple of 32
 static int tc_conv_try(nc_net* net, int mode, const Layer& L, int n, const float* src, const float* wmat, float* out,
                        const float* bias, cudaStream_t st, bool* done) {
@@ -500,7 +529,7 @@ static int tc_conv_try(nc_net* net, int mode, const Layer& L, int n, const float
     const size_t need = nc_tc_gemm_workspace(net->ctx->sm_count, M, N, K, nullptr, nullptr);
     int rc = reserve_ws(net, need);
     if (rc != NC_OK) return rc;
-    rc = nc_tc_conv(net->ctx, mode, g, n, src, wmat, out, bias, net->ws, net->ws_bytes, st, net->math == 1);
+    rc = nc_tc_conv(net->ctx, mode, g, n, src, wmat, out, bias, net->ws, net->ws_bytes, st, x3_for(net, mode != 0));
     if (rc == NC_OK) *done = true;
     return rc;
 }
@@ -511,7 +540,7 @@ static PoolGeom pgeom(const Layer& L) { return PoolGeom{L.ih, L.iw, L.ic, L.oh, 
 // ------------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------------
-static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st) {
+static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, bool training = false) {
     int rc = reserve_batch(net, n);
     if (rc != NC_OK) return rc;
     const int sms = net->ctx->sm_count;
@@ -526,6 +555,7 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st) {
             bool done;
             rc = tc_conv_try(net, 0, L, n, in, W, out, Bp, st, &done);
             if (rc != NC_OK) return rc;
+            (void)training;
             const size_t smallc_smem = (size_t)K * ((N + 31) / 32 * 32) * sizeof(float);
             if (!done && L.ic <= 4 && smallc_smem <= 48 * 1024) {     // first layer: direct convolution
                 const long long total = (long long)M * ((N + 31) / 32);
@@ -614,7 +644,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         return net_err(net, NC_ECONFIG, "loss_function returns None for this loss_name (reference: ValueError in minimize); use entropy or mse");
     NET_CUDA(net, cudaSetDevice(net->ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
-    rc = forward_impl(net, x, n, st);
+    rc = forward_impl(net, x, n, st, true);
     if (rc != NC_OK) return rc;
     const int sms = net->ctx->sm_count;
     float* d = net->dbuf0;
@@ -634,14 +664,14 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             const int M = n, N = L.oc, K = (int)L.in_size;
             // dW[K][N] = X^T[K][M] * dY[M][N]   (reduction over the batch: both operands MN-major)
             bool done;
-            rc = tc_try(net, in, d, dW, nullptr, K, N, M, true, true, st, &done);
+            rc = tc_try(net, in, d, dW, nullptr, K, N, M, true, true, st, &done, true);
             if (rc != NC_OK) return rc;
             if (!done) rc = run_gemm<false, true>(net, K, N, M, ColMajor{in, K}, RowMajor{d, N}, dW, nullptr, st);
             if (rc != NC_OK) return rc;
             rc = run_colsum(net, d, M, N, dB, st);
             if (rc != NC_OK) return rc;
             if (need_dx) {   // dX[M][K] = dY[M][N] * W^T[N][K]   (W[in][out] is already the K-major B operand)
-                rc = tc_try(net, d, W, dn, nullptr, M, K, N, false, false, st, &done);
+                rc = tc_try(net, d, W, dn, nullptr, M, K, N, false, false, st, &done, true);
                 if (rc != NC_OK) return rc;
                 if (!done) rc = run_gemm<true, false>(net, M, K, N, RowMajor{d, N}, ColMajor{W, N}, dn, nullptr, st);
                 if (rc != NC_OK) return rc;
@@ -654,6 +684,17 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             rc = tc_conv_try(net, 2, L, n, in, d, dW, nullptr, st, &done);
             if (rc != NC_OK) return rc;
             bool bias_done = false;
+            if (!done && smallc_tc_ok(net, L, W, d)) {
+                // first layer: dW[K][N] = col^T[K][M] . dY[M][N] on the tensor cores over an explicit im2col
+                int Kp;
+                rc = smallc_im2col(net, L, n, in, st, &Kp);
+                if (rc != NC_OK) return rc;
+                rc = reserve_ws(net, nc_tc_gemm_workspace(sms, K, N, M, nullptr, nullptr));
+                if (rc != NC_OK) return rc;
+                rc = nc_tc_gemm_ex(net->ctx, net->col, d, dW, nullptr, K, N, M, true, true, Kp, N, M, M, 0, 0.0f, net->ws, net->ws_bytes, st, x3_for(net, true));
+                if (rc != NC_OK) return rc;
+                done = true;
+            }
             if (!done && L.ic <= 4 && K <= 32) {
                 // first layer: weight AND bias gradient in one pass over dY, per-CTA partials summed in fixed order
                 const int blocks = sms * 4;

@@ -219,6 +219,30 @@ conv_smallc_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
     }
 }
 
+// im2col for few input channels: col[m][kp] (kp = K rounded up to 32, zero padded) so that the first
+// layer can ride the tensor-core GEMM as well (forward: col . W, weight gradient: col^T . dY)
+__global__ void im2col_smallc_kernel(const float* __restrict__ x, float* __restrict__ col, ConvGeom g, long long M, int K, int Kp) {
+    const long long total = M * (Kp / 4);
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const int k4 = (int)(idx % (Kp / 4)) * 4;
+        const long long m = idx / (Kp / 4);
+        const int ox = (int)(m % g.ow); const long long q = m / g.ow; const int oy = (int)(q % g.oh); const int n = (int)(q / g.oh);
+        float v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int k = k4 + u;
+            float r = 0.0f;
+            if (k < K) {
+                const int c = k % g.ic, ij = k / g.ic, j = ij % g.fw, i = ij / g.fw;
+                const int yy = oy * g.sh - g.pt + i, xx = ox * g.sw - g.pl + j;
+                if (yy >= 0 && yy < g.ih && xx >= 0 && xx < g.iw) r = __ldg(x + (((long long)n * g.ih + yy) * g.iw + xx) * g.ic + c);
+            }
+            v[u] = r;
+        }
+        *reinterpret_cast<float4*>(col + m * Kp + k4) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+}
+
 // partial_w[block][T*oc], partial_b[block][oc]; T = fh*fw*ic <= 32
 __global__ void __launch_bounds__(256)
 conv_smallc_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partial_w,

@@ -70,9 +70,9 @@ int get_encode(nc_ctx* ctx) {
 
 // row-major fp32 matrix [rows][cols] (ld = cols), box = 32 columns x box_rows rows, 128-byte swizzle, zero OOB fill
 int make_map(nc_ctx* ctx, CUtensorMap* map, const float* base, long long rows, long long cols, int box_rows,
-             bool mn_major = false) {
+             bool mn_major = false, long long ld = 0) {
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)cols * sizeof(float)};
+    cuuint64_t strides[1] = {(cuuint64_t)(ld > 0 ? ld : cols) * sizeof(float)};
     cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1u, 1u};
     CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,

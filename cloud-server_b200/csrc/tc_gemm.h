@@ -9,6 +9,9 @@ bool nc_tc_gemm_supported(const float* A, const float* B, int M, int N, int K, b
 size_t nc_tc_gemm_workspace(int sm_count, int M, int N, int K, int* splits_out, int* kbps_out);
 int nc_tc_gemm(nc_ctx* ctx, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
                bool b_mn, int act, float slope, float* ws, size_t ws_bytes, cudaStream_t st, bool x3);
+int nc_tc_gemm_ex(nc_ctx* ctx, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
+                  bool b_mn, int lda, int ldb, int ka, int kb, int act, float slope, float* ws, size_t ws_bytes, cudaStream_t st,
+                  bool x3);
 
 namespace nck {
 struct ConvGeom {

@@ -134,6 +134,12 @@ int nc_pp_gaussian_q8(int k, int32_t* q);
  * (DataSet.__init__, construct_distribute.py:503-504). */
 int nc_pp_normalise(nc_ctx* ctx, const uint8_t* in, int64_t count, float* out, void* stream);
 
+/* Batch assembly on the device: out[r][:] = src[idx[r]][:] for float32 rows of `width` floats --
+ * the `self._images[perm]` / slice of DataSet.next_batch (construct_distribute.py:526-569) with the
+ * dataset resident in HBM.  idx is a DEVICE array of int64 row numbers in [0, n_src). */
+int nc_gather_rows(nc_ctx* ctx, const float* src, int64_t n_src, int width, const int64_t* idx, int n,
+                   float* out, void* stream);
+
 /* ---- CNN graph: construct / forward / backward / update --------------------------------
  * nc_net_create replaces cnn() + get_net() (construct_distribute.py:208-281, identical copy in
  * construct_inference.py:53-279): it interprets net_config_json = the value of
@@ -157,7 +163,9 @@ float* nc_net_grads(nc_net* net);
 int nc_net_set_params(nc_net* net, const float* host_params);   /* synchronous H2D */
 int nc_net_get_params(nc_net* net, float* host_params);         /* synchronous D2H */
 /* math: 0 = fp32 SIMT everywhere; 1 = tcgen05 tensor-core tiles in 3xTF32 (fp32-class accuracy);
- * 2 = tcgen05 tiles with one round-to-nearest TF32 product (logits within ~2e-3 relative). */
+ * 2 = tcgen05 tiles with one round-to-nearest TF32 product (logits within ~2e-3 relative);
+ * 3 = 3xTF32 for the forward pass (logits / loss as in mode 1), one rounded TF32 product for the
+ *     two gradient contractions (gradients ~1e-3 relative, post-step weights far inside 1e-3). */
 int nc_net_set_math(nc_net* net, int math);
 
 /* logits[n][classes] = net(x[n][in_h*in_w*in_c])   -- sess.run(y_conv / argmax)

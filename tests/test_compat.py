@@ -170,3 +170,23 @@ def test_train_and_inference_scripts_end_to_end(ctx, tmp_path, monkeypatch):
     with pytest.raises(ValueError):
         ci.main(["--config=" + json.dumps(config), "--filename=x.jpg", "--save_path=./nowhere/"] if os.path.isdir("./nowhere/") else
                 ["--config=" + json.dumps(config), "--filename=x.jpg", "--model_name=absent"])
+
+
+@pytest.mark.gpu
+def test_device_dataset_matches_reference_dataset(ctx):
+    """DeviceDataSet.next_batch (HBM-resident pictures, gather kernel) == the reference DataSet semantics
+    (oracle restatement of construct_distribute.py:526-569) batch for batch, under the same RNG state."""
+    import torch
+    from cloud_server_b200.dataset import DeviceDataSet
+    rng = np.random.default_rng(0)
+    imgs = rng.integers(0, 256, (203, 28, 28, 1), np.uint8)
+    labs = np.eye(10, dtype=np.float32)[rng.integers(0, 10, 203)]
+    np.random.seed(11)
+    dev_ds = DeviceDataSet(imgs, labs, ctx)
+    ref = tfref.DataSet(imgs, labs, rs=np.random.RandomState(11))
+    for step in range(12):
+        xb, yb = dev_ds.next_batch(50)
+        xr, yr = ref.next_batch(50)
+        assert np.array_equal(xb.cpu().numpy(), xr), step
+        assert np.array_equal(yb.cpu().numpy(), yr), step
+    assert dev_ds.epochs_completed == 2
