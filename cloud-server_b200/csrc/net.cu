@@ -120,6 +120,7 @@ struct Layer {
     int64_t aux_off = -1;                                   // pool argmax (bytes/sample) or norm xhat (floats/sample)
     int64_t stat_off = -1;                                  // norm: inv-std per channel (floats, absolute)
     bool in_is_4d = true;
+    bool relu_into_pool = false;    // ACT(relu) whose only consumer is the next POOL: applied inside the pool kernels
 };
 
 struct TensorInfo { int64_t off, size; int ndim; int64_t dims[4]; int init; double arg; };
@@ -285,6 +286,9 @@ static int build_layers(nc_net* net, const JVal& cfg) {
     const int64_t wd[2] = {feat, net->classes}; add_tensor(net, 2, wd, INIT_NORM, 0.1, &o.w_off);
     const int64_t bd[1] = {net->classes}; add_tensor(net, 1, bd, INIT_CONST, 0.1, &o.b_off);
     net->layers.push_back(o);
+    for (size_t i = 0; i + 1 < net->layers.size(); ++i)
+        if (net->layers[i].kind == L_ACT && net->layers[i].act == ACT_RELU && net->layers[i + 1].kind == L_POOL)
+            net->layers[i].relu_into_pool = true;
     // arena offsets
     int64_t act = 0, aux = 0, stat = 0, mx = (int64_t)net->in_h * net->in_w * net->in_c;
     for (auto& L : net->layers) {
@@ -545,7 +549,9 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
     if (rc != NC_OK) return rc;
     const int sms = net->ctx->sm_count;
     const float* in = x;
+    bool pending_relu = false;
     for (auto& L : net->layers) {
+        if (L.kind == L_ACT && L.relu_into_pool) { pending_relu = true; continue; }   // `in` stays the pre-activation
         float* out = act_ptr(net, L);
         const float* W = L.w_off >= 0 ? net->params + L.w_off : nullptr;
         const float* Bp = L.b_off >= 0 ? net->params + L.b_off : nullptr;
@@ -578,8 +584,9 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
         }
         case L_POOL: {
             const long long total = (long long)n * L.out_size;
-            maxpool_fwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(in, out, net->aux + L.aux_off * net->cap, pgeom(L), total);
+            maxpool_fwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(in, out, net->aux + L.aux_off * net->cap, pgeom(L), total, pending_relu ? 1 : 0);
             NET_LAUNCH(net);
+            pending_relu = false;
             break;
         }
         case L_ACT: {
@@ -651,8 +658,11 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
     float* dn = net->dbuf1;
     loss_kernel<<<1, 1024, 0, st>>>(act_ptr(net, net->layers.back()), y_onehot, d, n, net->classes, loss_name, grad_scale, loss_out, (int*)correct_out);
     NET_LAUNCH(net);
+    bool skip_fused_relu = false;
     for (int li = (int)net->layers.size() - 1; li >= 0; --li) {
         Layer& L = net->layers[li];
+        if (L.kind == L_ACT && L.relu_into_pool && skip_fused_relu) { skip_fused_relu = false; continue; }   // done inside the pool backward
+        // the input of a layer that follows a fused relu is that relu's (never materialised) output: pool kernels take the pre-activation
         const float* in = li == 0 ? x : act_ptr(net, net->layers[li - 1]);
         const float* out = act_ptr(net, L);
         const float* W = L.w_off >= 0 ? net->params + L.w_off : nullptr;
@@ -729,7 +739,10 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             if (need_dx) {
                 const long long total_in = (long long)n * L.in_size, total_out = (long long)n * L.out_size;
                 const bool tiled = L.fh == L.sh && L.fw == L.sw && L.pt == 0 && L.pl == 0 && L.oh * L.sh >= L.ih && L.ow * L.sw >= L.iw;
-                if (tiled) maxpool_bwd_tiled_kernel<<<grid_for(total_out, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_out);
+                const bool fused = tiled && li > 0 && net->layers[li - 1].relu_into_pool;
+                if (fused) skip_fused_relu = true;      // this launch already yields the gradient w.r.t. the pre-activation
+                if (tiled) maxpool_bwd_tiled_kernel<<<grid_for(total_out, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_out,
+                                                                                          fused ? out : nullptr);
                 else maxpool_bwd_kernel<<<grid_for(total_in, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_in);
                 NET_LAUNCH(net);
             }

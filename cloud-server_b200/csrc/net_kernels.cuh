@@ -305,8 +305,9 @@ conv_smallc_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ 
 // ---------------------------------------------------------------------------------------------
 struct PoolGeom { int ih, iw, c, oh, ow, kh, kw, sh, sw, pt, pl; };
 
+// relu != 0: the input is a pre-activation and relu is applied on the fly (active(relu) + max_pool in one pass)
 __global__ void maxpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ arg,
-                                   PoolGeom g, long long total) {
+                                   PoolGeom g, long long total, int relu) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
         const int c = idx % g.c; long long t = idx / g.c;
@@ -319,7 +320,8 @@ __global__ void maxpool_fwd_kernel(const float* __restrict__ x, float* __restric
             for (int j = 0; j < g.kw; ++j) {
                 const int xx = ox * g.sw - g.pl + j;
                 if (xx < 0 || xx >= g.iw) continue;
-                const float v = __ldg(x + (((long long)n * g.ih + yy) * g.iw + xx) * g.c + c);
+                float v = __ldg(x + (((long long)n * g.ih + yy) * g.iw + xx) * g.c + c);
+                if (relu) v = fmaxf(v, 0.0f);
                 if (v > best) { best = v; bi = i * g.kw + j; }   // strict '>': first maximum wins
             }
         }
@@ -358,14 +360,17 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* 
 
 // scatter form for windows that tile the input exactly (kernel == stride, no padding): one thread per
 // window writes its kh*kw input positions (dy at the argmax, 0 elsewhere) -- no searching, coalesced in c
+// pooled != nullptr: the pool input was relu(pre-activation); the relu mask at the argmax is pooled > 0, so the
+// result is the gradient w.r.t. the pre-activation (max_pool backward + relu backward in one pass)
 __global__ void maxpool_bwd_tiled_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ arg, float* __restrict__ dx,
-                                         PoolGeom g, long long total_out) {
+                                         PoolGeom g, long long total_out, const float* __restrict__ pooled) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total_out; idx += stride) {
         const int c = idx % g.c; long long t = idx / g.c;
         const int ox = t % g.ow; t /= g.ow;
         const int oy = t % g.oh; const int n = (int)(t / g.oh);
-        const float gv = __ldg(dy + idx);
+        float gv = __ldg(dy + idx);
+        if (pooled && !(__ldg(pooled + idx) > 0.0f)) gv = 0.0f;
         const int a = arg[idx];
         for (int i = 0; i < g.kh; ++i) {
             const int yy = oy * g.sh + i;
@@ -402,7 +407,7 @@ __global__ void act_bwd_kernel(const float* __restrict__ x, const float* __restr
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
         const float g = __ldg(dy + i);
         float r;
-        if (fn == ACT_RELU) r = __ldg(y + i) > 0.0f ? g : 0.0f;
+        if (fn == ACT_RELU) r = __ldg(x + i) > 0.0f ? g : 0.0f;      // x > 0 <=> relu(x) > 0; x is always kept
         else if (fn == ACT_SIGMOID) { const float v = __ldg(y + i); r = g * v * (1.0f - v); }
         else { const float v = __ldg(x + i); r = (v >= slope * v) ? g : slope * g; }
         dx[i] = r;
