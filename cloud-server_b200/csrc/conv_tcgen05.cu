@@ -119,7 +119,7 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
     if (threadIdx.x == 0) {
         for (int s = 0; s < BRING; ++s) {
             mbar_init(smem_u32(&s_full[s]), 1);
-            mbar_init(smem_u32(&s_bempty[s]), kGatherThreads / 32);
+            mbar_init(smem_u32(&s_bempty[s]), X3 ? kGatherThreads / 32 : 1);   // 1x: released by the MMA commit
         }
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(smem_u32(&s_empty[s]), 1);
@@ -168,9 +168,11 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
                 const int s = i % STAGES;
                 const unsigned ph = (unsigned)(i / STAGES) & 1u;
                 mbar_wait(smem_u32(&s_ready[s]), ph);
+                const int sbr = i % BRING;
+                if (!X3) mbar_wait(smem_u32(&s_full[sbr]), (unsigned)(i / BRING) & 1u);   // 1x: B is consumed raw, straight from the TMA ring
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const unsigned sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
-                const unsigned sb = sa + A_BYTES;
+                const unsigned sb = X3 ? sa + A_BYTES : smem_u32(braw + (size_t)sbr * B_BYTES);
 #pragma unroll
                 for (int kk = 0; kk < BK / 8; ++kk) {
                     const unsigned long long da = A_MN ? umma_desc(sa + kk * 1024, 4096, 512, 1) : umma_desc(sa + kk * 32, 16, 1024);
@@ -186,6 +188,7 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
                     }
                 }
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_empty[s])) : "memory");
+                if (!X3) asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_bempty[sbr])) : "memory");
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_tmem_full)) : "memory");
         }
@@ -224,7 +227,9 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
                 const unsigned off = !A_MN ? ((unsigned)(c ^ (t & 7)) << 4)
                                            : ((((unsigned)(c >> 1) ^ (unsigned)(t & 3)) << 5) | ((unsigned)(c & 1) << 4));
                 const uint4 v = cur[cc];
-                uint4 hi = make_uint4(rna(__uint_as_float(v.x)), rna(__uint_as_float(v.y)), rna(__uint_as_float(v.z)), rna(__uint_as_float(v.w)));
+                // 1x mode stores the fp32 bits as they are: kind::tf32 truncates them, a one-sided ~5e-4 relative shrink
+                // that is harmless for gradients (mode 3) and is what the lossy mode 2 states
+                uint4 hi = X3 ? make_uint4(rna(__uint_as_float(v.x)), rna(__uint_as_float(v.y)), rna(__uint_as_float(v.z)), rna(__uint_as_float(v.w))) : v;
                 *reinterpret_cast<uint4*>(arow + off) = hi;
                 if (X3) {
                     uint4 lo = make_uint4(lo_part(__uint_as_float(v.x), hi.x), lo_part(__uint_as_float(v.y), hi.y),
@@ -232,13 +237,13 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
                     *reinterpret_cast<uint4*>(arow + HI_BYTES + off) = lo;
                 }
             }
-            // ---- B tile: raw fp32 from the TMA ring -> rounded hi (+ lo) in the operand stage
+            // ---- B tile (3x only): raw fp32 from the TMA ring -> rounded hi + lo in the operand stage
             const int sbr = i % BRING;
-            mbar_wait(smem_u32(&s_full[sbr]), (unsigned)(i / BRING) & 1u);
+            if (X3) mbar_wait(smem_u32(&s_full[sbr]), (unsigned)(i / BRING) & 1u);
             const uint4* praw = reinterpret_cast<const uint4*>(braw + (size_t)sbr * B_BYTES);
             uint4* pb = reinterpret_cast<uint4*>(st + A_BYTES);
 #pragma unroll 2
-            for (int jj = t2; jj < (int)(B_BYTES / 16); jj += kGatherThreads) {
+            for (int jj = t2; X3 && jj < (int)(B_BYTES / 16); jj += kGatherThreads) {
                 const uint4 v = praw[jj];
                 uint4 hi = make_uint4(rna(__uint_as_float(v.x)), rna(__uint_as_float(v.y)), rna(__uint_as_float(v.z)), rna(__uint_as_float(v.w)));
                 pb[jj] = hi;
@@ -252,7 +257,7 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
             __syncwarp();
             if (lane == 0) {
                 asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[s])) : "memory");
-                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_bempty[sbr])) : "memory");
+                if (X3) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_bempty[sbr])) : "memory");
             }
 #pragma unroll
             for (int c = 0; c < 4; ++c) { cur[c] = nx1[c]; nx1[c] = nx2[c]; }

@@ -102,7 +102,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
                 const unsigned ph = (unsigned)(i / STAGES) & 1u;
-                mbar_wait(smem_u32(&s_ready[s]), ph);      // operands landed AND rounded to TF32
+                mbar_wait(smem_u32(X3 ? &s_ready[s] : &s_full[s]), ph);      // 3x: operands landed AND split; 1x: as TMA left them
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const unsigned sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 const unsigned sb = sa + A_BYTES;
@@ -137,7 +137,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // During the main loop these four warps round the staged fp32 operands to TF32 (round to nearest,
         // ties away: cvt.rna) in place.  kind::tf32 otherwise TRUNCATES the 13 low mantissa bits, a
         // one-sided error of ~1e-3 per product that does not average out over the dot product.
-        for (int i = 0; i < nkb; ++i) {
+        // (1x mode feeds the fp32 bits as they are: kind::tf32 truncates -- fine for gradients, stated for mode 2)
+        for (int i = 0; X3 && i < nkb; ++i) {
             const int s = i % STAGES;
             const unsigned ph = (unsigned)(i / STAGES) & 1u;
             mbar_wait(smem_u32(&s_full[s]), ph);

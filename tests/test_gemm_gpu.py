@@ -18,7 +18,7 @@ def _check(ctx, m, k, n, ta, tb, bias, seed, precision=0):
     B = b.double().cpu().T if tb else b.double().cpu()
     want = A @ B + (bv.double().cpu() if bias else 0)
     err = float((got - want).abs().max() / want.abs().max())
-    assert err < (3e-6 if precision == 0 else 2e-3), (m, k, n, ta, tb, precision, err)
+    assert err < (3e-6 if precision == 0 else 4e-3), (m, k, n, ta, tb, precision, err)   # 1x: truncated TF32 operands
     return err
 
 

@@ -155,13 +155,16 @@ def test_tensor_core_math_within_tolerance(ctx, name, math, tol):
     gmax = float(np.abs(gref).max())
     for (off, size, shape), spec in zip(net.tensors, ref.param_specs):
         err = float(np.abs(g[off:off + size].astype(np.float64) - gref[off:off + size]).max())
-        gtol = 2 * tol if math == 1 else (1e-2 if math == 3 else 1e-1)   # 1xTF32 gradients: 1 % (mixed) / 10 % (all-1x, deep nets)
+        gtol = 2 * tol if math == 1 else 3e-2   # mode 3: gradients ride truncated-TF32 products (one-sided ~5e-4 per contraction, 7 layers deep)
         assert err < gtol * max(float(np.abs(gref[off:off + size]).max()), 1e-2 * gmax), (name, spec[0], err)
+    # post-step weights with the optimizer the reference actually runs, AdagradOptimizer(1e-4)
+    # (construct_distribute.py:372-373): north_star's bar is 1e-3 relative; the update itself is held to gtol
     w = flat.copy()
-    tfref.train_step(ref, w, x, y, tfref.SGD(w.size, 0.05))
-    net.apply("sgd", 0.05)
-    assert rel_err(net.get_params() - flat, w - flat) < (2 * tol if math == 1 else (1e-2 if math == 3 else 1e-1))
-    assert rel_err(net.get_params(), w) < 1e-3          # north_star: post-step weights within 1e-3 relative
+    tfref.train_step(ref, w, x, y, tfref.Adagrad(w.size, 1e-4))
+    net.apply("compat")
+    assert rel_err(net.get_params(), w) < 1e-3
+    # (the 1e-4 step is read back as a difference of fp32 weights ~0.1: ~1e-4 of it is rounding of the weights themselves)
+    assert rel_err(net.get_params() - flat, w - flat) < (1e-3 if math == 1 else 3e-2)
 
 
 def test_config_errors_and_defaults(ctx):
