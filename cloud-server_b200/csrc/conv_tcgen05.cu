@@ -11,9 +11,11 @@
 //   wgrad    dW[(i,j,c)][co]  = sum_(n,oy,ox) X[n,oy*s-p+i,ox*s-p+j,c] . dY[(n,oy,ox)][co]
 //            A = gathered rows placed as k-rows of an MN-major tile, B = dY by TMA (MN-major);
 //            the reduction runs over all output positions: deterministic split-K through a workspace
-// Warps 2-5 (128 threads) gather: each thread owns ONE 128-byte row of the A tile per k block, loads it
-// with 8 x LDG.128 (the next block's row is prefetched into registers), rounds it to TF32 (hi, and lo
-// for 3xTF32) and stores it into the swizzled UMMA layout; the same warps round the TMA-loaded B tile.
+// Warps 2-9 (256 threads) gather: two threads share ONE 128-byte row of the A tile per k block (4 x LDG.128
+// each, a register ring keeps the rows of the next two k blocks in flight), and store it into the swizzled UMMA
+// layout.  3xTF32 (forward): the row is split into rounded hi + lo parts, and the same warps split the TMA-loaded
+// B tile from a raw ring into the operand stage.  1x (gradients): rows are stored as loaded and the MMA reads B
+// straight from the TMA ring -- kind::tf32 truncates the operands itself.
 #include "nc_internal.h"
 #include "tc_gemm.h"
 #include "tc_common.cuh"
