@@ -109,7 +109,8 @@ __device__ __forceinline__ void finish_picture(const PredHdr& hdr, const unsigne
 // dp2a (16-bit coefficient pairs x pixel bytes): 8 dp2a + 3 prmt per 4 pixels.
 // ---------------------------------------------------------------------------------------------
 constexpr int kStageRows = 8;
-constexpr int kBlockRows = 16;    // gray block consumed by one horizontal pass (2 stages)
+constexpr int kBlockRows = 16;    // gray block consumed by one horizontal pass
+constexpr int kSPB = kBlockRows / kStageRows;   // raw stages per gray block
 
 __device__ __forceinline__ unsigned dp2a_lo(unsigned coef16x2, unsigned px, unsigned c) {
     unsigned d;
@@ -206,7 +207,7 @@ predict_chain_tma_kernel(const uint8_t* __restrict__ src, long long img_stride, 
         mbar_wait(bar0 + 8u * (s & 1), (unsigned)((s >> 1) & 1));
         // ---------------- phase 1: staged bytes -> rgb2l -> gray block rows (s&1)*8 ..
         const unsigned char* rbuf = raw + (size_t)(s & 1) * stage_bytes;
-        unsigned* gdst = s_gbuf + (size_t)((s & 1) * kStageRows) * wq;
+        unsigned* gdst = s_gbuf + (size_t)((s % kSPB) * kStageRows) * wq;
         const unsigned items = (unsigned)rows * ipr;                      // ipr = 16-pixel items per row
         for (unsigned it = tid; it < items; it += kThreads) {
             const unsigned rl = ipr_magic ? __umulhi(it, ipr_magic) : it;
@@ -227,9 +228,9 @@ predict_chain_tma_kernel(const uint8_t* __restrict__ src, long long img_stride, 
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic reads before async writes
             issue(s + 2);
         }
-        if ((s & 1) || s == nstages - 1) {
+        if ((s % kSPB) == kSPB - 1 || s == nstages - 1) {
             // ---------------- phase 2: horizontal pass over the 16-row gray block
-            const int b0 = (s & ~1) * kStageRows;                 // first picture row of this block
+            const int b0 = (s / kSPB) * kBlockRows;               // first picture row of this block
             const int brow = min(kBlockRows, h - b0);
             const unsigned* ra = ra0;
             const unsigned* rb = ra0 + wq;
@@ -494,7 +495,7 @@ extern "C" int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h
     if (c == 3 && (w % 16) == 0 && (reinterpret_cast<uintptr_t>(src) % 16) == 0 && (img_stride % 16) == 0 && h >= 16 &&
         !getenv("NC_PREDICT_NO_TMA")) {
         const int wq2 = w / 4 + 2;                 // even, = 2 mod 4: 8-byte stores, row pairs on distinct banks
-        const size_t stage = (size_t)8 * w * 3;
+        const size_t stage = (size_t)kStageRows * w * 3;
         const size_t smem2 = 2 * stage + (size_t)tabs.hdr.total_groups * 16 + (size_t)16 * wq2 * 4 + ((size_t)h * kOut + 15) / 16 * 16;
         if (smem2 <= 220 * 1024) {
             const unsigned A01 = (unsigned)c0 | ((unsigned)c1 << 16), A2_ = (unsigned)c2, A_0 = (unsigned)c0 << 16,
