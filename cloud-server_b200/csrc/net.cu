@@ -562,8 +562,17 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
             rc = tc_conv_try(net, 0, L, n, in, W, out, Bp, st, &done);
             if (rc != NC_OK) return rc;
             (void)training;
+            if (!done && L.ic <= 4 && K <= 32) {                       // first layer: tile kernel, lane = output channel
+                const long long ntiles = ((long long)M + 63) / 64;
+                const int blocks = (int)(ntiles < (long long)sms * 8 ? ntiles : (long long)sms * 8);
+                for (int ob = 0; ob < (N + 31) / 32; ++ob) {
+                    conv_smallc_fwd_tile_kernel<<<blocks, 256, 0, st>>>(in, W, Bp, out, geom(L), M, ob);
+                    NET_LAUNCH(net);
+                }
+                done = true;
+            }
             const size_t smallc_smem = (size_t)K * ((N + 31) / 32 * 32) * sizeof(float);
-            if (!done && L.ic <= 4 && smallc_smem <= 48 * 1024) {     // first layer: direct convolution
+            if (!done && L.ic <= 4 && smallc_smem <= 48 * 1024) {     // few channels, larger filters: direct convolution
                 const long long total = (long long)M * ((N + 31) / 32);
                 conv_smallc_fwd_kernel<<<grid_for(total, sms), 256, smallc_smem, st>>>(in, W, Bp, out, geom(L), M);
                 NET_LAUNCH(net);
@@ -694,6 +703,27 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             rc = tc_conv_try(net, 2, L, n, in, d, dW, nullptr, st, &done);
             if (rc != NC_OK) return rc;
             bool bias_done = false;
+            if (!done && L.ic <= 4 && K <= 32) {
+                // first layer: weight AND bias gradient in one pass over dY (tile kernel), CTA partials summed in fixed order
+                const long long ntiles = ((long long)M + 63) / 64;
+                const int blocks = (int)(ntiles < (long long)sms * 4 ? ntiles : (long long)sms * 4);
+                rc = reserve_ws(net, (size_t)blocks * (K + 1) * N * sizeof(float));
+                if (rc != NC_OK) return rc;
+                float* pw = net->ws;
+                float* pb = net->ws + (size_t)blocks * K * N;
+                for (int ob = 0; ob < (N + 31) / 32; ++ob) {
+                    conv_smallc_wgrad_tile_kernel<<<blocks, 256, 0, st>>>(in, d, pw, pb, geom(L), M, ob);
+                    NET_LAUNCH(net);
+                }
+                reduce_partials_warp_kernel<<<(K * N + 7) / 8, 256, 0, st>>>(dW, pw, blocks, (long long)K * N);
+                NET_LAUNCH(net);
+                if (dB) {
+                    reduce_partials_warp_kernel<<<(N + 7) / 8, 256, 0, st>>>(dB, pb, blocks, N);
+                    NET_LAUNCH(net);
+                }
+                done = true;
+                bias_done = true;
+            }
             if (!done && smallc_tc_ok(net, L, W, d)) {
                 // first layer: dW[K][N] = col^T[K][M] . dY[M][N] on the tensor cores over an explicit im2col
                 int Kp;

@@ -153,6 +153,20 @@ __global__ void reduce_partials_kernel(float* __restrict__ dst, const float* __r
     }
 }
 
+// many splits, few outputs: one warp per output, lanes stride over the splits, fixed shuffle tree (deterministic)
+__global__ void reduce_partials_warp_kernel(float* __restrict__ dst, const float* __restrict__ ws, int splits, long long count) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long i = warp; i < count; i += nwarps) {
+        float s = 0.0f;
+        for (int k = lane; k < splits; k += 32) s += ws[(long long)k * count + i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) dst[i] = s;
+    }
+}
+
 // column sums of Y[rows][cols] (bias gradients): partial[split][col]
 __global__ void colsum_partial_kernel(const float* __restrict__ y, int rows, int cols, int rows_per_split, float* __restrict__ ws) {
     const int col = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -216,6 +230,137 @@ conv_smallc_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
 #pragma unroll
         for (int o = 0; o < 32; ++o)
             if (ob * 32 + o < g.oc) py[o] = acc[o] + (bias ? __ldg(bias + ob * 32 + o) : 0.0f);
+    }
+}
+
+// ---- tile versions for T = fh*fw*Cin <= 32 (the usual first layer: 5x5x1, 3x3x3): a CTA builds the im2col of 64
+// output positions in shared memory once (bounds handled there), then lane = output channel:
+//   forward: the 32 weights of the lane's channel sit in registers, each warp turns 8 positions into 8 coalesced
+//            128-byte output rows with two broadcast LDS.128 + 8 FMA per tap;
+//   wgrad:   the lane keeps dW[t][channel] for all taps in registers, 8 broadcast LDS.128 + 32 FMA per position,
+//            bias gradient for free; warps are summed in shared memory, CTAs in a fixed-order reduction.
+struct SmallcTile {
+    int pn[64], py[64], px[64];     // decoded output positions of the tile
+    int tdy[32], tdx[32], tc[32];   // decoded taps
+};
+
+__device__ __forceinline__ void smallc_decode(SmallcTile& S, const ConvGeom& g, long long m0, long long M, int T) {
+    const int tid = threadIdx.x;
+    if (tid < 64) {
+        const long long m = m0 + tid;
+        if (m < M) {
+            S.px[tid] = (int)(m % g.ow); const long long q = m / g.ow;
+            S.py[tid] = (int)(q % g.oh); S.pn[tid] = (int)(q / g.oh);
+        } else { S.pn[tid] = -1; S.py[tid] = 0; S.px[tid] = 0; }
+    } else if (tid < 96) {
+        const int t = tid - 64;
+        const int tt = t < T ? t : 0;
+        const int c = tt % g.ic, ij = tt / g.ic;
+        S.tdy[t] = ij / g.fw; S.tdx[t] = ij % g.fw; S.tc[t] = c;
+    }
+}
+__device__ __forceinline__ float smallc_fetch(const SmallcTile& S, const ConvGeom& g, const float* __restrict__ x, int p, int t, int T) {
+    if (t >= T || S.pn[p] < 0) return 0.0f;
+    const int yy = S.py[p] * g.sh - g.pt + S.tdy[t], xx = S.px[p] * g.sw - g.pl + S.tdx[t];
+    if (yy < 0 || yy >= g.ih || xx < 0 || xx >= g.iw) return 0.0f;
+    return __ldg(x + (((long long)S.pn[p] * g.ih + yy) * g.iw + xx) * g.ic + S.tc[t]);
+}
+
+__global__ void __launch_bounds__(256)
+conv_smallc_fwd_tile_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                            float* __restrict__ y, ConvGeom g, long long M, int ob) {
+    __shared__ SmallcTile S;
+    __shared__ __align__(16) float colT[32][64];        // [tap][position]
+    const int T = g.fh * g.fw * g.ic;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    float wreg[32];
+#pragma unroll
+    for (int t = 0; t < 32; ++t) wreg[t] = (t < T && co < g.oc) ? __ldg(w + (long long)t * g.oc + co) : 0.0f;
+    const float bv = (bias && co < g.oc) ? __ldg(bias + co) : 0.0f;
+    const long long ntiles = (M + 63) / 64;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long m0 = tile * 64;
+        __syncthreads();                                  // previous tile fully consumed
+        smallc_decode(S, g, m0, M, T);
+        __syncthreads();
+        for (int e = threadIdx.x; e < 32 * 64; e += 256) colT[e >> 6][e & 63] = smallc_fetch(S, g, x, e & 63, e >> 6, T);
+        __syncthreads();
+        float acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = 0.0f;
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+            if (t < T) {
+                const float4 a = *reinterpret_cast<const float4*>(&colT[t][warp * 8]);
+                const float4 b = *reinterpret_cast<const float4*>(&colT[t][warp * 8 + 4]);
+                acc[0] = fmaf(a.x, wreg[t], acc[0]); acc[1] = fmaf(a.y, wreg[t], acc[1]);
+                acc[2] = fmaf(a.z, wreg[t], acc[2]); acc[3] = fmaf(a.w, wreg[t], acc[3]);
+                acc[4] = fmaf(b.x, wreg[t], acc[4]); acc[5] = fmaf(b.y, wreg[t], acc[5]);
+                acc[6] = fmaf(b.z, wreg[t], acc[6]); acc[7] = fmaf(b.w, wreg[t], acc[7]);
+            }
+        }
+        if (co < g.oc) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const long long m = m0 + warp * 8 + k;
+                if (m < M) y[m * g.oc + co] = acc[k] + bv;
+            }
+        }
+    }
+}
+
+// partial_w[block][T*oc] and partial_b[block][oc] hold this CTA's sums for output-channel block `ob`
+__global__ void __launch_bounds__(256)
+conv_smallc_wgrad_tile_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partial_w,
+                              float* __restrict__ partial_b, ConvGeom g, long long M, int ob) {
+    __shared__ SmallcTile S;
+    __shared__ __align__(16) float col[64][32];         // [position][tap]
+    __shared__ float red[8][33];
+    const int T = g.fh * g.fw * g.ic;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    float acc[32];
+#pragma unroll
+    for (int t = 0; t < 32; ++t) acc[t] = 0.0f;
+    float accb = 0.0f;
+    const long long ntiles = (M + 63) / 64;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const long long m0 = tile * 64;
+        __syncthreads();
+        smallc_decode(S, g, m0, M, T);
+        __syncthreads();
+        for (int e = threadIdx.x; e < 64 * 32; e += 256) col[e >> 5][e & 31] = smallc_fetch(S, g, x, e >> 5, e & 31, T);
+        __syncthreads();
+#pragma unroll 2
+        for (int k = 0; k < 8; ++k) {
+            const int p = warp * 8 + k;
+            const long long m = m0 + p;
+            const float gv = (m < M && co < g.oc) ? __ldg(dy + m * g.oc + co) : 0.0f;
+            accb += gv;
+#pragma unroll
+            for (int t4 = 0; t4 < 8; ++t4) {
+                const float4 v = *reinterpret_cast<const float4*>(&col[p][t4 * 4]);
+                acc[t4 * 4 + 0] = fmaf(v.x, gv, acc[t4 * 4 + 0]); acc[t4 * 4 + 1] = fmaf(v.y, gv, acc[t4 * 4 + 1]);
+                acc[t4 * 4 + 2] = fmaf(v.z, gv, acc[t4 * 4 + 2]); acc[t4 * 4 + 3] = fmaf(v.w, gv, acc[t4 * 4 + 3]);
+            }
+        }
+    }
+    // warps -> CTA partial, fixed order
+#pragma unroll
+    for (int t = 0; t <= 32; ++t) {
+        if (t < T || t == 32) {
+            __syncthreads();
+            red[warp][lane] = t < 32 ? acc[t < 32 ? t : 0] : accb;
+            __syncthreads();
+            if (warp == 0 && co < g.oc) {
+                float sum = 0.0f;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) sum += red[k][lane];
+                if (t < 32) partial_w[(size_t)blockIdx.x * T * g.oc + (size_t)t * g.oc + co] = sum;
+                else partial_b[(size_t)blockIdx.x * g.oc + co] = sum;
+            }
+        }
     }
 }
 
