@@ -593,7 +593,11 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
         }
         case L_POOL: {
             const long long total = (long long)n * L.out_size;
-            maxpool_fwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(in, out, net->aux + L.aux_off * net->cap, pgeom(L), total, pending_relu ? 1 : 0);
+            uint8_t* argp = net->aux + L.aux_off * net->cap;
+            const bool v4 = (L.ic % 4) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0 &&
+                            (reinterpret_cast<uintptr_t>(argp) & 3) == 0;
+            if (v4) maxpool_fwd_vec4_kernel<<<grid_for(total / 4, sms), 256, 0, st>>>(in, out, argp, pgeom(L), total / 4, pending_relu ? 1 : 0);
+            else maxpool_fwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(in, out, argp, pgeom(L), total, pending_relu ? 1 : 0);
             NET_LAUNCH(net);
             pending_relu = false;
             break;
@@ -771,8 +775,11 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                 const bool tiled = L.fh == L.sh && L.fw == L.sw && L.pt == 0 && L.pl == 0 && L.oh * L.sh >= L.ih && L.ow * L.sw >= L.iw;
                 const bool fused = tiled && li > 0 && net->layers[li - 1].relu_into_pool;
                 if (fused) skip_fused_relu = true;      // this launch already yields the gradient w.r.t. the pre-activation
-                if (tiled) maxpool_bwd_tiled_kernel<<<grid_for(total_out, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_out,
-                                                                                          fused ? out : nullptr);
+                uint8_t* argp = net->aux + L.aux_off * net->cap;
+                const bool v4 = tiled && (L.ic % 4) == 0 && (reinterpret_cast<uintptr_t>(argp) & 3) == 0 &&
+                                ((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(dn) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+                if (v4) maxpool_bwd_tiled_vec4_kernel<<<grid_for(total_out / 4, sms), 256, 0, st>>>(d, argp, dn, pgeom(L), total_out / 4, fused ? out : nullptr);
+                else if (tiled) maxpool_bwd_tiled_kernel<<<grid_for(total_out, sms), 256, 0, st>>>(d, argp, dn, pgeom(L), total_out, fused ? out : nullptr);
                 else maxpool_bwd_kernel<<<grid_for(total_in, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_in);
                 NET_LAUNCH(net);
             }

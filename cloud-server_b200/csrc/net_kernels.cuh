@@ -475,6 +475,68 @@ __global__ void maxpool_fwd_kernel(const float* __restrict__ x, float* __restric
     }
 }
 
+// four channels per thread (c % 4 == 0, 16-byte aligned tensors): one index decode and 128-bit accesses per window tap
+__global__ void maxpool_fwd_vec4_kernel(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ arg,
+                                        PoolGeom g, long long total4, int relu) {
+    const int c4n = g.c >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total4; idx += stride) {
+        const int c4 = idx % c4n; long long t = idx / c4n;
+        const int ox = t % g.ow; t /= g.ow;
+        const int oy = t % g.oh; const int n = (int)(t / g.oh);
+        float b0 = -INFINITY, b1 = -INFINITY, b2 = -INFINITY, b3 = -INFINITY;
+        int a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        for (int i = 0; i < g.kh; ++i) {
+            const int yy = oy * g.sh - g.pt + i;
+            if (yy < 0 || yy >= g.ih) continue;
+            for (int j = 0; j < g.kw; ++j) {
+                const int xx = ox * g.sw - g.pl + j;
+                if (xx < 0 || xx >= g.iw) continue;
+                float4 v = __ldg(reinterpret_cast<const float4*>(x + (((long long)n * g.ih + yy) * g.iw + xx) * g.c) + c4);
+                if (relu) { v.x = fmaxf(v.x, 0.0f); v.y = fmaxf(v.y, 0.0f); v.z = fmaxf(v.z, 0.0f); v.w = fmaxf(v.w, 0.0f); }
+                const int k = i * g.kw + j;
+                if (v.x > b0) { b0 = v.x; a0 = k; }
+                if (v.y > b1) { b1 = v.y; a1 = k; }
+                if (v.z > b2) { b2 = v.z; a2 = k; }
+                if (v.w > b3) { b3 = v.w; a3 = k; }
+            }
+        }
+        reinterpret_cast<float4*>(y)[idx] = make_float4(b0, b1, b2, b3);
+        reinterpret_cast<uchar4*>(arg)[idx] = make_uchar4((unsigned char)a0, (unsigned char)a1, (unsigned char)a2, (unsigned char)a3);
+    }
+}
+
+__global__ void maxpool_bwd_tiled_vec4_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ arg, float* __restrict__ dx,
+                                              PoolGeom g, long long total4, const float* __restrict__ pooled) {
+    const int c4n = g.c >> 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total4; idx += stride) {
+        const int c4 = idx % c4n; long long t = idx / c4n;
+        const int ox = t % g.ow; t /= g.ow;
+        const int oy = t % g.oh; const int n = (int)(t / g.oh);
+        float4 gv = __ldg(reinterpret_cast<const float4*>(dy) + idx);
+        if (pooled) {
+            const float4 p = __ldg(reinterpret_cast<const float4*>(pooled) + idx);
+            if (!(p.x > 0.0f)) gv.x = 0.0f;
+            if (!(p.y > 0.0f)) gv.y = 0.0f;
+            if (!(p.z > 0.0f)) gv.z = 0.0f;
+            if (!(p.w > 0.0f)) gv.w = 0.0f;
+        }
+        const uchar4 a = reinterpret_cast<const uchar4*>(arg)[idx];
+        for (int i = 0; i < g.kh; ++i) {
+            const int yy = oy * g.sh + i;
+            if (yy >= g.ih) continue;
+            for (int j = 0; j < g.kw; ++j) {
+                const int xx = ox * g.sw + j;
+                if (xx >= g.iw) continue;
+                const int k = i * g.kw + j;
+                reinterpret_cast<float4*>(dx + (((long long)n * g.ih + yy) * g.iw + xx) * g.c)[c4] =
+                    make_float4(a.x == k ? gv.x : 0.0f, a.y == k ? gv.y : 0.0f, a.z == k ? gv.z : 0.0f, a.w == k ? gv.w : 0.0f);
+            }
+        }
+    }
+}
+
 // gather form (deterministic, handles overlapping windows): each input element sums the dy of the
 // windows whose argmax it is
 __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ arg, float* __restrict__ dx,
