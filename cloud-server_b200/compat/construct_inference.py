@@ -50,7 +50,7 @@ def main(argv=None):
     im = np.asarray(Image.open(FLAGS.filename))                   # :312 (convert('L') happens on the GPU)
     if im.ndim == 3 and im.shape[2] == 4:
         im = im[:, :, :3]
-    src = torch.from_numpy(np.ascontiguousarray(im)[None]).to(ctx.tdev)
+    src = torch.from_numpy(np.array(im)[None]).to(ctx.tdev)
     arr, status, small = ctx.predict_chain(src, channel_order="RGB", compat=not FLAGS.intended, want_small20=True)
     print(tuple(small[0].shape))                                  # print(arr.shape), :317
     if int(status[0].item()) != 0:

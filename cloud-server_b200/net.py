@@ -152,10 +152,16 @@ class DataParallel:
     (construct_distribute.py:344-357, cmd.py:63-69); the parity target is the single-device step at
     the global batch."""
 
-    def __init__(self, net, group=None):
+    def __init__(self, net, group=None, allow_local_norm=False):
         import torch.distributed as dist
         self.net, self.dist, self.group = net, dist, group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        cfg = getattr(net, "config", None)
+        if self.world > 1 and cfg and '"norm"' in cfg and not allow_local_norm:
+            # normalize() uses batch statistics (construct_distribute.py:155-165): per-rank moments would differ from
+            # the single-device step at the global batch; the cross-rank moment all-reduce is not built yet
+            raise NotImplementedError("data parallel training of a net with 'norm' layers would use per-rank batch "
+                                      "statistics; pass allow_local_norm=True to accept that")
         if self.world > 1:
             dist.broadcast(net.params, src=0, group=group)     # identical initial weights
 

@@ -54,7 +54,7 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".h", ".cuh")):
                 src = open(os.path.join(dp, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
-                assert "import cv2" not in src or f in ("preprocess.py", "imageio.py"), f
+                assert "import cv2" not in src or f in ("preprocess.py", "preprocess_view.py", "imageio.py"), f   # host JPEG codec only
 
 
 @pytest.mark.parametrize("src", [28, 29, 37, 56, 100, 255, 480, 640, 768, 1024, 1080, 1920, 4001])

@@ -190,3 +190,45 @@ def test_device_dataset_matches_reference_dataset(ctx):
         assert np.array_equal(xb.cpu().numpy(), xr), step
         assert np.array_equal(yb.cpu().numpy(), yr), step
     assert dev_ds.epochs_completed == 2
+
+
+@pytest.mark.gpu
+def test_batched_view_adapter_equals_per_file_loop(ctx, tmp_path):
+    """compat.preprocess_view.execute (one batch per step) leaves the same files and tag.json as the reference's
+    per-file loop (resize(path); op(path, overlap, v1, v2) for every tag entry, views.py:118-132)."""
+    import shutil
+    import cv2
+    from cloud_server_b200.compat import preprocess_view as pv
+    from cloud_server_b200.compat.apps.preprocess import preprocess as pp
+    pics = golden("pics.npz")
+    rng = np.random.default_rng(4)
+    for d in ("a", "b"):
+        os.mkdir(tmp_path / d)
+    tags = {}
+    for i in range(6):
+        name = "p%d.jpg" % i
+        img = rng.integers(0, 256, (40 + 8 * (i % 2), 60, 3), np.uint8) if i < 4 else np.repeat(pics["gray_cv"][i][..., None], 3, 2)
+        cv2.imwrite(str(tmp_path / "a" / name), img)
+        tags[name] = str(i)
+    for name in tags:
+        shutil.copy(tmp_path / "a" / name, tmp_path / "b" / name)
+    for d in ("a", "b"):
+        json.dump(tags, open(tmp_path / ("tag_%s.json" % d), "w"))
+    for opname, fname, overlap, v1, v2 in [("均值滤波", "mean_filter", False, 3, None), ("腐蚀", "erode", True, 3, None)]:
+        pv.execute({"operationName": opname, "overlap": overlap, "value1": v1, "value2": v2}, str(tmp_path / "a") + "/",
+                   str(tmp_path / "tag_a.json"), ctx)
+        tb = json.load(open(tmp_path / "tag_b.json"))                     # the reference's loop, with the per-file shim
+        tb_edit = tb.copy()
+        for rel, tag in tb.items():
+            p = str(tmp_path / "b" / rel)
+            pp.resize(p)
+            getattr(pp, fname)(p, overlap, v1, v2)
+            if overlap:
+                parts = os.path.splitext(rel)
+                tb_edit[parts[0] + "_copy" + parts[1]] = tag
+        json.dump(tb_edit, open(tmp_path / "tag_b.json", "w"))
+    assert json.load(open(tmp_path / "tag_a.json")) == json.load(open(tmp_path / "tag_b.json"))
+    files = sorted(os.listdir(tmp_path / "a"))
+    assert files == sorted(os.listdir(tmp_path / "b")) and len(files) > 6
+    for f in files:
+        assert open(tmp_path / "a" / f, "rb").read() == open(tmp_path / "b" / f, "rb").read(), f
