@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <string.h>
 #include <string>
 #include <vector>
 #include <map>
@@ -35,6 +36,14 @@ struct nc_ctx {
 int nc_set_error(nc_ctx* ctx, int code, const char* fmt, ...);
 int nc_ws_reserve(nc_ctx* ctx, size_t bytes);       // ctx->ws valid for >= bytes afterwards
 int nc_pinned_reserve(nc_ctx* ctx, size_t bytes);
+
+// ---- NCCL, bound with dlopen at run time (nccl_glue.cpp) ------------------------------------
+int nc_nccl_load(nc_ctx* ctx, const char* path);    // idempotent; NULL / "" = "libnccl.so.2" on the loader path
+int nc_nccl_version();
+int nc_nccl_unique_id_impl(nc_ctx* ctx, unsigned char out[128]);
+int nc_nccl_comm_init(nc_ctx* ctx, void** comm, const unsigned char id[128], int rank, int world);
+void nc_nccl_comm_destroy(void* comm);
+int nc_nccl_allreduce_sum_f32(nc_ctx* ctx, void* comm, float* buf, size_t count, cudaStream_t st);
 
 #define NC_CUDA(ctx, call)                                                                     \
     do {                                                                                       \

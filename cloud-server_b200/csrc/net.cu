@@ -142,6 +142,9 @@ struct nc_net {
     float *dbuf0 = nullptr, *dbuf1 = nullptr;
     float* ws = nullptr; size_t ws_bytes = 0;              // split-K partial sums (scratch)
     float* col = nullptr; size_t col_bytes = 0;            // im2col of the first (few-channel) conv layer, tensor path
+    // data parallel (nc_net_attach_nccl): communicator + 2*max(norm channels) floats for the cross-rank moments
+    void* comm = nullptr; int rank = 0, world = 1;
+    float* dp_buf = nullptr;
     std::string err;
 };
 
@@ -321,6 +324,8 @@ static double trunc_normal(uint64_t& s) {
 
 static void free_net(nc_net* net) {
     if (!net) return;
+    if (net->comm) { nc_nccl_comm_destroy(net->comm); net->comm = nullptr; }
+    cudaFree(net->dp_buf);
     cudaFree(net->params); cudaFree(net->grads); cudaFree(net->st_adagrad); cudaFree(net->st_adam);
     cudaFree(net->act); cudaFree(net->aux); cudaFree(net->stat); cudaFree(net->dbuf0); cudaFree(net->dbuf1); cudaFree(net->ws); cudaFree(net->col);
     delete net;
@@ -610,6 +615,23 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
         }
         case L_NORM: {
             const long long rows = (long long)n * (L.out_size / L.oc);
+            if (net->world > 1 && training) {
+                // moments over the GLOBAL batch: two small all-reduces keep the two-pass mean / variance arithmetic
+                float* sum = net->dp_buf; float* sq = net->dp_buf + L.oc;
+                const float inv_total = 1.0f / (float)(rows * net->world);
+                norm_sum_kernel<<<L.oc, 256, 0, st>>>(in, rows, L.oc, sum);
+                NET_LAUNCH(net);
+                int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, sum, (size_t)L.oc, st);
+                if (rc != NC_OK) return rc;
+                norm_sqdev_kernel<<<L.oc, 256, 0, st>>>(in, rows, L.oc, sum, inv_total, sq);
+                NET_LAUNCH(net);
+                rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, sq, (size_t)L.oc, st);
+                if (rc != NC_OK) return rc;
+                norm_apply_kernel<<<L.oc, 256, 0, st>>>(in, out, net->act + L.aux_off * net->cap, net->stat + L.stat_off, W, Bp, rows, L.oc,
+                                                         L.eps, sum, sq, inv_total);
+                NET_LAUNCH(net);
+                break;
+            }
             norm_fwd_kernel<<<L.oc, 256, 0, st>>>(in, out, net->act + L.aux_off * net->cap, net->stat + L.stat_off, W, Bp, rows, L.oc, L.eps);
             NET_LAUNCH(net);
             break;
@@ -793,6 +815,17 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             break;
         case L_NORM: {
             const long long rows = (long long)n * (L.out_size / L.oc);
+            if (net->world > 1) {
+                float* sums = net->dp_buf;
+                norm_bwd_sums_kernel<<<L.oc, 256, 0, st>>>(d, net->act + L.aux_off * net->cap, rows, L.oc, sums, dW, dB);
+                NET_LAUNCH(net);
+                const int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, sums, (size_t)2 * L.oc, st);
+                if (rc != NC_OK) return rc;
+                norm_bwd_apply_kernel<<<L.oc, 256, 0, st>>>(d, net->act + L.aux_off * net->cap, net->stat + L.stat_off, W, dn, rows, L.oc, sums,
+                                                             (float)(rows * net->world));
+                NET_LAUNCH(net);
+                break;
+            }
             norm_bwd_kernel<<<L.oc, 256, 0, st>>>(d, net->act + L.aux_off * net->cap, net->stat + L.stat_off, W, dn, dW, dB, rows, L.oc);
             NET_LAUNCH(net);
             break;
@@ -843,8 +876,11 @@ extern "C" int nc_net_apply(nc_net* net, int opt, float lr, void* stream) {
 
 extern "C" int nc_net_train_step(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name, int opt, float lr,
                                  float* loss_out, int32_t* correct_out, void* stream) {
-    int rc = nc_net_backward(net, x, y_onehot, n, loss_name, 1.0f, loss_out, correct_out, stream);
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    // attached to a communicator: this rank's slice of the global batch; the loss is a batch mean, so scale by 1/world and sum
+    int rc = nc_net_backward(net, x, y_onehot, n, loss_name, 1.0f / (float)net->world, loss_out, correct_out, stream);
     if (rc != NC_OK) return rc;
+    if (net->world > 1) { rc = nc_net_allreduce_grads(net, stream); if (rc != NC_OK) return rc; }
     return nc_net_apply(net, opt, lr, stream);
 }
 
@@ -874,4 +910,52 @@ extern "C" int nc_net_set_state(nc_net* net, int opt, const float* host_state, i
     }
     net->global_step = global_step;
     return NC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// data parallel over NCCL (one process per GPU).  Replaces the reference's ps/worker gRPC exchange
+// (construct_distribute.py:344-357) with a synchronous sum of the flat gradient buffer, and makes
+// normalize() (:155-165) see the moments of the GLOBAL batch.
+// ------------------------------------------------------------------------------------------------
+extern "C" int nc_nccl_unique_id(nc_ctx* ctx, const char* libnccl_path, unsigned char out_id[128]) {
+    if (!ctx || !out_id) return nc_set_error(ctx, NC_EINVAL, "NULL argument");
+    const int rc = nc_nccl_load(ctx, libnccl_path);
+    if (rc != NC_OK) return rc;
+    return nc_nccl_unique_id_impl(ctx, out_id);
+}
+
+extern "C" int nc_net_attach_nccl(nc_net* net, const char* libnccl_path, const unsigned char id[128], int rank, int world) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (!id || world < 1 || rank < 0 || rank >= world) return net_err(net, NC_EINVAL, "bad rank %d / world %d", rank, world);
+    if (net->comm) return net_err(net, NC_EINVAL, "net is already attached to a communicator");
+    int rc = nc_nccl_load(net->ctx, libnccl_path);
+    if (rc != NC_OK) return rc;
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    int maxc = 0;
+    for (auto& L : net->layers) if (L.kind == L_NORM && L.oc > maxc) maxc = L.oc;
+    if (maxc && !net->dp_buf) NET_CUDA(net, cudaMalloc(&net->dp_buf, (size_t)2 * maxc * sizeof(float)));
+    rc = nc_nccl_comm_init(net->ctx, &net->comm, id, rank, world);
+    if (rc != NC_OK) return rc;
+    net->rank = rank; net->world = world;
+    return NC_OK;
+}
+
+extern "C" int nc_net_detach_nccl(nc_net* net) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (net->comm) {
+        cudaSetDevice(net->ctx->device);
+        cudaDeviceSynchronize();
+        nc_nccl_comm_destroy(net->comm);
+        net->comm = nullptr;
+    }
+    net->rank = 0; net->world = 1;
+    return NC_OK;
+}
+
+extern "C" int nc_net_allreduce_grads(nc_net* net, void* stream) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (!net->comm) return net_err(net, NC_EINVAL, "net is not attached to a communicator (nc_net_attach_nccl)");
+    if (net->world == 1) return NC_OK;
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    return nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads, (size_t)net->nparams, (cudaStream_t)stream);
 }

@@ -679,6 +679,71 @@ norm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, co
     }
 }
 
+// ---- data-parallel variants: the batch statistics span all ranks (construct_distribute.py:155-165 at the GLOBAL
+// batch), so each reduction is split into a per-rank partial sum, an all-reduce, and the apply pass
+__global__ void __launch_bounds__(256)
+norm_sum_kernel(const float* __restrict__ x, long long rows, int C, float* __restrict__ out) {
+    __shared__ float sh[8];
+    const int c = blockIdx.x;
+    float s = 0.0f;
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) s += __ldg(x + r * C + c);
+    const float t = block_sum(s, sh);
+    if (threadIdx.x == 0) out[c] = t;
+}
+__global__ void __launch_bounds__(256)
+norm_sqdev_kernel(const float* __restrict__ x, long long rows, int C, const float* __restrict__ sum, float inv_total,
+                  float* __restrict__ out) {
+    __shared__ float sh[8];
+    const int c = blockIdx.x;
+    const float mean = __ldg(sum + c) * inv_total;
+    float q = 0.0f;
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) { const float d = __ldg(x + r * C + c) - mean; q += d * d; }
+    const float t = block_sum(q, sh);
+    if (threadIdx.x == 0) out[c] = t;
+}
+__global__ void __launch_bounds__(256)
+norm_apply_kernel(const float* __restrict__ x, float* __restrict__ y, float* __restrict__ xhat, float* __restrict__ inv_out,
+                  const float* __restrict__ scale, const float* __restrict__ offset, long long rows, int C, float eps,
+                  const float* __restrict__ sum, const float* __restrict__ sqdev, float inv_total) {
+    const int c = blockIdx.x;
+    const float mean = __ldg(sum + c) * inv_total, var = __ldg(sqdev + c) * inv_total;
+    const float inv = 1.0f / sqrtf(var + eps);
+    if (threadIdx.x == 0) inv_out[c] = inv;
+    const float sc = __ldg(scale + c), of = __ldg(offset + c);
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) {
+        const float h = (__ldg(x + r * C + c) - mean) * inv;
+        xhat[r * C + c] = h;
+        y[r * C + c] = h * sc + of;
+    }
+}
+// sums[0..C) = sum dy, sums[C..2C) = sum dy*xhat over this rank's rows; also the LOCAL dscale / doffset
+__global__ void __launch_bounds__(256)
+norm_bwd_sums_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, long long rows, int C, float* __restrict__ sums,
+                     float* __restrict__ dscale, float* __restrict__ doffset) {
+    __shared__ float sh[8];
+    const int c = blockIdx.x;
+    float s1 = 0.0f, s2 = 0.0f;
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) {
+        const float g = __ldg(dy + r * C + c);
+        s1 += g; s2 += g * __ldg(xhat + r * C + c);
+    }
+    const float a = block_sum(s1, sh);
+    const float b = block_sum(s2, sh);
+    if (threadIdx.x == 0) { sums[c] = a; sums[C + c] = b; doffset[c] = a; dscale[c] = b; }
+}
+__global__ void __launch_bounds__(256)
+norm_bwd_apply_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, const float* __restrict__ inv_in,
+                      const float* __restrict__ scale, float* __restrict__ dx, long long rows, int C, const float* __restrict__ sums,
+                      float total_rows) {
+    const int c = blockIdx.x;
+    const float sc = __ldg(scale + c), inv = __ldg(inv_in + c), m = total_rows;
+    const float sum_dy = __ldg(sums + c), sum_dyx = __ldg(sums + C + c);
+    for (long long r = threadIdx.x; r < rows; r += blockDim.x) {
+        const float g = __ldg(dy + r * C + c) * sc;
+        dx[r * C + c] = inv / m * (m * g - sum_dy * sc - __ldg(xhat + r * C + c) * sum_dyx * sc);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // loss (loss_function, :285-298) fused with its gradient and the accuracy count (:381-382).
 // One CTA; rows strided over threads; deterministic in-block reduction.

@@ -138,10 +138,65 @@ class Net:
         _lib.check(self.ctx.handle, _lib.lib().nc_net_apply(self.handle, oid, C.c_float(lr), self.ctx._stream()))
 
     def train_step(self, x, y, loss_name="entropy", opt="compat", lr=1e-4):
-        """One sess.run(train_op) (construct_distribute.py:413)."""
-        r = self.backward(x, y, loss_name, 1.0)
+        """One sess.run(train_op) (construct_distribute.py:413).  On a net attached to a communicator
+        (attach_nccl) x, y are this rank's slice of the global batch and every rank ends with the
+        weights of the global-batch step; the returned loss / hit count stay per-rank."""
+        r = self.backward(x, y, loss_name, 1.0 / self.world)
+        if self.world > 1:
+            self.allreduce_grads()
         self.apply(opt, lr)
         return r
+
+    # ---- data parallel inside the library (nc_net_attach_nccl)
+    world = 1
+
+    def attach_nccl(self, unique_id, rank, world, libnccl_path=None):
+        """Collective: joins this net to an NCCL communicator of `world` processes (one per GPU).
+        `unique_id` is the 128 bytes rank 0 got from new_nccl_unique_id()."""
+        if len(unique_id) != 128:
+            raise ValueError("an NCCL unique id is 128 bytes")
+        buf = (C.c_ubyte * 128).from_buffer_copy(bytes(unique_id))
+        path = (libnccl_path or find_libnccl()).encode()
+        with torch.cuda.device(self.ctx.tdev):
+            _lib.check(self.ctx.handle, _lib.lib().nc_net_attach_nccl(self.handle, path, buf, int(rank), int(world)))
+        self.world = int(world)
+
+    def detach_nccl(self):
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_detach_nccl(self.handle))
+        self.world = 1
+
+    def allreduce_grads(self):
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_allreduce_grads(self.handle, self.ctx._stream()))
+
+
+def find_libnccl():
+    """Path of the NCCL this process should share with torch: the one already mapped if torch loaded it,
+    else the wheel's copy, else the loader's default."""
+    import os
+    try:
+        with open("/proc/self/maps") as f:
+            for line in f:
+                if "libnccl.so" in line:
+                    return line.split()[-1]
+    except OSError:
+        pass
+    try:
+        import nvidia.nccl as _n
+        for d in list(getattr(_n, "__path__", [])):
+            cand = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                return cand
+    except ImportError:
+        pass
+    return "libnccl.so.2"
+
+
+def new_nccl_unique_id(ctx=None, libnccl_path=None):
+    """128-byte NCCL unique id (call on rank 0, hand the bytes to every rank)."""
+    ctx = ctx or default_context()
+    buf = (C.c_ubyte * 128)()
+    _lib.check(ctx.handle, _lib.lib().nc_nccl_unique_id(ctx.handle, (libnccl_path or find_libnccl()).encode(), buf))
+    return bytes(buf)
 
 
 class DataParallel:
@@ -152,20 +207,34 @@ class DataParallel:
     (construct_distribute.py:344-357, cmd.py:63-69); the parity target is the single-device step at
     the global batch."""
 
-    def __init__(self, net, group=None, allow_local_norm=False):
+    def __init__(self, net, group=None, allow_local_norm=False, in_library=None):
+        """in_library: sum the gradients (and the batch-norm moments) with the library's own NCCL communicator
+        instead of torch.distributed.  Default: only when the net has 'norm' layers, which need it --
+        normalize() uses batch statistics (construct_distribute.py:155-165) and per-rank moments would differ
+        from the single-device step at the global batch.  allow_local_norm=True keeps per-rank moments."""
         import torch.distributed as dist
         self.net, self.dist, self.group = net, dist, group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         cfg = getattr(net, "config", None)
-        if self.world > 1 and cfg and '"norm"' in cfg and not allow_local_norm:
-            # normalize() uses batch statistics (construct_distribute.py:155-165): per-rank moments would differ from
-            # the single-device step at the global batch; the cross-rank moment all-reduce is not built yet
-            raise NotImplementedError("data parallel training of a net with 'norm' layers would use per-rank batch "
-                                      "statistics; pass allow_local_norm=True to accept that")
+        has_norm = bool(cfg and '"norm"' in cfg)
+        if in_library is None:
+            in_library = has_norm and not allow_local_norm
+        self.in_library = bool(in_library) and self.world > 1
         if self.world > 1:
             dist.broadcast(net.params, src=0, group=group)     # identical initial weights
+        if self.in_library:
+            if not hasattr(net, "attach_nccl"):
+                raise NotImplementedError("data parallel training of a net with 'norm' layers needs the library's "
+                                          "communicator (Net.attach_nccl); pass allow_local_norm=True for per-rank moments")
+            rank = dist.get_rank(group)
+            box = [new_nccl_unique_id(net.ctx) if rank == 0 else None]
+            src = dist.get_global_rank(group, 0) if group is not None else 0
+            dist.broadcast_object_list(box, src=src, group=group)
+            net.attach_nccl(box[0], rank, self.world)
 
     def train_step(self, x_local, y_local, loss_name="entropy", opt="compat", lr=1e-4):
+        if self.in_library:
+            return self.net.train_step(x_local, y_local, loss_name, opt, lr)
         loss, correct = self.net.backward(x_local, y_local, loss_name, 1.0 / self.world)
         if self.world > 1:
             self.dist.all_reduce(self.net.grads, group=self.group)

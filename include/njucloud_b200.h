@@ -17,9 +17,10 @@
  *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls are
  *    asynchronous on that stream unless stated otherwise.
  *  - a ctx is bound to one device; it is not thread-safe: one ctx per thread / process.
- *    Data parallel training = one process per GPU, gradients exchanged by the host binding
- *    (torch.distributed / NCCL) on the flat gradient buffer between nc_net_backward and
- *    nc_net_apply.
+ *    Data parallel training = one process per GPU; gradients are summed either by the host
+ *    binding (torch.distributed / NCCL) on the flat gradient buffer between nc_net_backward and
+ *    nc_net_apply, or inside the library once a net is attached to a communicator
+ *    (nc_net_attach_nccl), which is also what batch-norm layers need.
  */
 #ifndef NJUCLOUD_B200_H
 #define NJUCLOUD_B200_H
@@ -188,6 +189,28 @@ int nc_net_apply(nc_net* net, int opt, float lr, void* stream);
 int nc_net_train_step(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name,
                       int opt, float lr, float* loss_out, int32_t* correct_out, void* stream);
 int64_t nc_net_global_step(nc_net* net);
+
+/* ---- data parallel inside the library (NCCL bound with dlopen, one process per GPU) ----------
+ * Replaces the 1 ps + 1 worker gRPC exchange of construct_distribute.py:344-357 (cmd.py:63-69) by
+ * a synchronous all-reduce; parity target = the single-device step at the GLOBAL batch.
+ * nc_nccl_unique_id: rank 0 creates the 128-byte id and hands it to the other ranks through
+ *   whatever channel the host has (torch.distributed broadcast, a file, the Django job row).
+ *   libnccl_path NULL / "" = "libnccl.so.2" on the loader path.
+ * nc_net_attach_nccl: collective over all ranks (ncclCommInitRank).  Afterwards, on this net:
+ *   - nc_net_backward / nc_net_train_step compute normalize() (:155-165) from the moments of the
+ *     global batch (per-channel partial sums all-reduced: two small exchanges forward, one
+ *     backward), assuming every rank holds the same number of rows; nc_net_forward / _predict
+ *     keep using the statistics of the batch they are given (they are per-rank replica calls);
+ *   - nc_net_train_step scales dLoss by 1/world, sums the flat gradient buffer over the ranks and
+ *     applies the update, so every rank ends the step with the weights of the global-batch step;
+ *   - nc_net_allreduce_grads does that sum alone (between nc_net_backward(grad_scale = 1/world)
+ *     and nc_net_apply).
+ *   All ranks must make the same calls in the same order (they contain collectives).
+ * nc_net_detach_nccl: synchronises the device, destroys the communicator, back to world = 1. */
+int nc_nccl_unique_id(nc_ctx* ctx, const char* libnccl_path, unsigned char out_id[128]);
+int nc_net_attach_nccl(nc_net* net, const char* libnccl_path, const unsigned char id[128], int rank, int world);
+int nc_net_allreduce_grads(nc_net* net, void* stream);
+int nc_net_detach_nccl(nc_net* net);
 /* optimizer state (Adagrad accumulator / Adam m,v) for checkpoints: float32[slots*param_count] */
 int nc_net_state_slots(nc_net* net, int opt);
 int nc_net_get_state(nc_net* net, int opt, float* host_state);

@@ -14,7 +14,7 @@ import torch.distributed as dist
 def main():
     from cloud_server_b200.context import Context
     from cloud_server_b200.net import Net, DataParallel
-    from cloud_server_b200.configs import LENET
+    from cloud_server_b200.configs import LENET, API_EXAMPLE
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -24,11 +24,17 @@ def main():
     x = torch.rand((3, B, 784), device="cuda", generator=g)
     y = torch.nn.functional.one_hot(torch.randint(0, 10, (3, B), device="cuda", generator=g), 10).float()
     ok = True
-    for opt, lr in (("compat", 1e-4), ("sgd", 0.05)):
-        net = Net(LENET, ctx, seed=100 + rank)                   # different init per rank: broadcast must fix it
-        dp = DataParallel(net)
+    # norm layers on a 4-D and on a 2-D activation: their batch moments must span all ranks (library communicator)
+    norm_net = {"middle_layer": [{"layer": "conv", "filter": [3, 3, 8], "isBias": "True"}, {"layer": "norm"},
+                                 {"layer": "active", "active_func": "relu"}, {"layer": "pool"},
+                                 {"layer": "connect", "hidden": 64}, {"layer": "norm"}, {"layer": "active", "active_func": "relu"}]}
+    cases = [(LENET, "compat", 1e-4, None), (LENET, "sgd", 0.05, None), (LENET, "sgd", 0.05, True),
+             (API_EXAMPLE, "sgd", 0.05, None), (norm_net, "sgd", 0.05, None), (norm_net, "compat", 1e-4, None)]
+    for cfg, opt, lr, in_library in cases:
+        net = Net(cfg, ctx, seed=100 + rank)                     # different init per rank: broadcast must fix it
+        dp = DataParallel(net, in_library=in_library)
         w0 = net.get_params().copy()
-        single = Net(LENET, ctx, seed=5)
+        single = Net(cfg, ctx, seed=5)
         single.set_params(w0)
         n = B // world
         for s in range(3):
@@ -42,8 +48,13 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         same = bool(torch.equal(t, net.params))
         if rank == 0:
-            print("dp_check world=%d opt=%s: |dp - single| / |update| = %.3e, ranks identical = %s" % (world, opt, err, same), flush=True)
+            name = "lenet" if cfg is LENET else "api_example(norm)" if cfg is API_EXAMPLE else "conv-norm-dense-norm"
+            print("dp_check world=%d net=%s opt=%s in_library=%s: |dp - single| / |update| = %.3e, ranks identical = %s"
+                  % (world, name, opt, dp.in_library, err, same), flush=True)
         ok = ok and err < 1e-3 and same
+        if dp.in_library:
+            net.detach_nccl()
+        net.close(); single.close()
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)

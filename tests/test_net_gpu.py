@@ -214,3 +214,29 @@ def test_full_size_batch_properties(ctx):
     # spot-check 4 rows of the big batch against the oracle
     want = ref.forward(x[:4].cpu().numpy(), ref.unflatten(flat))
     assert rel_err(full[:4].cpu().numpy(), want) < 2e-5
+
+
+def test_library_communicator_world1_is_identity(ctx):
+    """nc_net_attach_nccl with a 1-rank communicator: same step as the unattached net (the split
+    moment kernels are only used for world > 1), and the error paths of the DP entry points."""
+    from cloud_server_b200.net import Net, new_nccl_unique_id
+    from cloud_server_b200.configs import API_EXAMPLE
+    rng = np.random.default_rng(3)
+    x = torch.from_numpy(rng.random((32, 784), dtype=np.float32)).cuda()
+    y = torch.nn.functional.one_hot(torch.from_numpy(rng.integers(0, 10, 32)).cuda(), 10).float()
+    a, b = Net(API_EXAMPLE, ctx, seed=4), Net(API_EXAMPLE, ctx, seed=4)
+    with pytest.raises(ValueError):
+        a.allreduce_grads()                                   # not attached
+    uid = new_nccl_unique_id(ctx)
+    assert len(uid) == 128
+    with pytest.raises(ValueError):
+        a.attach_nccl(uid, 1, 1)                              # rank out of range
+    a.attach_nccl(uid, 0, 1)
+    with pytest.raises(ValueError):
+        a.attach_nccl(uid, 0, 1)                              # already attached
+    for _ in range(2):
+        a.train_step(x, y, "entropy", "sgd", 0.05)
+        b.train_step(x, y, "entropy", "sgd", 0.05)
+    np.testing.assert_array_equal(a.get_params(), b.get_params())
+    a.detach_nccl()
+    a.close(); b.close()
