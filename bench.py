@@ -376,12 +376,16 @@ def run_ours(args, rank, local_rank, world):
     sampler.stop()
     ms_max = max_over_ranks(torch, ms, dist_on, device)
     value = world * n * args.steps / (ms_max * 1e-3)
+    # the opt-in single-pass kernel (both chains from one read of every upload), same step, for the record
+    os.environ["NC_FUSED_CHAINS"] = "1"
+    ms_fused = time_steps(torch, step, args.steps, 3, dist_on) / args.steps
+    del os.environ["NC_FUSED_CHAINS"]
     # each kernel alone, same inputs (per-launch duration for the rooflines)
     ms_t = time_steps(torch, step_train, args.steps, 3, dist_on) / args.steps
     ms_p = time_steps(torch, step_pred, args.steps, 3, dist_on) / args.steps
     ach_t = ALG_BYTES_TRAIN_CHAIN * n / (ms_t * 1e-3) / 1e9
     ach_p = ALG_BYTES_PREDICT_CHAIN * n / (ms_p * 1e-3) / 1e9
-    tr_t, tr_p = traffic.get("train_chain_rows_kernel"), traffic.get("predict_chain_tma_kernel")
+    tr_t, tr_p = traffic.get("train_chain_rows_kernel"), traffic.get("predict_chain_mma_kernel")
     peak = peaks["hbm_gbs"]
 
     line = {
@@ -392,9 +396,12 @@ def run_ours(args, rank, local_rank, world):
                    "l2": "inputs (%.2f GB) larger than L2" % (n * H * W * C / 1e9)},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": ach_p, "peak": peak, "unit": "GB/s", "frac": ach_p / peak,
-                     "traffic": tr_p * n if tr_p else None, "kernel": "predict_chain_tma_kernel (dominant: %.0f%% of the step)"
+                     "traffic": tr_p * n if tr_p else None, "kernel": "predict_chain_mma_kernel (dominant: %.0f%% of the step)"
                      % (100 * ms_p / (ms_p + ms_t)), "peak_source": peak_src + " (burst copy bandwidth)",
-                     "algorithmic_bytes_per_launch": ALG_BYTES_PREDICT_CHAIN * n, "launch_ms": ms_p},
+                     "algorithmic_bytes_per_launch": ALG_BYTES_PREDICT_CHAIN * n, "launch_ms": ms_p,
+                     "note": "peak = copy bandwidth (half reads, half writes); this kernel only reads (99.7 %), and a "
+                             "read-only stream can pass the copy figure: frac > 1 is possible.  ncu: 77-82 % of the 8.18 TB/s "
+                             "pin rate (profiles/r01n_ncu_preprocess.md)"},
         "train_side_chain": {"value": world * n / (ms_t * 1e-3), "unit": "images/s", "launch_ms": ms_t,
                              "roofline": {"bound": "hbm", "achieved": ach_t, "peak": peak, "unit": "GB/s", "frac": ach_t / peak,
                                           "traffic": tr_t * n if tr_t else None, "kernel": "train_chain_rows_kernel",
@@ -403,6 +410,9 @@ def run_ours(args, rank, local_rank, world):
                                           "note": "4x4-tap resize: DRAM moves the 112 source rows whole (64 B bursts, taps "
                                                   "110 B apart), 8.3x the algorithmic bytes; dram_frac = ncu traffic / time / peak"}},
         "predict_side_chain": {"value": world * n / (ms_p * 1e-3), "unit": "images/s", "launch_ms": ms_p},
+        "single_pass_opt_in": {"value": world * n / (ms_fused * 1e-3), "unit": "images/s", "ms_per_step": ms_fused,
+                               "note": "NC_FUSED_CHAINS=1: one kernel, every upload read once (13% less HBM traffic); "
+                                       "not the default because it is no faster"},
         "clocks": sampler.summary(),
     }
 

@@ -29,6 +29,8 @@ _SIGS = {
                                               c_u8p, c_f32p, C.POINTER(C.c_int), C.c_void_p]),
     "nc_pp_predict_chain": (C.c_int, [C.c_void_p, c_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int,
                                       c_f32p, c_u8p, c_i32p, C.c_void_p]),
+    "nc_pp_both_chains": (C.c_int, [C.c_void_p, c_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int,
+                                    c_u8p, c_f32p, c_f32p, c_u8p, c_i32p, c_i32p, C.c_void_p]),
     "nc_pp_op": (C.c_int, [C.c_void_p, C.c_int, c_u8p, c_u8p, C.c_int, C.c_double, C.c_double, C.c_int,
                            C.c_void_p, C.c_int64, C.c_void_p]),
     "nc_pp_cubic_table": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p]),

@@ -114,13 +114,45 @@ class Context:
         _lib.check(self.handle, rc)
         return out, status, small
 
+    def _status_buf(self, n):
+        b = getattr(self, "_status", None)
+        if b is None or b.numel() < n:
+            b = self._status = torch.zeros((max(n, 256),), dtype=torch.int32, device=self.tdev)
+        return b[:n]
+
     # ---------------------------------------------------------------- both chains over one batch
+    def both_chains(self, src, channel_order="BGR", compat=False, want_small20=False, out=None, status=None):
+        """Train-side chain (P2-P4) and predict-side chain (P5) of a CUDA batch [N,H,W,C] in one call; for
+        aligned 3-channel uploads of >= ~160 rows that is ONE kernel reading every upload once
+        (nc_pp_both_chains).  Returns (u8[N,28,28], f32_train[N,784], f32_predict[N,784], status[N],
+        small20 | None, fused: bool); bytes identical to resize_gray_norm + predict_chain."""
+        if src.dtype != torch.uint8 or not src.is_cuda or src.dim() != 4:
+            raise ValueError("src must be a uint8 CUDA tensor [N,H,W,C]")
+        src = src if src.is_contiguous() else src.contiguous()
+        n, h, w, c = src.shape
+        if out is None:
+            out = (torch.empty((n, 28, 28), dtype=torch.uint8, device=self.tdev),
+                   torch.empty((n, 784), dtype=torch.float32, device=self.tdev),
+                   torch.empty((n, 784), dtype=torch.float32, device=self.tdev))
+        u8, f32, pred = out
+        if status is None:
+            status = torch.zeros((n,), dtype=torch.int32, device=self.tdev)
+        small = torch.empty((n, 20, 20), dtype=torch.uint8, device=self.tdev) if want_small20 else None
+        fused = C.c_int(0)
+        rc = _lib.lib().nc_pp_both_chains(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, h * w * c,
+                                          {"RGB": 0, "BGR": 1}[channel_order], 1 if compat else 0,
+                                          C.c_void_p(u8.data_ptr()), C.c_void_p(f32.data_ptr()), C.c_void_p(pred.data_ptr()),
+                                          C.c_void_p(small.data_ptr()) if small is not None else None,
+                                          C.c_void_p(status.data_ptr()), C.byref(fused), self._stream())
+        _lib.check(self.handle, rc)
+        return u8, f32, pred, status, small, bool(fused.value)
+
     def preprocess_uploads(self, src, channel_order="BGR", chunk=256, out=None):
         """The whole preprocess half for a batch of decoded uploads [N,H,W,3] uint8: the train-side
         chain (P2-P4) and the predict-side chain (P5).  Returns device tensors
         (u8[N,28,28], f32_train[N,784], f32_predict[N,784]).
 
-        src on the GPU: two launches.  src in (pinned) host memory: the batch is streamed through two
+        src on the GPU: one launch (two for shapes outside the fused kernel's plan).  src in (pinned) host memory: the batch is streamed through two
         device staging buffers of `chunk` pictures -- H2D copies on a side stream overlap the kernels of
         the previous chunk, so the end-to-end rate is the PCIe rate."""
         if src.dtype != torch.uint8 or src.dim() != 4:
@@ -132,8 +164,7 @@ class Context:
                    torch.empty((n, 784), dtype=torch.float32, device=self.tdev))
         u8, f32, pred = out
         if src.is_cuda:
-            self.resize_gray_norm(src, out_u8=u8, out_f32=f32)
-            self.predict_chain(src, channel_order=channel_order, out=pred)
+            self.both_chains(src, channel_order=channel_order, out=out, status=self._status_buf(n))
             return out
         key = (chunk, h, w, c)
         st = getattr(self, "_stage", None)
@@ -154,8 +185,8 @@ class Context:
                 st["ready"][b].record(st["copy"])
             main.wait_event(st["ready"][b])
             d = st["buf"][b][:hi - lo]
-            self.resize_gray_norm(d, out_u8=u8[lo:hi], out_f32=f32[lo:hi])
-            self.predict_chain(d, channel_order=channel_order, out=pred[lo:hi])
+            self.both_chains(d, channel_order=channel_order, out=(u8[lo:hi], f32[lo:hi], pred[lo:hi]),
+                             status=self._status_buf(hi - lo))
             st["free"][b].record(main)
         return out
 

@@ -17,6 +17,7 @@
 #include "nc_internal.h"
 #include <string.h>
 #include <stdlib.h>
+#include <algorithm>
 
 namespace {
 
@@ -375,13 +376,321 @@ predict_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int 
     finish_picture(hdr, s_temp, s_small, s_canvas, &s_err, g_kky, compat, out_f32, out_small20, status, kThreads);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tensor-core variant of the horizontal pass.  The pass is a banded integer matrix product
+// (gray rows [16 x w] u8) x (weights [w x 20] s32); with the weights split into three signed
+// byte digits (k = d0 + 256 d1 + 65536 d2, each in [-128,127]) it is exact in int32 on the
+// u8 x s8 -> s32 warp MMA (m16n8k32).  Warp v owns output columns 2v and 2v+1: the 8 MMA
+// columns are {o0d0, o0d1, o1d0, o1d1, o0d2, 0, o1d2, 0}, its K range is the union of the two tap
+// windows (nch 32-pixel chunks from kw[v]), and its B fragments are constant for the whole
+// picture, so they live in registers.  The MMA's K slots are permuted (slots 4t..4t+3 and
+// 16+4t..16+4t+3 of thread-in-group t = pixels 8t..8t+7 of the chunk) so a thread's A registers are
+// one 8-byte shared load per row.  One raw stage = one gray block of `sr` <= 16 rows, gray
+// blocks double buffered: a single __syncthreads per stage.
+// Costs 9 MMA + 36 LDS per warp and block where the dp4a pass needs ~270 instructions.
+// ---------------------------------------------------------------------------------------------
+struct MmaPlan {
+    int kw[kOut / 2];        // first gray word (4 pixels) of the warp's K range, even
+    int nch;                 // 32-pixel chunks in every warp's range
+};
+
+__device__ __forceinline__ void mma_u8s8(int& c0, int& c1, int& c2, int& c3, unsigned a0, unsigned a1, unsigned a2, unsigned a3,
+                                         unsigned b0, unsigned b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c0), "+r"(c1), "+r"(c2), "+r"(c3)
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// FUSE: the train-side chain (pp_train_chain.cu: OpenCV cubic 28x28 -> BGR2GRAY -> *1/255) computed from the same
+// staged rows, so the upload is read from HBM once for both chains.  The 112 (output row, tap) source rows are met in
+// increasing order while the picture streams through; each one's horizontal pass (84 int32) goes to a ring of 8 row
+// slots (two output rows), and an output row is finished -- vertical pass, gray, store -- by warp 0 in the stage after
+// its fourth tap row.  The host only selects FUSE when the tap rows are sorted and two output rows apart never share
+// two consecutive stages, which makes the ring race free with the one __syncthreads per stage.
+struct FuseArgs {
+    CvCubicAxis x, y;
+    uint8_t* out_u8;          // [n][784] gray, nullable
+    float* out_f32;           // [n][784] gray / 255, nullable
+};
+
+// VResizeCubic (float32 body for the first 80 interleaved elements, integer tail) + BGR2GRAY + *1/255 of output row dy,
+// pixel dx, from the four tap rows in the ring; same arithmetic as train_chain_rows_kernel (pp_train_chain.cu)
+__device__ __forceinline__ void train_row_finish(const FuseArgs& fa, const int (*hbuf)[84], int dy, int dx) {
+    constexpr int NSIMD = (84 / 8) * 8;
+    const float scale = 1.0f / (2048.0f * 2048.0f);
+    const int b0 = fa.y.coef[dy][0], b1 = fa.y.coef[dy][1], b2 = fa.y.coef[dy][2], b3 = fa.y.coef[dy][3];
+    const float f0 = __fmul_rn((float)b0, scale), f1 = __fmul_rn((float)b1, scale);
+    const float f2 = __fmul_rn((float)b2, scale), f3 = __fmul_rn((float)b3, scale);
+    const int q = (4 * dy) & 7;
+    int col[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const int e = dx * 3 + c;
+        const int S0 = hbuf[q][e], S1 = hbuf[q + 1][e], S2 = hbuf[q + 2][e], S3 = hbuf[q + 3][e];
+        int v;
+        if (e < NSIMD) {
+            float t = __fmul_rn(__int2float_rn(S3), f3);
+            t = __fadd_rn(__fmul_rn(__int2float_rn(S2), f2), t);
+            t = __fadd_rn(__fmul_rn(__int2float_rn(S1), f1), t);
+            t = __fadd_rn(__fmul_rn(__int2float_rn(S0), f0), t);
+            v = __float2int_rn(t);
+        } else {
+            const int sum = S0 * b0 + S1 * b1 + S2 * b2 + S3 * b3;
+            v = (sum + (1 << 21)) >> 22;
+        }
+        col[c] = v < 0 ? 0 : (v > 255 ? 255 : v);
+    }
+    const int g = (3735 * col[0] + 19235 * col[1] + 9798 * col[2] + (1 << 14)) >> 15;
+    const long long o = (long long)blockIdx.x * 784 + dy * 28 + dx;
+    if (fa.out_u8) fa.out_u8[o] = (uint8_t)g;
+    if (fa.out_f32) fa.out_f32[o] = __fmul_rn((float)g, (float)(1.0 / 255.0));
+}
+
+template <int NCH, bool FUSE>
+__global__ void __launch_bounds__(kThreads + 32, 2)
+predict_chain_mma_kernel(const uint8_t* __restrict__ src, long long img_stride, int h, int w,
+                         const PredHdr* __restrict__ g_hdr, const MmaPlan* __restrict__ g_plan,
+                         const uint2* __restrict__ g_bfrag,
+                         const int* __restrict__ g_kky, unsigned A01, unsigned A2_, unsigned A_0, unsigned A12,
+                         int compat, float* __restrict__ out_f32, uint8_t* __restrict__ out_small20,
+                         int* __restrict__ status, int pitch, int sr, unsigned ipr, const __grid_constant__ FuseArgs fa) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ int s_hbuf[FUSE ? 8 : 1][84];
+    __shared__ int s_xofs3[FUSE ? 28 : 1][4], s_xcoef[FUSE ? 28 : 1][4];
+    __shared__ PredHdr hdr;
+    __shared__ unsigned char s_small[kOut * kOut];
+    __shared__ unsigned char s_canvas[784];
+    __shared__ int s_err;
+    __shared__ __align__(8) unsigned long long s_bar[2];
+
+    // FUSE adds an 11th warp that finishes the train-side output rows (vertical pass, gray, stores), so that serial
+    // piece never sits between a worker warp and the stage barrier; the tap sums themselves are spread over the workers
+    constexpr int kAll = FUSE ? kThreads + 32 : kThreads;
+    const int tid = threadIdx.x;
+    const bool worker = !FUSE || tid < kThreads;
+    for (int i = tid; i < (int)(sizeof(PredHdr) / 4); i += kAll) ((int*)&hdr)[i] = ((const int*)g_hdr)[i];
+    if (FUSE)
+        for (int i = tid; i < 112; i += kAll) {
+            s_xofs3[i >> 2][i & 3] = fa.x.ofs[i >> 2][i & 3] * 3;
+            s_xcoef[i >> 2][i & 3] = fa.x.coef[i >> 2][i & 3];
+        }
+    const unsigned row_bytes = (unsigned)w * 3u;
+    const unsigned stage_bytes = (unsigned)sr * row_bytes;
+    unsigned char* raw = smem;                                            // 2 stages of raw rows
+    // 2 gray blocks of sr rows x pitch words + (16 - sr) rows of slack: the MMA always reads 16 rows, the rows past sr
+    // belong to the other block / the slack and only feed accumulator rows that are dropped
+    unsigned* s_gbuf = reinterpret_cast<unsigned*>(smem + 2 * stage_bytes);
+    const unsigned gblock = (unsigned)sr * (unsigned)pitch;
+    const unsigned gwords = (unsigned)(sr + 16) * (unsigned)pitch;
+    unsigned char* s_temp = reinterpret_cast<unsigned char*>(s_gbuf + gwords);
+
+    const uint8_t* base = src + (long long)blockIdx.x * img_stride;
+    const int nstages = (h + sr - 1) / sr;
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&s_bar[0]);
+    const unsigned raw0 = (unsigned)__cvta_generic_to_shared(raw);
+
+    auto issue = [&](int s) {
+        const int r0 = s * sr;
+        const unsigned bytes = (unsigned)min(sr, h - r0) * row_bytes;
+        const unsigned bar = bar0 + 8u * (s & 1);
+        const unsigned dst = raw0 + (s & 1) * stage_bytes;
+        const uint8_t* gsrc = base + (long long)r0 * row_bytes;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(gsrc), "r"(bytes), "r"(bar) : "memory");
+    };
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        issue(0);
+        if (nstages > 1) issue(1);
+    }
+    // rows sr..15 of a gray block are never written by phase 1 but are MMA operands (their results are dropped)
+    for (unsigned i = tid; i < gwords; i += kAll) s_gbuf[i] = 0u;
+
+    // this warp's B fragments and K range
+    const int wv = worker ? tid >> 5 : 0, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
+    unsigned bx[NCH], by[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+        const uint2 b = __ldg(g_bfrag + ((size_t)wv * NCH + c) * 32 + lane);
+        bx[c] = b.x; by[c] = b.y;
+    }
+    const unsigned a_off = (unsigned)gid * (unsigned)pitch + (unsigned)g_plan->kw[wv] + 2u * (unsigned)tig;
+
+    // phase-1 item walk: item = 16 pixels = 48 contiguous staged bytes -> 4 gray words; items of a stage are
+    // contiguous in the raw buffer (row_bytes = 48 ipr), the gray rows have `pitch - 4 ipr` words of padding
+    const unsigned it_g0 = (unsigned)tid % ipr, it_r0 = (unsigned)tid / ipr;
+    const unsigned dg = (unsigned)kThreads % ipr, dr = (unsigned)kThreads / ipr;
+    const unsigned padw = (unsigned)pitch - 4u * ipr;
+    const unsigned d_dst = 4u * (unsigned)kThreads + dr * padw;          // words per step without wrap
+    const unsigned dst0 = it_r0 * (unsigned)pitch + 4u * it_g0;
+    const unsigned full_items = (unsigned)sr * ipr, last_items = (unsigned)(h - (nstages - 1) * sr) * ipr;
+    // per-buffer bases (buffer = s & 1), selected per stage instead of recomputed
+    const uint4* p_b0 = reinterpret_cast<const uint4*>(raw) + 3u * (unsigned)tid;
+    const uint4* p_b1 = reinterpret_cast<const uint4*>(raw + stage_bytes) + 3u * (unsigned)tid;
+    unsigned* g_b0 = s_gbuf;
+    unsigned* g_b1 = s_gbuf + gblock;
+    const int out_col = 2 * wv + (tig & 1);
+    const int out_row = gid + ((tig & 2) ? 8 : 0);
+    unsigned char* t_out = s_temp + out_row * kOut + out_col;
+    int ns = 0, nv = 0;       // FUSE: next tap-row slot to fill (0..112), next output row to finish (0..28); uniform
+    int next_row = FUSE ? fa.y.ofs[0][0] : 0x7fffffff;        // source row of slot ns
+    __syncthreads();
+
+    for (int s = 0; s < nstages; ++s) {
+        const int odd = s & 1;
+        const bool last = s == nstages - 1;
+        if (worker) mbar_wait(bar0 + 8u * odd, (unsigned)((s >> 1) & 1));
+        // ---------------- phase 1: staged bytes -> rgb2l -> gray block (s & 1)
+        unsigned* gblk = odd ? g_b1 : g_b0;
+        if (worker) {
+            const unsigned items = last ? last_items : full_items;
+            unsigned g = it_g0;
+            unsigned dst = dst0;
+            const uint4* p = odd ? p_b1 : p_b0;
+            for (unsigned it = tid; it < items; it += kThreads) {
+                const uint4 q0 = p[0], q1 = p[1], q2 = p[2];
+                uint2 o0, o1;
+                o0.x = gray4(q0.x, q0.y, q0.z, A01, A2_, A_0, A12);
+                o0.y = gray4(q0.w, q1.x, q1.y, A01, A2_, A_0, A12);
+                o1.x = gray4(q1.z, q1.w, q2.x, A01, A2_, A_0, A12);
+                o1.y = gray4(q2.y, q2.z, q2.w, A01, A2_, A_0, A12);
+                *reinterpret_cast<uint4*>(gblk + dst) = make_uint4(o0.x, o0.y, o1.x, o1.y);   // pitch % 4 == 0: 16-byte aligned
+                p += 3 * kThreads;
+                g += dg;
+                dst += d_dst;
+                if (g >= ipr) { g -= ipr; dst += padw; }
+            }
+        }
+        if (FUSE) {
+            // train-side horizontal pass (HResizeCubic<uchar,int,short>) of the tap rows that are in this stage:
+            // (slot, element) pairs spread over the worker threads, 4 taps each.  About every second stage has none.
+            const int r0 = s * sr;
+            const int rend = last ? h : r0 + sr;
+            if (next_row < rend) {
+                const int ns0 = ns;
+                do {
+                    ++ns;
+                    next_row = ns < 112 ? fa.y.ofs[ns >> 2][ns & 3] : 0x7fffffff;
+                } while (next_row < rend);
+                if (worker) {
+                    const unsigned char* rb = raw + (size_t)odd * stage_bytes;
+                    const int pairs = (ns - ns0) * 84;
+                    for (int pi = tid; pi < pairs; pi += kThreads) {
+                        const int sl = pi / 84, e = pi - sl * 84;
+                        const int slot = ns0 + sl;
+                        const int dx = e / 3, ch = e - dx * 3;
+                        const unsigned char* rp = rb + (size_t)(fa.y.ofs[slot >> 2][slot & 3] - r0) * row_bytes + ch;
+                        int acc = 0;
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) acc += (int)rp[s_xofs3[dx][t]] * s_xcoef[dx][t];
+                        s_hbuf[slot & 7][e] = acc;
+                    }
+                }
+            }
+        }
+        __syncthreads();          // raw stage consumed; gray block (s&1) complete; everyone is past phase 2 of stage s-1
+        if (FUSE && !worker) {
+            while (4 * nv + 3 < ns) {                     // ns <= 112, so nv stops at 28
+                if (lane < 28) train_row_finish(fa, s_hbuf, nv, lane);
+                ++nv;
+            }
+        }
+        if (tid == 0 && s + 2 < nstages) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic reads before async writes
+            issue(s + 2);
+        }
+        // ---------------- phase 2: horizontal pass, one m16n8k32 MMA per 32-pixel chunk
+        if (worker) {
+            const uint2* a_lo = reinterpret_cast<const uint2*>(gblk + a_off);
+            const uint2* a_hi = a_lo + 4u * (unsigned)pitch;
+            int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                const uint2 lo = a_lo[4 * c], hi = a_hi[4 * c];           // 8 consecutive pixels of rows gid, gid + 8
+                mma_u8s8(c0, c1, c2, c3, lo.x, hi.x, lo.y, hi.y, bx[c], by[c]);
+            }
+            // columns held: (2 tig, 2 tig + 1) = tig 0: o0 d0,d1 | tig 1: o1 d0,d1 | tig 2: o0 d2,0 | tig 3: o1 d2,0
+            int p_lo = tig < 2 ? c0 + c1 * 256 : c0 * 65536;
+            int p_hi = tig < 2 ? c2 + c3 * 256 : c2 * 65536;
+            p_lo += __shfl_xor_sync(0xffffffffu, p_lo, 2);
+            p_hi += __shfl_xor_sync(0xffffffffu, p_hi, 2);
+            const int v = (tig & 2) ? p_hi : p_lo;
+            if (out_row < (last ? h - s * sr : sr)) *t_out = (unsigned char)clip8((v + (1 << 21)) >> 22);
+            t_out += sr * kOut;
+        }
+    }
+    __syncthreads();
+    if (FUSE && !worker) {
+        while (4 * nv + 3 < ns) {
+            if (lane < 28) train_row_finish(fa, s_hbuf, nv, lane);
+            ++nv;
+        }
+    }
+    finish_picture(hdr, s_temp, s_small, s_canvas, &s_err, g_kky, compat, out_f32, out_small20, status, kAll);
+}
+
 struct PredTabDev {
     PredHdr hdr;
     PredHdr* d_hdr;
     uint4* d_groups;
     int* d_kky;
+    MmaPlan* d_plan;
+    uint2* d_bfrag;
+    int bstride;             // chunks per warp in d_bfrag (= max nch)
 };
 
+// B fragments of the tensor-core horizontal pass: [warp v][chunk c][lane] -> (b0, b1), see predict_chain_mma_kernel
+void build_mma_plan(const PilAxisHost& ax, int w, MmaPlan* plan, std::vector<uint2>* frag) {
+    int maxch = 1;
+    int k0s[kOut / 2];
+    for (int v = 0; v < kOut / 2; ++v) {
+        const int lo = std::min(ax.xmin[2 * v], ax.xmin[2 * v + 1]);
+        const int hi = std::max(ax.xmin[2 * v] + ax.cnt[2 * v], ax.xmin[2 * v + 1] + ax.cnt[2 * v + 1]);
+        k0s[v] = lo & ~7;
+        maxch = std::max(maxch, (hi - k0s[v] + 31) / 32);
+    }
+    plan->nch = maxch;
+    // every warp runs maxch chunks; slide a range down where it would pass the 32 pixels of slack behind the row
+    for (int v = 0; v < kOut / 2; ++v) {
+        int k0 = k0s[v];
+        const int limit = (w + 32 - 32 * maxch) & ~7;
+        if (k0 > limit) k0 = limit;
+        if (k0 < 0) k0 = 0;
+        plan->kw[v] = k0 / 4;
+    }
+    frag->assign((size_t)(kOut / 2) * maxch * 32, make_uint2(0u, 0u));
+    auto digit = [&](int o, int x, int d) -> int {      // signed byte digit d of output o's weight at pixel x
+        const int xmin = ax.xmin[o], cnt = ax.cnt[o];
+        if (x < xmin || x >= xmin + cnt) return 0;
+        int k = ax.kk[(size_t)o * ax.ksize + (x - xmin)];
+        for (int i = 0;; ++i) {
+            const int dg = ((k + 128) & 255) - 128;
+            if (i == d) return dg;
+            k = (k - dg) / 256;                          // exact: k - dg is a multiple of 256
+        }
+    };
+    for (int v = 0; v < kOut / 2; ++v)
+        for (int c = 0; c < maxch; ++c)
+            for (int lane = 0; lane < 32; ++lane) {
+                const int n = lane >> 2, tig = lane & 3;
+                // column n: {o0 d0, o0 d1, o1 d0, o1 d1, o0 d2, 0, o1 d2, 0}
+                static const int col_o[8] = {0, 0, 1, 1, 0, -1, 1, -1}, col_d[8] = {0, 1, 0, 1, 2, 0, 2, 0};
+                uint2 q = make_uint2(0u, 0u);
+                if (col_o[n] >= 0) {
+                    const int o = 2 * v + col_o[n];
+                    for (int i = 0; i < 4; ++i) {
+                        // K slots 4 tig + i (b0) and 16 + 4 tig + i (b1) are pixels 8 tig + i and 8 tig + 4 + i of the chunk
+                        const int x0 = plan->kw[v] * 4 + 32 * c + 8 * tig + i;
+                        q.x |= ((unsigned)digit(o, x0, col_d[n]) & 255u) << (8 * i);
+                        q.y |= ((unsigned)digit(o, x0 + 4, col_d[n]) & 255u) << (8 * i);
+                    }
+                }
+                (*frag)[((size_t)v * maxch + c) * 32 + lane] = q;
+            }
+}
 }  // namespace
 
 // Build (or fetch from the ctx cache) the per-shape tables.
@@ -421,32 +730,52 @@ static int get_pred_tables(nc_ctx* ctx, int h, int w, PredTabDev* out) {
         }
         hdr.ksize_y = ay.ksize;
         hdr.total_groups = (int)groups.size();
+        MmaPlan plan;
+        std::vector<uint2> frag;
+        build_mma_plan(ax, w, &plan, &frag);
+        const int bstride = plan.nch;
         const size_t b_hdr = (sizeof(PredHdr) + 15) / 16 * 16;
         const size_t b_groups = groups.size() * sizeof(uint4);
-        const size_t b_kky = ay.kk.size() * sizeof(int);
+        const size_t b_kky = (ay.kk.size() * sizeof(int) + 15) / 16 * 16;
+        const size_t b_plan = (sizeof(MmaPlan) + 15) / 16 * 16;
+        const size_t b_frag = frag.size() * sizeof(uint2);
         nc_dev_table tab;
-        tab.bytes = b_hdr + b_groups + b_kky;
+        tab.bytes = b_hdr + b_groups + b_kky + b_plan + b_frag;
         NC_CUDA(ctx, cudaMalloc(&tab.dptr, tab.bytes));
         std::vector<unsigned char> blob(tab.bytes, 0);
         memcpy(blob.data(), &hdr, sizeof(hdr));
         memcpy(blob.data() + b_hdr, groups.data(), b_groups);
-        memcpy(blob.data() + b_hdr + b_groups, ay.kk.data(), b_kky);
+        memcpy(blob.data() + b_hdr + b_groups, ay.kk.data(), ay.kk.size() * sizeof(int));
+        memcpy(blob.data() + b_hdr + b_groups + b_kky, &plan, sizeof(plan));
+        memcpy(blob.data() + b_hdr + b_groups + b_kky + b_plan, frag.data(), b_frag);
         NC_CUDA(ctx, cudaMemcpy(tab.dptr, blob.data(), tab.bytes, cudaMemcpyHostToDevice));
+        // host copy: header, then the sizes needed to find the other sections again
         tab.host.assign(blob.begin(), blob.begin() + sizeof(PredHdr));
+        const int64_t extra[3] = {(int64_t)b_kky, (int64_t)bstride, 0};
+        tab.host.insert(tab.host.end(), (const unsigned char*)extra, (const unsigned char*)extra + sizeof(extra));
         it = ctx->pil_tables.emplace(key, tab).first;
     }
     unsigned char* d = (unsigned char*)it->second.dptr;
     const size_t b_hdr = (sizeof(PredHdr) + 15) / 16 * 16;
     memcpy(&out->hdr, it->second.host.data(), sizeof(PredHdr));
+    int64_t extra[3];
+    memcpy(extra, it->second.host.data() + sizeof(PredHdr), sizeof(extra));
+    const size_t b_groups = (size_t)out->hdr.total_groups * sizeof(uint4);
     out->d_hdr = (PredHdr*)d;
     out->d_groups = (uint4*)(d + b_hdr);
-    out->d_kky = (int*)(d + b_hdr + (size_t)out->hdr.total_groups * sizeof(uint4));
+    out->d_kky = (int*)(d + b_hdr + b_groups);
+    out->d_plan = (MmaPlan*)(d + b_hdr + b_groups + (size_t)extra[0]);
+    out->d_bfrag = (uint2*)(d + b_hdr + b_groups + (size_t)extra[0] + (sizeof(MmaPlan) + 15) / 16 * 16);
+    out->bstride = (int)extra[1];
     return NC_OK;
 }
 
-extern "C" int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
-                                   int64_t img_stride, int channel_order, int compat, float* out_f32,
-                                   uint8_t* out_small20, int* status, void* stream) {
+// fuse: when non-NULL and the tensor-core kernel with the fused train-side chain can take this shape, it is launched
+// with FUSE and *fused is set; otherwise the predict-side chain alone runs and *fused stays 0.
+static int predict_impl(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
+                        int64_t img_stride, int channel_order, int compat, float* out_f32,
+                        uint8_t* out_small20, int* status, void* stream, FuseArgs* fuse, int* fused) {
+    if (fused) *fused = 0;
     if (!ctx) return nc_set_error(nullptr, NC_EINVAL, "ctx is NULL");
     if (n < 0 || h <= 0 || w <= 0) return nc_set_error(ctx, NC_EINVAL, "bad shape n=%d h=%d w=%d", n, h, w);
     if (c != 1 && c != 3) return nc_set_error(ctx, NC_EINVAL, "channels must be 1 or 3, got %d", c);
@@ -494,6 +823,71 @@ extern "C" int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h
     // TMA-staged kernel: 3 channels, rows and pictures 16-byte aligned, the plan fits shared memory
     if (c == 3 && (w % 16) == 0 && (reinterpret_cast<uintptr_t>(src) % 16) == 0 && (img_stride % 16) == 0 && h >= 16 &&
         !getenv("NC_PREDICT_NO_TMA")) {
+        // tensor-core horizontal pass: needs the warp's K range in <= 16 chunks (w <= ~2000) and a stage plan that fits
+        if (!getenv("NC_PREDICT_NO_MMA") && tabs.bstride <= 16) {
+            const unsigned ipr = (unsigned)w / 16;
+            int pitch = w / 4 + 8;                       // >= 8 words of slack: the last chunk may overrun the row by < 32 pixels
+            while ((pitch & 15) != 8) pitch += 4;        // = 8 mod 16 words: 16-byte item stores, and the 4 rows x 8 words of a
+                                                         // half-warp's 8-byte A loads cover 32 distinct banks
+            // rows per stage: a multiple of the 320-thread item walk when possible (w = 1024: 10 rows = 2 items per thread)
+            int sr = 16;
+            while (sr > 1 && (size_t)sr * w * 3 > 32 * 1024) --sr;
+            int best = sr; double best_eff = 0.0;
+            for (int r = sr; r >= (sr + 1) / 2 && r >= 1; --r) {
+                const unsigned items = (unsigned)r * ipr;
+                const double eff = (double)items / (double)(((items + kThreads - 1) / kThreads) * kThreads);
+                if (eff > best_eff + 1e-9) { best_eff = eff; best = r; }
+            }
+            sr = best;
+            const size_t smem3 = 2 * (size_t)sr * w * 3 + (size_t)(sr + 16) * pitch * 4 + ((size_t)h * kOut + 15) / 16 * 16;
+            if (smem3 <= 220 * 1024 && ((size_t)sr * w * 3) % 16 == 0) {
+                // fused train-side chain: tap rows sorted, and output rows g, g + 2 never within two consecutive stages
+                // (so the 8-slot ring of horizontal results is race free, see the kernel)
+                // Measured on B200 (profiles/r01p_fused_chains.md): the single pass costs as much issue time as the
+                // separate train-side launch costs DRAM time, so it is opt-in (it saves 13 % of the HBM traffic, no time).
+                bool do_fuse = fuse != nullptr && !(h == 28 && w == 28) && getenv("NC_FUSED_CHAINS") != nullptr;
+                FuseArgs fa;
+                memset(&fa, 0, sizeof(fa));
+                if (do_fuse) {
+                    fa = *fuse;
+                    nc_cv_cubic_axis(w, 28, &fa.x);
+                    nc_cv_cubic_axis(h, 28, &fa.y);
+                    const int* yo = &fa.y.ofs[0][0];
+                    for (int i = 0; i + 1 < 112 && do_fuse; ++i) if (yo[i] > yo[i + 1]) do_fuse = false;
+                    for (int g = 0; g + 2 < 28 && do_fuse; ++g) if (yo[4 * g + 8] - yo[4 * g + 3] < 2 * sr) do_fuse = false;
+                }
+
+                const unsigned A01 = (unsigned)c0 | ((unsigned)c1 << 16), A2_ = (unsigned)c2, A_0 = (unsigned)c0 << 16,
+                               A12 = (unsigned)c1 | ((unsigned)c2 << 16);
+#define NC_LAUNCH_MMA_F(NCH, F)                                                                                          \
+    do {                                                                                                                 \
+        NC_CUDA(ctx, cudaFuncSetAttribute(predict_chain_mma_kernel<NCH, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                          (int)smem3));                                                                  \
+        predict_chain_mma_kernel<NCH, F><<<n, (F) ? kThreads + 32 : kThreads, smem3, st>>>(src, img_stride, h, w, tabs.d_hdr, tabs.d_plan,     \
+                                                                      tabs.d_bfrag, tabs.d_kky, A01, A2_, A_0, A12,      \
+                                                                      compat, out_f32, out_small20, status, pitch, sr,   \
+                                                                      ipr, fa);                                          \
+    } while (0)
+#define NC_LAUNCH_MMA(NCH)                                                                                               \
+    do {                                                                                                                 \
+        if (do_fuse) NC_LAUNCH_MMA_F(NCH, true);                                                                         \
+        else NC_LAUNCH_MMA_F(NCH, false);                                                                                \
+    } while (0)
+                switch (tabs.bstride) {                   // chunks per warp = registers held, so one instantiation each
+                    case 1: NC_LAUNCH_MMA(1); break;   case 2: NC_LAUNCH_MMA(2); break;   case 3: NC_LAUNCH_MMA(3); break;
+                    case 4: NC_LAUNCH_MMA(4); break;   case 5: NC_LAUNCH_MMA(5); break;   case 6: NC_LAUNCH_MMA(6); break;
+                    case 7: NC_LAUNCH_MMA(7); break;   case 8: NC_LAUNCH_MMA(8); break;   case 9: NC_LAUNCH_MMA(9); break;
+                    case 10: NC_LAUNCH_MMA(10); break; case 11: NC_LAUNCH_MMA(11); break; case 12: NC_LAUNCH_MMA(12); break;
+                    case 13: NC_LAUNCH_MMA(13); break; case 14: NC_LAUNCH_MMA(14); break; case 15: NC_LAUNCH_MMA(15); break;
+                    default: NC_LAUNCH_MMA(16); break;
+                }
+                if (do_fuse && fused) *fused = 1;
+#undef NC_LAUNCH_MMA_F
+#undef NC_LAUNCH_MMA
+                NC_LAUNCH_CHECK(ctx);
+                return NC_OK;
+            }
+        }
         const int wq2 = w / 4 + 2;                 // even, = 2 mod 4: 8-byte stores, row pairs on distinct banks
         const size_t stage = (size_t)kStageRows * w * 3;
         const size_t smem2 = 2 * stage + (size_t)tabs.hdr.total_groups * 16 + (size_t)16 * wq2 * 4 + ((size_t)h * kOut + 15) / 16 * 16;
@@ -523,4 +917,32 @@ extern "C" int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h
     }
     NC_LAUNCH_CHECK(ctx);
     return NC_OK;
+}
+
+extern "C" int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
+                                   int64_t img_stride, int channel_order, int compat, float* out_f32,
+                                   uint8_t* out_small20, int* status, void* stream) {
+    return predict_impl(ctx, src, n, h, w, c, img_stride, channel_order, compat, out_f32, out_small20, status, stream,
+                        nullptr, nullptr);
+}
+
+extern "C" int nc_pp_both_chains(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c, int64_t img_stride,
+                                 int channel_order, int compat, uint8_t* out_train_u8, float* out_train_f32,
+                                 float* out_predict_f32, uint8_t* out_small20, int* status, int* fused, void* stream) {
+    if (fused) *fused = 0;
+    if (!ctx) return nc_set_error(nullptr, NC_EINVAL, "ctx is NULL");
+    if (n == 0) return NC_OK;
+    if (!out_train_u8 && !out_train_f32) return nc_set_error(ctx, NC_EINVAL, "both train-side outputs are NULL");
+    FuseArgs fa;
+    memset(&fa, 0, sizeof(fa));
+    fa.out_u8 = out_train_u8;
+    fa.out_f32 = out_train_f32;
+    int did = 0;
+    int rc = predict_impl(ctx, src, n, h, w, c, img_stride, channel_order, compat, out_predict_f32, out_small20, status,
+                          stream, &fa, &did);
+    if (rc != NC_OK) return rc;
+    if (fused) *fused = did;
+    if (did) return NC_OK;
+    // shape outside the fused plan: the train-side chain as its own launch (same bytes out)
+    return nc_pp_resize_gray_norm(ctx, src, n, h, w, c, img_stride, 0, out_train_u8, out_train_f32, stream);
 }

@@ -92,6 +92,24 @@ int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, in
                         int64_t img_stride, int channel_order, int compat, float* out_f32,
                         uint8_t* out_small20, int* status, void* stream);
 
+/* ---- P2-P5 in one pass: both chains over the same uploads ------------------------------
+ * The platform runs both chains over every upload: the train-side one when a dataset is
+ * preprocessed (apps/preprocess/preprocess.py:28-30,40 + construct_distribute.py:503-504) and the
+ * predict-side one when a picture is classified (construct_inference.py:312-330).  For a batch
+ * resident in HBM this entry point produces exactly the bytes of nc_pp_resize_gray_norm(mode 0)
+ * (out_train_u8 / out_train_f32, either nullable) and of nc_pp_predict_chain (out_predict_f32,
+ * out_small20, status); its single-pass kernel reads each upload from HBM once: the cubic taps of the
+ * train-side chain are taken from the rows the predict-side chain streams through shared memory.  The train
+ * side reads the buffer as BGR (cv2), channel_order applies to the predict side as above.
+ * Two launches by default; with NC_FUSED_CHAINS set in the environment, one single-pass kernel
+ * where the shape is inside its plan (3 channels, 16-byte aligned rows, >= ~160 rows, width
+ * <= ~2000).  On B200 the two take the same time (the single pass trades the 13 % of HBM traffic
+ * it saves for issue slots), which is why it is opt-in.  *fused (nullable) reports which ran;
+ * the outputs are identical either way. */
+int nc_pp_both_chains(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c, int64_t img_stride,
+                      int channel_order, int compat, uint8_t* out_train_u8, float* out_train_f32,
+                      float* out_predict_f32, uint8_t* out_small20, int* status, int* fused, void* stream);
+
 /* ---- P6-P19: the 14 per-picture ops on 28x28 8-bit gray --------------------------------
  * in/out: [n][28][28] uint8 device buffers (in == out allowed).  One call = one op applied
  * to every picture, as PreprocessView.execute's loop does (apps/preprocess/views.py:118-126).

@@ -198,20 +198,74 @@ def test_predict_chain_random_shapes_vs_oracle(ctx):
                     assert int(status[i]) == 1
 
 
-def test_predict_chain_both_kernels_agree(ctx, monkeypatch):
-    """The TMA-staged kernel (aligned 3-channel pictures) and the generic kernel give identical bytes."""
+def test_predict_chain_all_kernels_agree(ctx, monkeypatch):
+    """The three kernels behind nc_pp_predict_chain give identical bytes: TMA-staged rows + tensor-core
+    (u8 x s8 IMMA) horizontal pass, TMA-staged rows + dp4a horizontal pass, and the generic kernel.
+    Shapes cover every instantiation of the IMMA kernel (<= 5, <= 9, <= 16 chunks per warp), upscaling
+    (w < 20), partial last stages and widths past the IMMA plan (falls back to dp4a)."""
     rng = np.random.default_rng(33)
-    for (h, w) in [(16, 16), (40, 64), (97, 160), (768, 1024), (333, 1008)]:
+    for (h, w) in [(16, 16), (40, 64), (97, 160), (768, 1024), (333, 1008), (50, 1936), (17, 2048), (200, 320), (31, 48)]:
         imgs = dev(rng.integers(0, 256, (3, h, w, 3), np.uint8))
         monkeypatch.delenv("NC_PREDICT_NO_TMA", raising=False)
+        monkeypatch.delenv("NC_PREDICT_NO_MMA", raising=False)
         o1, s1, m1 = ctx.predict_chain(imgs, compat=True, want_small20=True)
+        monkeypatch.setenv("NC_PREDICT_NO_MMA", "1")
+        o3, s3, m3 = ctx.predict_chain(imgs, compat=True, want_small20=True)
         monkeypatch.setenv("NC_PREDICT_NO_TMA", "1")
         o2, s2, m2 = ctx.predict_chain(imgs, compat=True, want_small20=True)
         monkeypatch.delenv("NC_PREDICT_NO_TMA", raising=False)
-        assert torch.equal(m1, m2), (h, w)
-        assert torch.equal(o1, o2) and torch.equal(s1, s2)
+        monkeypatch.delenv("NC_PREDICT_NO_MMA", raising=False)
+        assert torch.equal(m1, m2) and torch.equal(m1, m3), (h, w)
+        assert torch.equal(o1, o2) and torch.equal(s1, s2) and torch.equal(o1, o3) and torch.equal(s1, s3)
         es = R.pil_resize_bicubic_l(R.pil_rgb2l(imgs[1].cpu().numpy()))
         assert np.array_equal(m1[1].cpu().numpy(), es), (h, w)
+    # extreme pixel values: the signed-digit split must stay exact at the ends of the u8 range
+    for fill in (0, 255):
+        imgs = torch.full((2, 64, 1024, 3), fill, dtype=torch.uint8, device="cuda")
+        imgs[1, :, ::2] = 255 - fill
+        _, _, m = ctx.predict_chain(imgs, want_small20=True)
+        for i in range(2):
+            assert np.array_equal(m[i].cpu().numpy(), R.pil_resize_bicubic_l(R.pil_rgb2l(imgs[i].cpu().numpy())))
+
+
+def test_both_chains_single_pass_equals_the_two_kernels(ctx, monkeypatch):
+    """nc_pp_both_chains: the fused single-pass kernel (where the shape allows it) and the two-launch fallback produce
+    the bytes of nc_pp_resize_gray_norm and nc_pp_predict_chain; the train side is also checked against the oracle."""
+    rng = np.random.default_rng(35)
+    seen = set()
+    for (h, w, expect_fused) in [(768, 1024, True), (1080, 1920, True), (600, 800, True), (333, 1008, True), (480, 640, False),
+                                 (97, 160, False), (28, 32, False), (768, 1000, False)]:
+        imgs = dev(rng.integers(0, 256, (3, h, w, 3), np.uint8))
+        monkeypatch.setenv("NC_FUSED_CHAINS", "1")
+        u8, f32, pred, status, small, fused = ctx.both_chains(imgs, channel_order="BGR", compat=True, want_small20=True)
+        monkeypatch.delenv("NC_FUSED_CHAINS")
+        assert fused == expect_fused, (h, w, fused)
+        seen.add(fused)
+        e8, ef = ctx.resize_gray_norm(imgs)
+        ep, es, em = ctx.predict_chain(imgs, channel_order="BGR", compat=True, want_small20=True)
+        assert torch.equal(u8, e8) and torch.equal(f32, ef), (h, w)
+        assert torch.equal(pred, ep) and torch.equal(status, es) and torch.equal(small, em), (h, w)
+        o8, _ = R.train_chain(imgs[2].cpu().numpy())
+        assert np.array_equal(u8[2].cpu().numpy(), o8), (h, w)
+        # default (two launches): same bytes
+        u8b, f32b, predb, _, _, fb = ctx.both_chains(imgs, channel_order="BGR", compat=True)
+        assert not fb and torch.equal(u8b, u8) and torch.equal(f32b, f32) and torch.equal(predb, pred)
+    assert seen == {True, False}
+    # only one of the train-side outputs requested; empty batch; argument errors
+    imgs = dev(rng.integers(0, 256, (2, 768, 1024, 3), np.uint8))
+    full = ctx.both_chains(imgs)
+    import ctypes as C
+    from cloud_server_b200 import _lib
+    f32 = torch.zeros((2, 784), dtype=torch.float32, device="cuda")
+    pred = torch.zeros((2, 784), dtype=torch.float32, device="cuda")
+    rc = _lib.lib().nc_pp_both_chains(ctx.handle, C.c_void_p(imgs.data_ptr()), 2, 768, 1024, 3, 768 * 1024 * 3, 1, 0, None,
+                                      C.c_void_p(f32.data_ptr()), C.c_void_p(pred.data_ptr()), None, None, None, None)
+    assert rc == 0 and torch.equal(f32, full[1]) and torch.equal(pred, full[2])
+    rc = _lib.lib().nc_pp_both_chains(ctx.handle, C.c_void_p(imgs.data_ptr()), 2, 768, 1024, 3, 768 * 1024 * 3, 1, 0, None,
+                                      None, C.c_void_p(pred.data_ptr()), None, None, None, None)
+    assert rc == -1
+    empty = ctx.both_chains(imgs[:0])
+    assert empty[0].shape[0] == 0 and empty[5] is False
 
 
 def test_predict_chain_full_size_properties(ctx):
