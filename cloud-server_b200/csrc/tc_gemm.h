@@ -25,3 +25,9 @@ bool nc_tc_conv_supported(int mode, const nck::ConvGeom& g, const float* src, co
 void nc_tc_conv_dims(int mode, const nck::ConvGeom& g, int batch, int* M, int* N, int* K);
 int nc_tc_conv(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, const float* src, const float* wmat, float* out,
                const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3);
+
+// the same forward / dgrad products with the A operand loaded by TMA in im2col mode (conv_im2col.cu):
+// stride 1, output size == input size, reduced channel count a multiple of 32
+bool nc_tc_conv_i2c_supported(int mode, const nck::ConvGeom& g, const float* src, const float* wmat);
+int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, const float* src, const float* wmat, float* out,
+                   const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3);

@@ -33,9 +33,10 @@ def rel_err(a, b):
     return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-12))
 
 
-def make(name, ctx, seed=0):
+def make(name, ctx, seed=0, n=None):
     from cloud_server_b200.net import Net
-    cfg, h, w, c, n = CONFIGS[name]
+    cfg, h, w, c, n0 = CONFIGS[name]
+    n = n or n0
     rng = np.random.default_rng(seed)
     ref = tfref.Net(cfg, h, w, c)
     params = tfref.init_params(ref.param_specs, rng)
@@ -240,3 +241,28 @@ def test_library_communicator_world1_is_identity(ctx):
     np.testing.assert_array_equal(a.get_params(), b.get_params())
     a.detach_nccl()
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("name", ["lenet", "deep"])
+def test_conv_im2col_tma_kernel_agrees_with_gather_kernel(ctx, name, monkeypatch):
+    """Stride-1 SAME convolutions with Cin % 32 == 0 take the TMA-im2col kernel (conv_im2col.cu) for forward and
+    dgrad; NC_CONV_NO_IM2COL=1 forces the register-gather kernel (conv_tcgen05.cu).  Same products in the same order
+    of k blocks: logits and gradients agree to rounding (3xTF32 mode), at a batch that leaves a partial last tile."""
+    ref, net, flat, x, y = make(name, ctx, seed=6, n=37)
+    xt, yt = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    out = {}
+    for tag, env in (("i2c", None), ("gather", "1")):
+        if env:
+            monkeypatch.setenv("NC_CONV_NO_IM2COL", env)
+        else:
+            monkeypatch.delenv("NC_CONV_NO_IM2COL", raising=False)
+        net.set_math(1)
+        logits = net.forward(xt).cpu().numpy()
+        net.backward(xt, yt, "entropy")
+        out[tag] = (logits, net.grads.cpu().numpy().copy())
+    monkeypatch.delenv("NC_CONV_NO_IM2COL", raising=False)
+    assert rel_err(out["i2c"][0], out["gather"][0]) < 1e-5
+    assert rel_err(out["i2c"][1], out["gather"][1]) < 1e-5
+    params = ref.unflatten(flat)
+    logits, _ = ref.forward(x, params, keep=True)
+    assert rel_err(out["i2c"][0], logits) < 1e-4
