@@ -23,9 +23,12 @@
 namespace {
 
 constexpr int BM = 128, BK = 32;
-constexpr int kThreads = 192;
-// operand stages: 4 x 24 KB (1x) or 2 x 48 KB (3xTF32: hi and lo tiles) -- either way two CTAs fit one SM
-template <bool X3> struct StageCount { static constexpr int value = X3 ? 2 : 4; };
+constexpr int kThreads = 320;             // 10 warps: TMA, MMA, 8 x (lo split + epilogue)
+constexpr unsigned kConvThreads = 256;
+// operand ring: 4 raw stages (1x: 96 KB at BN = 64, two CTAs per SM); 3xTF32 adds two lo buffers (see gemm_tcgen05.cu:
+// the raw tile is the hi part) and, owning the SM anyway, runs the ring 6 deep at BN = 64 (192 KB)
+template <int BN, bool X3> struct StageCount { static constexpr int value = (X3 && BN == 64) ? 6 : 4; };
+constexpr int LO_SLOTS = 2;              // two: converting block i+1 overlaps the MMAs of block i
 
 struct I2cArgs {
     int W, H;              // spatial size (input == output: stride 1, SAME)
@@ -50,13 +53,14 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     constexpr bool DGRAD = MODE == 1, WGRAD = MODE == 2;
     constexpr bool A_MN = WGRAD;                 // wgrad: the im2col rows are k-rows (pixels) of an MN-major tile
     constexpr bool B_MN = !DGRAD;
-    constexpr int STAGES = StageCount<X3>::value;
+    constexpr int STAGES = StageCount<BN, X3>::value;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     constexpr unsigned A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
     constexpr unsigned HI_BYTES = A_BYTES + B_BYTES;
-    constexpr unsigned STAGE_BYTES = X3 ? 2 * HI_BYTES : HI_BYTES;   // [A_hi | B_hi | A_lo | B_lo]
+    constexpr unsigned STAGE_BYTES = HI_BYTES;                       // raw fp32 tiles [A | B]
+    constexpr unsigned LO_BASE = STAGES * STAGE_BYTES;               // 3xTF32: LO_SLOTS buffers [A_lo | B_lo] behind the ring
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[STAGES], s_tmem_full;
+    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[LO_SLOTS], s_loempty[LO_SLOTS], s_tmem_full;
     __shared__ unsigned s_tmem_base;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -68,7 +72,10 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(smem_u32(&s_full[s]), 1);
             mbar_init(smem_u32(&s_empty[s]), 1);
-            mbar_init(smem_u32(&s_ready[s]), 4);
+        }
+        for (int s = 0; s < LO_SLOTS; ++s) {
+            mbar_init(smem_u32(&s_ready[s]), kConvThreads / 32);
+            mbar_init(smem_u32(&s_loempty[s]), 1);
         }
         mbar_init(smem_u32(&s_tmem_full), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -153,7 +160,9 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
                 const unsigned ph = (unsigned)(i / STAGES) & 1u;
-                mbar_wait(smem_u32(X3 ? &s_ready[s] : &s_full[s]), ph);
+                const int l = i % LO_SLOTS;
+                if (X3) mbar_wait(smem_u32(&s_ready[l]), (unsigned)(i / LO_SLOTS) & 1u);   // raw tile landed AND its lo part is written
+                else mbar_wait(smem_u32(&s_full[s]), ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const unsigned sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 const unsigned sb = sa + A_BYTES;
@@ -163,15 +172,17 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     const unsigned long long db = B_MN ? umma_desc(sb + kk * 1024, 4096, 512, 1) : umma_desc(sb + kk * 32, 16, 1024);
                     const unsigned accum = (i > 0 || kk > 0) ? 1u : 0u;
                     if (X3) {
-                        const unsigned long long off = (unsigned long long)(HI_BYTES >> 4);
+                        // lo tiles: same layout as the raw ones, LO_BASE + l * HI_BYTES - s * STAGE_BYTES further on
+                        const unsigned long long off = (unsigned long long)((LO_BASE + (unsigned)l * HI_BYTES - (unsigned)s * STAGE_BYTES) >> 4);
                         umma_tf32(tmem, da + off, db, idesc, accum);         // lo(A) . hi(B)
                         umma_tf32(tmem, da, db + off, idesc, 1u);            // hi(A) . lo(B)
-                        umma_tf32(tmem, da, db, idesc, 1u);                  // hi(A) . hi(B)
+                        umma_tf32(tmem, da, db, idesc, 1u);                  // hi(A) . hi(B): raw bits, truncated by the tensor core
                     } else {
                         umma_tf32(tmem, da, db, idesc, accum);
                     }
                 }
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_empty[s])) : "memory");
+                if (X3) asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_loempty[l])) : "memory");
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_tmem_full)) : "memory");
         }
@@ -180,33 +191,35 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int q = warp & 3;
         const int row = m0 + q * 32 + lane;
         for (int i = 0; X3 && i < nkb; ++i) {
-            const int s = i % STAGES;
-            const unsigned ph = (unsigned)(i / STAGES) & 1u;
-            mbar_wait(smem_u32(&s_full[s]), ph);
-            uint4* p = reinterpret_cast<uint4*>(smem + (size_t)s * STAGE_BYTES);
-#pragma unroll 4
-            for (int j = (warp - 2) * 32 + lane; j < (int)(HI_BYTES / 16); j += 128) {
-                const uint4 v = p[j];
-                const uint4 hi = make_uint4((v.x + 0x1000u) & 0xFFFFE000u, (v.y + 0x1000u) & 0xFFFFE000u,
-                                            (v.z + 0x1000u) & 0xFFFFE000u, (v.w + 0x1000u) & 0xFFFFE000u);
-                p[j] = hi;
-                const uint4 lo = make_uint4(__float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x)),
-                                            __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y)),
-                                            __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z)),
-                                            __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w)));
-                p[j + HI_BYTES / 16] = lo;
+            const int s = i % STAGES, l = i % LO_SLOTS;
+            mbar_wait(smem_u32(&s_full[s]), (unsigned)(i / STAGES) & 1u);               // raw tiles landed
+            mbar_wait(smem_u32(&s_loempty[l]), ((unsigned)(i / LO_SLOTS) & 1u) ^ 1u);   // the MMAs that read this lo buffer are done
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const unsigned praw = smem_u32(smem + (size_t)s * STAGE_BYTES);
+            const unsigned plo = smem_u32(smem + LO_BASE + (size_t)l * HI_BYTES);
+#pragma unroll 3
+            for (unsigned j = (unsigned)(warp - 2) * 32u + (unsigned)lane; j < HI_BYTES / 16; j += kConvThreads) {
+                // lo = x - trunc_tf32(x): exact in fp32, at most 13 significant bits; the tensor core keeps its top 11
+                unsigned vx, vy, vz, vw;
+                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(vx), "=r"(vy), "=r"(vz), "=r"(vw) : "r"(praw + j * 16u));
+                const unsigned lx = __float_as_uint(__uint_as_float(vx) - __uint_as_float(vx & 0xFFFFE000u));
+                const unsigned ly = __float_as_uint(__uint_as_float(vy) - __uint_as_float(vy & 0xFFFFE000u));
+                const unsigned lz = __float_as_uint(__uint_as_float(vz) - __uint_as_float(vz & 0xFFFFE000u));
+                const unsigned lw = __float_as_uint(__uint_as_float(vw) - __uint_as_float(vw & 0xFFFFE000u));
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(plo + j * 16u), "r"(lx), "r"(ly), "r"(lz), "r"(lw) : "memory");
             }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core (async proxy) reads
             __syncwarp();
-            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[s])) : "memory");
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[l])) : "memory");
         }
         if (nkb > 0) {
             mbar_wait(smem_u32(&s_tmem_full), 0);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
         float* out = partial ? partial + (size_t)blockIdx.z * M * N : C;
+        // warps 2-5 take the even 32-column chunks, warps 6-9 the odd ones (a warp reads the TMEM lane quarter warp % 4)
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = (warp >= 6 ? 32 : 0); c0 < BN; c0 += 64) {
             if (n0 + c0 >= N) break;                     // uniform: tile columns past N hold products with foreign W rows
             unsigned r[32];
             if (nkb > 0) {
@@ -286,7 +299,7 @@ int get_encode_i2c(nc_ctx* ctx) {
 template <int BN, int MODE, bool X3>
 int launch_i2c(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const I2cArgs& ia, float* C, const float* bias, int M,
                int N, int nkb, int kbps, int splits, float* partial, cudaStream_t st) {
-    const size_t smem = (size_t)StageCount<X3>::value * (BM * BK * 4 + BN * BK * 4) * (X3 ? 2 : 1) + 1024;
+    const size_t smem = (size_t)(StageCount<BN, X3>::value + (X3 ? LO_SLOTS : 0)) * (BM * BK * 4 + BN * BK * 4) + 1024;
     auto kfn = conv_i2c_kernel<BN, MODE, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);

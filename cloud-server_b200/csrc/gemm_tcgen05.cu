@@ -23,8 +23,13 @@
 namespace {
 
 constexpr int BM = 128, BK = 32;          // BK * 4 B = 128 B = one swizzle-128B row
-constexpr int STAGES = 3;
-constexpr int kThreads = 192;             // 6 warps
+constexpr int kThreads = 320;             // 10 warps: TMA, MMA, 8 x (lo split + epilogue)
+constexpr unsigned kConvThreads = 256;
+// Operand ring.  1x: 3 stages of raw fp32 tiles.  3xTF32: the raw tile doubles as the "hi" part (kind::tf32 reads only the
+// top 19 bits of an fp32 operand, i.e. hi = trunc_tf32(x) costs nothing), so only lo = x - trunc(x) is materialised, into
+// a separate pair of buffers; the ring itself stays read-only for the converter warps, so the TMA runs 4 blocks ahead.
+template <int BN, bool X3> struct StageCount { static constexpr int value = (X3 && BN == 64) ? 6 : 4; };
+constexpr int LO_SLOTS = 2;              // two: converting block i+1 overlaps the MMAs of block i
 
 // X3 = true: "3xTF32" -- every fp32 operand is split into hi = rna_tf32(x) and lo = rna_tf32(x - hi) and
 // the product is accumulated as hi.hi + lo.hi + hi.lo (three MMAs per k step), which restores fp32-class
@@ -34,13 +39,15 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ C,
                  const float* __restrict__ bias, int M, int N, int K, int kb_per_slice, int act, float slope,
                  float* __restrict__ partial) {
+    constexpr int STAGES = StageCount<BN, X3>::value;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     constexpr unsigned A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
-    constexpr unsigned HI_BYTES = A_BYTES + B_BYTES;                 // TMA destination (hi parts after conversion)
-    constexpr unsigned STAGE_BYTES = X3 ? 2 * HI_BYTES : HI_BYTES;   // [A_hi | B_hi | A_lo | B_lo]
+    constexpr unsigned HI_BYTES = A_BYTES + B_BYTES;                 // TMA destination: raw fp32 tiles [A | B]
+    constexpr unsigned STAGE_BYTES = HI_BYTES;
+    constexpr unsigned LO_BASE = STAGES * STAGE_BYTES;               // 3xTF32: LO_SLOTS buffers [A_lo | B_lo] behind the ring
     // 1024-byte aligned stage buffers (swizzle atoms are 8 rows x 128 B)
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[STAGES], s_tmem_full;
+    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[LO_SLOTS], s_loempty[LO_SLOTS], s_tmem_full;
     __shared__ unsigned s_tmem_base;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -53,7 +60,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(smem_u32(&s_full[s]), 1);
             mbar_init(smem_u32(&s_empty[s]), 1);
-            mbar_init(smem_u32(&s_ready[s]), 4);       // one arrive per converter warp
+        }
+        for (int s = 0; s < LO_SLOTS; ++s) {
+            mbar_init(smem_u32(&s_ready[s]), kConvThreads / 32);       // one arrive per converter warp
+            mbar_init(smem_u32(&s_loempty[s]), 1);
         }
         mbar_init(smem_u32(&s_tmem_full), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -102,7 +112,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
                 const unsigned ph = (unsigned)(i / STAGES) & 1u;
-                mbar_wait(smem_u32(X3 ? &s_ready[s] : &s_full[s]), ph);      // 3x: operands landed AND split; 1x: as TMA left them
+                const int l = i % LO_SLOTS;
+                if (X3) mbar_wait(smem_u32(&s_ready[l]), (unsigned)(i / LO_SLOTS) & 1u);   // raw tile landed AND its lo part is written
+                else mbar_wait(smem_u32(&s_full[s]), ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const unsigned sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 const unsigned sb = sa + A_BYTES;
@@ -117,16 +129,18 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const unsigned accum = (i > 0 || kk > 0) ? 1u : 0u;
                     if (X3) {
                         // lo parts live HI_BYTES further on in the stage: same layout, same descriptors + offset
-                        const unsigned long long off = (unsigned long long)(HI_BYTES >> 4);
+                        // lo tiles: same layout as the raw ones, LO_BASE + l * HI_BYTES - s * STAGE_BYTES further on
+                        const unsigned long long off = (unsigned long long)((LO_BASE + (unsigned)l * HI_BYTES - (unsigned)s * STAGE_BYTES) >> 4);
                         umma_tf32(tmem, da + off, db, idesc, accum);         // lo(A) . hi(B)
                         umma_tf32(tmem, da, db + off, idesc, 1u);            // hi(A) . lo(B)
-                        umma_tf32(tmem, da, db, idesc, 1u);                  // hi(A) . hi(B)
+                        umma_tf32(tmem, da, db, idesc, 1u);                  // hi(A) . hi(B): raw bits, truncated by the tensor core
                     } else {
                         umma_tf32(tmem, da, db, idesc, accum);
                     }
                 }
                 // frees the smem stage once these MMAs have read it
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_empty[s])) : "memory");
+                if (X3) asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_loempty[l])) : "memory");
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_tmem_full)) : "memory");
         }
@@ -134,42 +148,40 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ===================== epilogue: warps 2..5 own TMEM lanes 32*(warp%4) .. +32 =====================
         const int q = warp & 3;
         const int row = m0 + q * 32 + lane;
-        // During the main loop these four warps round the staged fp32 operands to TF32 (round to nearest,
-        // ties away: cvt.rna) in place.  kind::tf32 otherwise TRUNCATES the 13 low mantissa bits, a
-        // one-sided error of ~1e-3 per product that does not average out over the dot product.
-        // (1x mode feeds the fp32 bits as they are: kind::tf32 truncates -- fine for gradients, stated for mode 2)
+        // kind::tf32 TRUNCATES the 13 low mantissa bits of its fp32 operands: alone that is a one-sided error of ~1e-3 per
+        // product which does not average out over the dot product (fine for gradients: 1x mode, stated for mode 2).
+        // 3xTF32: during the main loop these four warps write lo = x - trunc(x) of every staged operand; the raw tile
+        // itself is the hi part.
         for (int i = 0; X3 && i < nkb; ++i) {
-            const int s = i % STAGES;
-            const unsigned ph = (unsigned)(i / STAGES) & 1u;
-            mbar_wait(smem_u32(&s_full[s]), ph);
-            uint4* p = reinterpret_cast<uint4*>(smem + (size_t)s * STAGE_BYTES);
-#pragma unroll 4
-            for (int j = (warp - 2) * 32 + lane; j < (int)(HI_BYTES / 16); j += 128) {
-                // round to nearest TF32 = add half an ulp of the 10-bit mantissa, clear the 13 low bits (2 integer ops;
-                // cvt.rna.tf32.f32 expands to ~5).  The lo part is only truncated by the tensor core: no rounding needed.
-                const uint4 v = p[j];
-                const uint4 hi = make_uint4((v.x + 0x1000u) & 0xFFFFE000u, (v.y + 0x1000u) & 0xFFFFE000u,
-                                            (v.z + 0x1000u) & 0xFFFFE000u, (v.w + 0x1000u) & 0xFFFFE000u);
-                p[j] = hi;
-                if (X3) {
-                    const uint4 lo = make_uint4(__float_as_uint(__uint_as_float(v.x) - __uint_as_float(hi.x)),
-                                                __float_as_uint(__uint_as_float(v.y) - __uint_as_float(hi.y)),
-                                                __float_as_uint(__uint_as_float(v.z) - __uint_as_float(hi.z)),
-                                                __float_as_uint(__uint_as_float(v.w) - __uint_as_float(hi.w)));
-                    p[j + HI_BYTES / 16] = lo;
-                }
+            const int s = i % STAGES, l = i % LO_SLOTS;
+            mbar_wait(smem_u32(&s_full[s]), (unsigned)(i / STAGES) & 1u);               // raw tiles landed
+            mbar_wait(smem_u32(&s_loempty[l]), ((unsigned)(i / LO_SLOTS) & 1u) ^ 1u);   // the MMAs that read this lo buffer are done
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const unsigned praw = smem_u32(smem + (size_t)s * STAGE_BYTES);
+            const unsigned plo = smem_u32(smem + LO_BASE + (size_t)l * HI_BYTES);
+#pragma unroll 3
+            for (unsigned j = (unsigned)(warp - 2) * 32u + (unsigned)lane; j < HI_BYTES / 16; j += kConvThreads) {
+                // lo = x - trunc_tf32(x): exact in fp32, at most 13 significant bits; the tensor core keeps its top 11
+                unsigned vx, vy, vz, vw;
+                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(vx), "=r"(vy), "=r"(vz), "=r"(vw) : "r"(praw + j * 16u));
+                const unsigned lx = __float_as_uint(__uint_as_float(vx) - __uint_as_float(vx & 0xFFFFE000u));
+                const unsigned ly = __float_as_uint(__uint_as_float(vy) - __uint_as_float(vy & 0xFFFFE000u));
+                const unsigned lz = __float_as_uint(__uint_as_float(vz) - __uint_as_float(vz & 0xFFFFE000u));
+                const unsigned lw = __float_as_uint(__uint_as_float(vw) - __uint_as_float(vw & 0xFFFFE000u));
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(plo + j * 16u), "r"(lx), "r"(ly), "r"(lz), "r"(lw) : "memory");
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core (async proxy) reads
             __syncwarp();
-            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[s])) : "memory");
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&s_ready[l])) : "memory");
         }
         if (nkb > 0) {
             mbar_wait(smem_u32(&s_tmem_full), 0);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
         float* out = partial ? partial + (size_t)blockIdx.z * M * N : C;
+        // warps 2-5 take the even 32-column chunks, warps 6-9 the odd ones (a warp reads the TMEM lane quarter warp % 4)
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = (warp >= 6 ? 32 : 0); c0 < BN; c0 += 64) {
             unsigned r[32];
             if (nkb > 0) {
                 const unsigned taddr = tmem + ((unsigned)(q * 32) << 16) + (unsigned)c0;
@@ -229,7 +241,7 @@ __global__ void tc_reduce_kernel(float* __restrict__ dst, const float* __restric
 template <int BN, bool A_MN, bool B_MN, bool X3>
 int launch(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, float* C, const float* bias, int M, int N, int K,
            int kbps, int splits, int act, float slope, float* partial, cudaStream_t st) {
-    const size_t smem = (size_t)STAGES * (BM * BK * 4 + BN * BK * 4) * (X3 ? 2 : 1) + 1024;
+    const size_t smem = (size_t)(StageCount<BN, X3>::value + (X3 ? LO_SLOTS : 0)) * (BM * BK * 4 + BN * BK * 4) + 1024;
     auto kfn = gemm_tf32_kernel<BN, A_MN, B_MN, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);

@@ -18,7 +18,9 @@ def _check(ctx, m, k, n, ta, tb, bias, seed, precision=0):
     B = b.double().cpu().T if tb else b.double().cpu()
     want = A @ B + (bv.double().cpu() if bias else 0)
     err = float((got - want).abs().max() / want.abs().max())
-    assert err < (3e-6 if precision == 0 else 4e-3), (m, k, n, ta, tb, precision, err)   # 1x: truncated TF32 operands
+    # 3x: hi = the operand as the tensor core truncates it, lo = the exact remainder (its own truncation and the dropped
+    # lo.lo term are one-sided, ~2^-21 each); 1x: truncated TF32 operands
+    assert err < (5e-6 if precision == 0 else 4e-3), (m, k, n, ta, tb, precision, err)
     return err
 
 
