@@ -143,6 +143,7 @@ struct nc_net {
     float* ws = nullptr; size_t ws_bytes = 0;              // split-K partial sums (scratch)
     float* col = nullptr; size_t col_bytes = 0;            // im2col of the first (few-channel) conv layer, tensor path
     // data parallel (nc_net_attach_nccl): communicator + 2*max(norm channels) floats for the cross-rank moments
+    bool fuse_first = false;    // layers 0..2 are conv (few channels, stride 1) -> relu -> pool 2x2/2: one kernel each way
     void* comm = nullptr; int rank = 0, world = 1;
     float* dp_buf = nullptr;
     std::string err;
@@ -292,6 +293,14 @@ static int build_layers(nc_net* net, const JVal& cfg) {
     for (size_t i = 0; i + 1 < net->layers.size(); ++i)
         if (net->layers[i].kind == L_ACT && net->layers[i].act == ACT_RELU && net->layers[i + 1].kind == L_POOL)
             net->layers[i].relu_into_pool = true;
+    if (net->layers.size() >= 3) {
+        const Layer& c = net->layers[0]; const Layer& a = net->layers[1]; const Layer& p = net->layers[2];
+        const size_t tile = (size_t)(2 * p.oh + c.fh - 1) * (2 * p.ow + c.fw - 1) * c.ic * sizeof(float);
+        net->fuse_first = c.kind == L_CONV && c.ic <= 4 && c.fh * c.fw * c.ic <= 32 && c.sh == 1 && c.sw == 1 &&
+                          a.kind == L_ACT && a.relu_into_pool && p.kind == L_POOL && p.fh == 2 && p.fw == 2 && p.sh == 2 &&
+                          p.sw == 2 && p.pt == 0 && p.pl == 0 && p.oh * 2 >= p.ih && p.ow * 2 >= p.iw && tile <= 40 * 1024 &&
+                          !getenv("NC_NO_FIRST_FUSION");
+    }
     // arena offsets
     int64_t act = 0, aux = 0, stat = 0, mx = (int64_t)net->in_h * net->in_w * net->in_c;
     for (auto& L : net->layers) {
@@ -546,6 +555,14 @@ static int tc_conv_try(nc_net* net, int mode, const Layer& L, int n, const float
 static ConvGeom geom(const Layer& L) { return ConvGeom{L.ih, L.iw, L.ic, L.oh, L.ow, L.oc, L.fh, L.fw, L.sh, L.sw, L.pt, L.pl}; }
 static PoolGeom pgeom(const Layer& L) { return PoolGeom{L.ih, L.iw, L.ic, L.oh, L.ow, L.fh, L.fw, L.sh, L.sw, L.pt, L.pl}; }
 
+static FirstGeom first_geom(const Layer& c, const Layer& p) {
+    FirstGeom g;
+    g.ih = c.ih; g.iw = c.iw; g.ic = c.ic; g.fh = c.fh; g.fw = c.fw; g.pt = c.pt; g.pl = c.pl;
+    g.coh = c.oh; g.cow = c.ow; g.oc = c.oc; g.poh = p.oh; g.pw_ = p.ow;
+    g.th = 2 * p.oh + c.fh - 1; g.tw = 2 * p.ow + c.fw - 1;
+    return g;
+}
+
 // ------------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------------
@@ -555,9 +572,31 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
     const int sms = net->ctx->sm_count;
     const float* in = x;
     bool pending_relu = false;
+    int li = -1;
     for (auto& L : net->layers) {
+        ++li;
         if (L.kind == L_ACT && L.relu_into_pool) { pending_relu = true; continue; }   // `in` stays the pre-activation
+        if (net->fuse_first && li == 0) continue;                                     // computed inside the pool launch below
         float* out = act_ptr(net, L);
+        if (net->fuse_first && li == 2) {
+            const Layer& c = net->layers[0];
+            const FirstGeom fg = first_geom(c, L);
+            const size_t smem = (size_t)fg.th * fg.tw * fg.ic * sizeof(float);
+            const int blocks = n < sms * 4 ? n : sms * 4;
+            const float* cw = net->params + c.w_off;
+            const float* cb = c.b_off >= 0 ? net->params + c.b_off : nullptr;
+            uint8_t* argp = net->aux + L.aux_off * net->cap;
+            const bool c1 = c.ic == 1 && (fg.tw & 1) == 0;       // compile-time filter variants: 5x5 and 3x3 on one channel
+            for (int ob = 0; ob < (c.oc + 31) / 32; ++ob) {
+                if (c1 && c.fh == 5 && c.fw == 5) first_conv_relu_pool_fwd_c1_kernel<5, 5><<<blocks, 256, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
+                else if (c1 && c.fh == 3 && c.fw == 3) first_conv_relu_pool_fwd_c1_kernel<3, 3><<<blocks, 256, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
+                else first_conv_relu_pool_fwd_kernel<<<blocks, 256, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
+                NET_LAUNCH(net);
+            }
+            pending_relu = false;
+            in = out;
+            continue;
+        }
         const float* W = L.w_off >= 0 ? net->params + L.w_off : nullptr;
         const float* Bp = L.b_off >= 0 ? net->params + L.b_off : nullptr;
         switch (L.kind) {
@@ -703,7 +742,40 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         const float* W = L.w_off >= 0 ? net->params + L.w_off : nullptr;
         float* dW = L.w_off >= 0 ? net->grads + L.w_off : nullptr;
         float* dB = L.b_off >= 0 ? net->grads + L.b_off : nullptr;
-        const bool need_dx = li > 0;
+        bool need_dx = li > 0;
+        if (net->fuse_first && li == 2) {
+            // fused first block: `d` (gradient of the pooled output) goes straight to the conv weight gradient below
+            skip_fused_relu = true;
+            continue;
+        }
+        if (net->fuse_first && li == 0) {
+            const Layer& P = net->layers[2];
+            const FirstGeom fg = first_geom(L, P);
+            const size_t smem = (size_t)fg.th * fg.tw * fg.ic * sizeof(float);
+            const int K = L.fh * L.fw * L.ic, N = L.oc;
+            const int blocks = n < sms * 2 ? n : sms * 2;
+            rc = reserve_ws(net, (size_t)blocks * (K + 1) * N * sizeof(float));
+            if (rc != NC_OK) return rc;
+            float* pw = net->ws;
+            float* pb = net->ws + (size_t)blocks * K * N;
+            const uint8_t* argp = net->aux + P.aux_off * net->cap;
+            const int npool = fg.poh * fg.pw_;
+            const size_t smem_c1 = (size_t)((fg.th * fg.tw + 3) & ~3) * sizeof(float) + (size_t)npool * 32 * 5;
+            const bool c1 = L.ic == 1 && (fg.tw & 1) == 0 && smem_c1 <= 48 * 1024 && ((L.fh == 5 && L.fw == 5) || (L.fh == 3 && L.fw == 3));
+            for (int ob = 0; ob < (N + 31) / 32; ++ob) {
+                if (c1 && L.fh == 5) first_conv_wgrad_from_pool_c1_kernel<5, 5><<<blocks, 256, smem_c1, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
+                else if (c1) first_conv_wgrad_from_pool_c1_kernel<3, 3><<<blocks, 256, smem_c1, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
+                else first_conv_wgrad_from_pool_kernel<<<blocks, 256, smem, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
+                NET_LAUNCH(net);
+            }
+            reduce_partials_warp_kernel<<<(K * N + 7) / 8, 256, 0, st>>>(dW, pw, blocks, (long long)K * N);
+            NET_LAUNCH(net);
+            if (dB) {
+                reduce_partials_warp_kernel<<<(N + 7) / 8, 256, 0, st>>>(dB, pb, blocks, N);
+                NET_LAUNCH(net);
+            }
+            continue;
+        }
         switch (L.kind) {
         case L_CONNECT: {
             const int M = n, N = L.oc, K = (int)L.in_size;

@@ -592,6 +592,265 @@ __global__ void maxpool_bwd_tiled_kernel(const float* __restrict__ dy, const uin
 }
 
 // ---------------------------------------------------------------------------------------------
+// first block fused: conv2d (few input channels, stride 1) -> relu -> max_pool 2x2 / 2
+// (cnn() on the usual LeNet-style net_config, construct_distribute.py:208-243: the first conv + active + pool).
+// The un-pooled activation (N x 28 x 28 x 32 floats for LeNet) is never written or read:
+//   forward   one CTA per picture: the zero-padded input tile sits in shared memory, lane = output channel keeps its
+//             <= 32 weights in registers, a warp computes the 2x2 conv outputs of one pooled pixel from broadcast
+//             shared loads and stores the pooled row (128 B) + argmax bytes.  Same fma order as conv_smallc_fwd_tile_kernel
+//             and the same first-maximum rule as maxpool_fwd_kernel: identical bytes.
+//   backward  weight / bias gradient straight from the POOLED gradient: only the argmax position of each window carries
+//             gradient (and only if the pooled value is > 0), so a pooled pixel costs one 25-tap pass instead of four.
+// ---------------------------------------------------------------------------------------------
+struct FirstGeom {
+    int ih, iw, ic;          // input
+    int fh, fw, pt, pl;      // conv filter and padding before
+    int coh, cow, oc;        // conv output
+    int poh, pw_;            // pooled output (pw_ = pooled width)
+    int th, tw;              // shared tile: rows / columns of input positions incl. padding (2*poh + fh - 1, 2*pw_ + fw - 1)
+};
+
+__device__ __forceinline__ void first_load_tile(float* tile, const float* __restrict__ xi, const FirstGeom& g) {
+    const int total = g.th * g.tw * g.ic;
+    for (int e = threadIdx.x; e < total; e += blockDim.x) {
+        const int ch = e % g.ic; const int q = e / g.ic;
+        const int c = q % g.tw, r = q / g.tw;
+        const int iy = r - g.pt, ix = c - g.pl;
+        tile[e] = (iy >= 0 && iy < g.ih && ix >= 0 && ix < g.iw) ? __ldg(xi + ((long long)iy * g.iw + ix) * g.ic + ch) : 0.0f;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+first_conv_relu_pool_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                                float* __restrict__ y, uint8_t* __restrict__ arg, FirstGeom g, int n, int ob) {
+    extern __shared__ float tile[];
+    const int T = g.fh * g.fw * g.ic;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    float wreg[32];
+    int off[32];                                  // tile offset of tap t relative to the window origin (uniform)
+#pragma unroll
+    for (int t = 0; t < 32; ++t) {
+        wreg[t] = (t < T && co < g.oc) ? __ldg(w + (long long)t * g.oc + co) : 0.0f;
+        const int tt = t < T ? t : 0;
+        const int c = tt % g.ic, ij = tt / g.ic;
+        off[t] = ((ij / g.fw) * g.tw + (ij % g.fw)) * g.ic + c;
+    }
+    const float bv = (bias && co < g.oc) ? __ldg(bias + co) : 0.0f;
+    const int rowp = g.tw * g.ic;                 // one tile row
+    const int npool = g.poh * g.pw_;
+    for (int img = blockIdx.x; img < n; img += gridDim.x) {
+        __syncthreads();
+        first_load_tile(tile, x + (long long)img * g.ih * g.iw * g.ic, g);
+        __syncthreads();
+        for (int pp = warp; pp < npool; pp += 8) {
+            const int py = pp / g.pw_, px = pp - py * g.pw_;
+            const float* b00 = tile + (2 * py) * rowp + (2 * px) * g.ic;
+            float a00 = 0.0f, a01 = 0.0f, a10 = 0.0f, a11 = 0.0f;
+#pragma unroll
+            for (int t = 0; t < 32; ++t) {
+                if (t < T) {
+                    const float* q = b00 + off[t];
+                    a00 = fmaf(q[0], wreg[t], a00);
+                    a01 = fmaf(q[g.ic], wreg[t], a01);
+                    a10 = fmaf(q[rowp], wreg[t], a10);
+                    a11 = fmaf(q[rowp + g.ic], wreg[t], a11);
+                }
+            }
+            // relu, then the first maximum of the window in scan order; positions past the conv output do not exist
+            const bool vy = 2 * py + 1 < g.coh, vx = 2 * px + 1 < g.cow;
+            float best = fmaxf(a00 + bv, 0.0f); int bi = 0;
+            if (vx) { const float v = fmaxf(a01 + bv, 0.0f); if (v > best) { best = v; bi = 1; } }
+            if (vy) { const float v = fmaxf(a10 + bv, 0.0f); if (v > best) { best = v; bi = 2; } }
+            if (vy && vx) { const float v = fmaxf(a11 + bv, 0.0f); if (v > best) { best = v; bi = 3; } }
+            if (co < g.oc) {
+                const long long o = ((long long)img * npool + pp) * g.oc + co;
+                y[o] = best;
+                arg[o] = (uint8_t)bi;
+            }
+        }
+    }
+}
+
+// Single input channel, compile-time filter (5x5 / 3x3: the LeNet-style heads): the (FH+1) x (FW+1) input patch of a
+// pooled pixel is read with 8-byte shared loads into registers (18 loads instead of 100 for 5x5) and every weight is used
+// four times from its register.  Same fma order per output as the generic kernel: identical bytes.
+template <int FH, int FW>
+__global__ void __launch_bounds__(256)
+first_conv_relu_pool_fwd_c1_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                                   float* __restrict__ y, uint8_t* __restrict__ arg, FirstGeom g, int n, int ob) {
+    extern __shared__ __align__(16) float tile[];
+    constexpr int T = FH * FW, PWD = (FW + 2) & ~1;          // patch columns loaded (even)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    float wreg[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) wreg[t] = co < g.oc ? __ldg(w + (long long)t * g.oc + co) : 0.0f;
+    const float bv = (bias && co < g.oc) ? __ldg(bias + co) : 0.0f;
+    const int npool = g.poh * g.pw_;
+    for (int img = blockIdx.x; img < n; img += gridDim.x) {
+        __syncthreads();
+        first_load_tile(tile, x + (long long)img * g.ih * g.iw, g);
+        __syncthreads();
+        for (int pp = warp; pp < npool; pp += 8) {
+            const int py = pp / g.pw_, px = pp - py * g.pw_;
+            const float* b = tile + (2 * py) * g.tw + 2 * px;        // tw even, 2 px even: 8-byte aligned
+            float pt[FH + 1][PWD];
+#pragma unroll
+            for (int r = 0; r <= FH; ++r)
+#pragma unroll
+                for (int c = 0; c < PWD; c += 2) {
+                    const float2 v = *reinterpret_cast<const float2*>(b + r * g.tw + c);
+                    pt[r][c] = v.x; pt[r][c + 1] = v.y;
+                }
+            float a00 = 0.0f, a01 = 0.0f, a10 = 0.0f, a11 = 0.0f;
+#pragma unroll
+            for (int r = 0; r < FH; ++r)
+#pragma unroll
+                for (int c = 0; c < FW; ++c) {
+                    const float wv = wreg[r * FW + c];
+                    a00 = fmaf(pt[r][c], wv, a00);
+                    a01 = fmaf(pt[r][c + 1], wv, a01);
+                    a10 = fmaf(pt[r + 1][c], wv, a10);
+                    a11 = fmaf(pt[r + 1][c + 1], wv, a11);
+                }
+            const bool vy = 2 * py + 1 < g.coh, vx = 2 * px + 1 < g.cow;
+            float best = fmaxf(a00 + bv, 0.0f); int bi = 0;
+            if (vx) { const float v = fmaxf(a01 + bv, 0.0f); if (v > best) { best = v; bi = 1; } }
+            if (vy) { const float v = fmaxf(a10 + bv, 0.0f); if (v > best) { best = v; bi = 2; } }
+            if (vy && vx) { const float v = fmaxf(a11 + bv, 0.0f); if (v > best) { best = v; bi = 3; } }
+            if (co < g.oc) {
+                const long long o = ((long long)img * npool + pp) * g.oc + co;
+                y[o] = best;
+                arg[o] = (uint8_t)bi;
+            }
+        }
+    }
+}
+
+// The matching weight gradient: the picture's masked pooled gradient and argmax bytes are staged in shared memory by the
+// whole CTA first (one exposed global latency per picture instead of one per pooled pixel), taps at compile-time offsets.
+// dynamic smem: tile | gm[npool][32] floats | am[npool][32] bytes
+template <int FH, int FW>
+__global__ void __launch_bounds__(256)
+first_conv_wgrad_from_pool_c1_kernel(const float* __restrict__ x, const float* __restrict__ dpool, const uint8_t* __restrict__ arg,
+                                     const float* __restrict__ pooled, float* __restrict__ partial_w, float* __restrict__ partial_b,
+                                     FirstGeom g, int n, int ob) {
+    extern __shared__ __align__(16) float tile[];
+    __shared__ float red[8][33];
+    constexpr int T = FH * FW;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    const int npool = g.poh * g.pw_;
+    const int tile_floats = (g.th * g.tw + 3) & ~3;
+    float* gm = tile + tile_floats;
+    uint8_t* am = reinterpret_cast<uint8_t*>(gm + (size_t)npool * 32);
+    float acc[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) acc[t] = 0.0f;
+    float accb = 0.0f;
+    for (int img = blockIdx.x; img < n; img += gridDim.x) {
+        __syncthreads();
+        first_load_tile(tile, x + (long long)img * g.ih * g.iw, g);
+        for (int e = threadIdx.x; e < npool * 32; e += 256) {
+            const int pp = e >> 5, c = ob * 32 + (e & 31);
+            float gv = 0.0f; uint8_t a = 0;
+            if (c < g.oc) {
+                const long long o = ((long long)img * npool + pp) * g.oc + c;
+                gv = __ldg(dpool + o);
+                if (!(__ldg(pooled + o) > 0.0f)) gv = 0.0f;          // relu under the pool
+                a = arg[o];
+            }
+            gm[e] = gv; am[e] = a;
+        }
+        __syncthreads();
+        for (int pp = warp; pp < npool; pp += 8) {
+            const int py = pp / g.pw_, px = pp - py * g.pw_;
+            const float gv = gm[pp * 32 + lane];
+            const int a = am[pp * 32 + lane];
+            accb += gv;
+            const float* q0 = tile + (2 * py + (a >> 1)) * g.tw + 2 * px + (a & 1);
+#pragma unroll
+            for (int r = 0; r < FH; ++r)
+#pragma unroll
+                for (int c = 0; c < FW; ++c) acc[r * FW + c] = fmaf(q0[r * g.tw + c], gv, acc[r * FW + c]);
+        }
+    }
+#pragma unroll
+    for (int t = 0; t <= T; ++t) {
+        __syncthreads();
+        red[warp][lane] = t < T ? acc[t < T ? t : 0] : accb;
+        __syncthreads();
+        if (warp == 0 && co < g.oc) {
+            float sum = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) sum += red[k][lane];
+            if (t < T) partial_w[(size_t)blockIdx.x * T * g.oc + (size_t)t * g.oc + co] = sum;
+            else partial_b[(size_t)blockIdx.x * g.oc + co] = sum;
+        }
+    }
+}
+
+// partial_w[block][T*oc] / partial_b[block][oc] for output-channel block `ob` (summed by reduce_partials_warp_kernel)
+__global__ void __launch_bounds__(256)
+first_conv_wgrad_from_pool_kernel(const float* __restrict__ x, const float* __restrict__ dpool, const uint8_t* __restrict__ arg,
+                                  const float* __restrict__ pooled, float* __restrict__ partial_w, float* __restrict__ partial_b,
+                                  FirstGeom g, int n, int ob) {
+    extern __shared__ float tile[];
+    __shared__ float red[8][33];
+    const int T = g.fh * g.fw * g.ic;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    float acc[32];
+    int off[32];
+#pragma unroll
+    for (int t = 0; t < 32; ++t) {
+        acc[t] = 0.0f;
+        const int tt = t < T ? t : 0;
+        const int c = tt % g.ic, ij = tt / g.ic;
+        off[t] = ((ij / g.fw) * g.tw + (ij % g.fw)) * g.ic + c;
+    }
+    float accb = 0.0f;
+    const int rowp = g.tw * g.ic;
+    const int npool = g.poh * g.pw_;
+    for (int img = blockIdx.x; img < n; img += gridDim.x) {
+        __syncthreads();
+        first_load_tile(tile, x + (long long)img * g.ih * g.iw * g.ic, g);
+        __syncthreads();
+        for (int pp = warp; pp < npool; pp += 8) {
+            const int py = pp / g.pw_, px = pp - py * g.pw_;
+            float gv = 0.0f; int a = 0;
+            if (co < g.oc) {
+                const long long o = ((long long)img * npool + pp) * g.oc + co;
+                gv = __ldg(dpool + o);
+                if (!(__ldg(pooled + o) > 0.0f)) gv = 0.0f;        // relu under the pool
+                a = arg[o];
+            }
+            accb += gv;
+            const float* q0 = tile + (2 * py + (a >> 1)) * rowp + (2 * px + (a & 1)) * g.ic;
+#pragma unroll
+            for (int t = 0; t < 32; ++t)
+                if (t < T) acc[t] = fmaf(q0[off[t]], gv, acc[t]);
+        }
+    }
+#pragma unroll
+    for (int t = 0; t <= 32; ++t) {
+        if (t < T || t == 32) {
+            __syncthreads();
+            red[warp][lane] = t < 32 ? acc[t < 32 ? t : 0] : accb;
+            __syncthreads();
+            if (warp == 0 && co < g.oc) {
+                float sum = 0.0f;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) sum += red[k][lane];
+                if (t < 32) partial_w[(size_t)blockIdx.x * T * g.oc + (size_t)t * g.oc + co] = sum;
+                else partial_b[(size_t)blockIdx.x * g.oc + co] = sum;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // activations (active(), construct_distribute.py:133-152)
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float act_apply(int fn, float x, float slope) {

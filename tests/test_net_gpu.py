@@ -266,3 +266,43 @@ def test_conv_im2col_tma_kernel_agrees_with_gather_kernel(ctx, name, monkeypatch
     params = ref.unflatten(flat)
     logits, _ = ref.forward(x, params, keep=True)
     assert rel_err(out["i2c"][0], logits) < 1e-4
+
+
+@pytest.mark.parametrize("n", [1, 37])
+def test_fused_first_block_equals_separate_kernels(ctx, n, monkeypatch):
+    """conv (few input channels, stride 1) -> relu -> max_pool 2x2/2 at the head of a net runs as one kernel each way
+    (first_conv_relu_pool_fwd_kernel / first_conv_wgrad_from_pool_kernel).  Same fma order and first-maximum rule as
+    the separate kernels: logits bit-identical in math mode 0; gradients equal to rounding (different summation order)."""
+    from cloud_server_b200.net import Net
+    cfgs = [tfref.LENET,
+            {"middle_layer": [{"layer": "conv", "filter": [3, 3, 40]}, {"layer": "active", "active_func": "relu"},
+                              {"layer": "pool"}, {"layer": "connect", "hidden": 32}]}]     # no bias, 2 output-channel blocks
+    cfgs.append({"middle_layer": [{"layer": "conv", "filter": [3, 3, 8], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
+                                  {"layer": "pool"}, {"layer": "connect", "hidden": 16}]})   # 3x3 on one channel, odd picture size
+    for cfg, (h, w, c) in zip(cfgs, [(28, 28, 1), (13, 11, 3), (15, 11, 1)]):
+        rng = np.random.default_rng(8)
+        x = torch.from_numpy(rng.random((n, h * w * c), dtype=np.float32)).cuda()
+        y = torch.nn.functional.one_hot(torch.from_numpy(rng.integers(0, 10, n)).cuda(), 10).float()
+        monkeypatch.setenv("NC_NO_FIRST_FUSION", "1")
+        plain = Net(cfg, ctx, h, w, c, seed=3)
+        monkeypatch.delenv("NC_NO_FIRST_FUSION")
+        fused = Net(cfg, ctx, h, w, c, seed=3)
+        launches = []
+        for net in (plain, fused):
+            net.set_math(0)
+            before = ctx.launches
+            logits = net.forward(x)
+            launches.append(ctx.launches - before)
+            net.backward(x, y, "entropy")
+        assert launches[1] < launches[0]                      # the fused net really took the other path
+        assert torch.equal(plain.forward(x), fused.forward(x))
+        assert rel_err(fused.grads.cpu().numpy(), plain.grads.cpu().numpy()) < 1e-5
+        # and against the oracle
+        ref = tfref.Net(cfg, h, w, c)
+        params = ref.unflatten(fused.get_params())
+        lg, cache = ref.forward(x.cpu().numpy(), params, keep=True)
+        assert rel_err(fused.forward(x).cpu().numpy(), lg) < 1e-5
+        _, dz = ref.loss_and_grad(lg, y.cpu().numpy(), "entropy")
+        gref = ref.flatten(ref.backward(dz, params, cache))
+        assert rel_err(fused.grads.cpu().numpy(), gref) < 1e-4
+        plain.close(); fused.close()
