@@ -256,11 +256,27 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
         cnt = [0]
         ms = time_steps(torch, step, steps, args.warmup, dist_on, counter=lambda: ctx.launches, count_out=cnt)
         ms = max_over_ranks(torch, ms, dist_on, device)
+        eager_per = ms / steps
+        graph = None
+        if world == 1 and not args.no_graph:
+            # the same step replayed from a CUDA graph (one graph launch instead of ~30 kernel launches); each step still
+            # copies its own batch into the graph's input buffers
+            from cloud_server_b200.net import GraphedTrainStep
+            graph = GraphedTrainStep(net, local, "entropy", "compat")
+
+            def gstep():
+                b = state["i"] % nb
+                state["i"] += 1
+                lo = b * global_batch
+                graph(xs[lo:lo + local], ys[lo:lo + local])
+
+            ms = time_steps(torch, gstep, steps, args.warmup, dist_on)
         per = ms / steps
         byts = lenet_step_bytes(local)
         out[key] = {
             "value": global_batch * steps / (ms * 1e-3), "unit": "images/s", "ms_per_step": per, "global_batch": global_batch,
             "per_gpu_batch": local, "optimizer": "Adagrad(1e-4) (what the reference runs)", "gpu_launches_per_step": cnt[0] / steps,
+            "cuda_graph": graph is not None, "ms_per_step_eager": eager_per,
             "math": {0: "fp32 simt", 1: "tcgen05 3xTF32 (fp32-class accuracy)", 2: "tcgen05 1xTF32", 3: "tcgen05 3xTF32 forward + 1xTF32 gradients"}[args.math],
             "roofline": {"bound": "hbm", "achieved": byts / (per * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": byts / (per * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts,
@@ -281,7 +297,18 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
         xd, yd = torch.empty_like(xs[:256]), torch.empty_like(ys[:256])
         lh = torch.zeros(1).pin_memory()
 
+        gstep = None
+        if not args.no_graph:
+            from cloud_server_b200.net import GraphedTrainStep
+            gstep = GraphedTrainStep(net, 256, "entropy", "compat")
+
         def e2e():
+            if gstep is not None:      # pinned host batch -> the graph's input buffers -> replay -> loss back to the host
+                gstep.x.copy_(xb, non_blocking=True)
+                gstep.y.copy_(yb, non_blocking=True)
+                gstep.graph.replay()
+                lh.copy_(gstep.loss, non_blocking=True)
+                return
             xd.copy_(xb, non_blocking=True)
             yd.copy_(yb, non_blocking=True)
             loss, _ = net.train_step(xd, yd, "entropy", "compat")
@@ -479,6 +506,7 @@ def main():
     ap.add_argument("--e2e-batch", type=int, default=1024, help="uploads per e2e step (host pinned)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="time the train step eagerly only (default: eager and CUDA-graph replay)")
     ap.add_argument("--math", type=int, default=3, help="CNN math: 0 fp32 SIMT, 1 tcgen05 3xTF32, 2 tcgen05 1xTF32, 3 (default) 3xTF32 forward + 1xTF32 gradients")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -59,6 +59,7 @@ _SIGS = {
     "nc_net_train_step": (C.c_int, [C.c_void_p, c_f32p, c_f32p, C.c_int, C.c_int, C.c_int, C.c_float, c_f32p, c_i32p,
                                     C.c_void_p]),
     "nc_net_global_step": (C.c_int64, [C.c_void_p]),
+    "nc_net_advance_step": (C.c_int, [C.c_void_p, C.c_int64]),
     "nc_nccl_unique_id": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p]),
     "nc_net_attach_nccl": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int]),
     "nc_net_allreduce_grads": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -946,6 +946,13 @@ extern "C" int nc_net_apply(nc_net* net, int opt, float lr, void* stream) {
     return NC_OK;
 }
 
+extern "C" int nc_net_advance_step(nc_net* net, int64_t k) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (k < 0) return net_err(net, NC_EINVAL, "k must be >= 0");
+    net->global_step += k;
+    return NC_OK;
+}
+
 extern "C" int nc_net_train_step(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name, int opt, float lr,
                                  float* loss_out, int32_t* correct_out, void* stream) {
     if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");

@@ -169,6 +169,51 @@ class Net:
         _lib.check(self.ctx.handle, _lib.lib().nc_net_allreduce_grads(self.handle, self.ctx._stream()))
 
 
+class GraphedTrainStep:
+    """One sess.run(train_op) (construct_distribute.py:413) captured into a CUDA graph and replayed: the ~30 kernel
+    launches of a LeNet step cost one graph launch.  Fixed batch size, loss and optimizer; Adagrad (what the reference
+    runs) or SGD only -- Adam's step size is a host-side function of global_step.  Single device.
+
+        step = GraphedTrainStep(net, 256)
+        loss, hits = step(x, y)          # x, y: CUDA tensors [256, features], [256, classes]; copied into the graph's inputs
+    """
+
+    def __init__(self, net, batch, loss_name="entropy", opt="compat", lr=1e-4):
+        oid = 0 if opt == "compat" else (OPT[opt] if isinstance(opt, str) else int(opt))
+        if oid == 2:
+            raise ValueError("Adam's bias-corrected step size changes every step on the host: it cannot be replayed from a graph")
+        if net.world > 1:
+            raise ValueError("a net attached to a communicator is stepped eagerly")
+        self.net, self.batch = net, int(batch)
+        dev = net.ctx.tdev
+        self.x = torch.zeros((self.batch, net.in_features), dtype=torch.float32, device=dev)
+        self.y = torch.zeros((self.batch, net.classes), dtype=torch.float32, device=dev)
+        self.y[:, 0] = 1.0
+        # one eager step on a side stream sizes every workspace (nothing may allocate during capture); its effect on
+        # the weights, the optimizer state and the step counter is undone afterwards
+        w0, st0, gs0 = net.params.clone(), net.get_state(oid), net.global_step
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            net.train_step(self.x, self.y, loss_name, opt, lr)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        net.params.copy_(w0)
+        net.set_state(oid, st0, gs0)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss, self.correct = net.train_step(self.x, self.y, loss_name, opt, lr)
+        net.set_state(oid, None, gs0)      # the captured call bumped the host-side counter without running anything
+        self._oid = oid
+
+    def __call__(self, x, y):
+        self.x.copy_(x.reshape(self.batch, -1), non_blocking=True)
+        self.y.copy_(y.reshape(self.batch, -1), non_blocking=True)
+        self.graph.replay()
+        _lib.check(self.net.ctx.handle, _lib.lib().nc_net_advance_step(self.net.handle, 1))
+        return self.loss, self.correct
+
+
 def find_libnccl():
     """Path of the NCCL this process should share with torch: the one already mapped if torch loaded it,
     else the wheel's copy, else the loader's default."""

@@ -207,6 +207,13 @@ int nc_net_apply(nc_net* net, int opt, float lr, void* stream);
 int nc_net_train_step(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name,
                       int opt, float lr, float* loss_out, int32_t* correct_out, void* stream);
 int64_t nc_net_global_step(nc_net* net);
+/* global_step += k without running anything.  For hosts that capture nc_net_train_step into a CUDA
+ * graph (every call of this library on a non-NULL stream is capturable once a first, un-captured call
+ * with the same batch size has sized the workspaces): replaying the graph repeats the device work
+ * of sess.run(train_op) (construct_distribute.py:413) but not the host-side counter the reference
+ * keeps in tf.train.get_or_create_global_step() (:371).  Adam must not be captured: its step size
+ * depends on global_step and is computed on the host. */
+int nc_net_advance_step(nc_net* net, int64_t k);
 
 /* ---- data parallel inside the library (NCCL bound with dlopen, one process per GPU) ----------
  * Replaces the 1 ps + 1 worker gRPC exchange of construct_distribute.py:344-357 (cmd.py:63-69) by

@@ -306,3 +306,33 @@ def test_fused_first_block_equals_separate_kernels(ctx, n, monkeypatch):
         gref = ref.flatten(ref.backward(dz, params, cache))
         assert rel_err(fused.grads.cpu().numpy(), gref) < 1e-4
         plain.close(); fused.close()
+
+
+@pytest.mark.parametrize("opt,lr", [("compat", 1e-4), ("sgd", 0.05)])
+def test_graphed_train_step_equals_eager(ctx, opt, lr):
+    """GraphedTrainStep replays the captured launches of Net.train_step: same kernels, same order, so weights,
+    optimizer state and the step counter after three replays equal three eager steps bit for bit; building the graph
+    leaves the net untouched; Adam is refused."""
+    from cloud_server_b200.net import Net, GraphedTrainStep
+    rng = np.random.default_rng(12)
+    xs = torch.from_numpy(rng.random((3, 64, 784), dtype=np.float32)).cuda()
+    ys = torch.nn.functional.one_hot(torch.from_numpy(rng.integers(0, 10, (3, 64))).cuda(), 10).float()
+    eager, graphed = Net(tfref.LENET, ctx, seed=9), Net(tfref.LENET, ctx, seed=9)
+    for net in (eager, graphed):
+        net.set_math(3)
+    eager.train_step(xs[0], ys[0], "entropy", opt, lr)        # both nets start from step 1 with live optimizer state
+    graphed.train_step(xs[0], ys[0], "entropy", opt, lr)
+    w_before = graphed.get_params().copy()
+    step = GraphedTrainStep(graphed, 64, "entropy", opt, lr)
+    assert np.array_equal(graphed.get_params(), w_before) and graphed.global_step == 1
+    for i in range(3):
+        le, ce = eager.train_step(xs[i], ys[i], "entropy", opt, lr)
+        lg, cg = step(xs[i], ys[i])
+        assert float(le.item()) == float(lg.item()) and int(ce.item()) == int(cg.item())
+    assert np.array_equal(eager.get_params(), graphed.get_params())
+    oid = 0 if opt == "compat" else 1
+    assert np.array_equal(eager.get_state(oid), graphed.get_state(oid))
+    assert eager.global_step == graphed.global_step == 4
+    with pytest.raises(ValueError):
+        GraphedTrainStep(graphed, 64, "entropy", "adam", 1e-3)
+    eager.close(); graphed.close()
