@@ -29,6 +29,9 @@ constexpr unsigned kConvThreads = 256;
 // the raw tile is the hi part) and, owning the SM anyway, runs the ring 6 deep at BN = 64 (192 KB)
 template <int BN, bool X3> struct StageCount { static constexpr int value = (X3 && BN == 64) ? 6 : 4; };
 constexpr int LO_SLOTS = 2;              // two: converting block i+1 overlaps the MMAs of block i
+#ifndef NC_TMEM_A
+#define NC_TMEM_A 1
+#endif
 
 struct I2cArgs {
     int W, H;              // spatial size (input == output: stride 1, SAME)
@@ -59,8 +62,14 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     constexpr unsigned HI_BYTES = A_BYTES + B_BYTES;
     constexpr unsigned STAGE_BYTES = HI_BYTES;                       // raw fp32 tiles [A | B]
     constexpr unsigned LO_BASE = STAGES * STAGE_BYTES;               // 3xTF32: LO_SLOTS buffers [A_lo | B_lo] behind the ring
+    // TA: the K-major A operand of the 3xTF32 product lives in tensor memory (see gemm_tcgen05.cu): hi and lo values of a
+    // row are parked in TMEM columns [BN, BN + 256) by the split warps, only B and B_lo are read from shared memory
+    constexpr bool TA = X3 && !A_MN && NC_TMEM_A;
+    constexpr int LOS = TA ? 4 : LO_SLOTS;                           // lo buffers in flight: the split warps may run this far ahead of the MMAs
+    constexpr unsigned LO_BYTES = TA ? B_BYTES : HI_BYTES;
+    constexpr unsigned TCOLS = TA ? 512u : (unsigned)BN;
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[LO_SLOTS], s_loempty[LO_SLOTS], s_tmem_full;
+    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[4], s_loempty[4], s_tmem_full;
     __shared__ unsigned s_tmem_base;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -73,7 +82,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             mbar_init(smem_u32(&s_full[s]), 1);
             mbar_init(smem_u32(&s_empty[s]), 1);
         }
-        for (int s = 0; s < LO_SLOTS; ++s) {
+        for (int s = 0; s < 4; ++s) {
             mbar_init(smem_u32(&s_ready[s]), kConvThreads / 32);
             mbar_init(smem_u32(&s_loempty[s]), 1);
         }
@@ -81,7 +90,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem_base)), "r"((unsigned)BN));
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem_base)), "r"(TCOLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -91,7 +100,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             if (!WGRAD) {
                 // first output pixel of the tile; the unit walks W, then H, then N from here
                 const int pw = m0 % ia.W, q = m0 / ia.W, ph0 = q % ia.H, pn = q / ia.H;
@@ -154,14 +163,14 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                                    ((unsigned)(BN >> 3) << 17) | ((unsigned)(BM >> 4) << 24);
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
                 const unsigned ph = (unsigned)(i / STAGES) & 1u;
-                const int l = i % LO_SLOTS;
-                if (X3) mbar_wait(smem_u32(&s_ready[l]), (unsigned)(i / LO_SLOTS) & 1u);   // raw tile landed AND its lo part is written
+                const int l = i % LOS;
+                if (X3) mbar_wait(smem_u32(&s_ready[l]), (unsigned)(i / LOS) & 1u);   // raw tile landed AND its lo part is written
                 else mbar_wait(smem_u32(&s_full[s]), ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const unsigned sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
@@ -171,7 +180,13 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     const unsigned long long da = A_MN ? umma_desc(sa + kk * 1024, 4096, 512, 1) : umma_desc(sa + kk * 32, 16, 1024);
                     const unsigned long long db = B_MN ? umma_desc(sb + kk * 1024, 4096, 512, 1) : umma_desc(sb + kk * 32, 16, 1024);
                     const unsigned accum = (i > 0 || kk > 0) ? 1u : 0u;
-                    if (X3) {
+                    if (TA) {
+                        const unsigned a_hi = tmem + (unsigned)BN + (unsigned)l * 64u + (unsigned)kk * 8u, a_lo = a_hi + 32u;
+                        const unsigned long long offb = (unsigned long long)((LO_BASE + (unsigned)l * LO_BYTES - ((unsigned)s * STAGE_BYTES + A_BYTES)) >> 4);
+                        umma_tf32_ta(tmem, a_lo, db, idesc, accum);          // lo(A) . hi(B)
+                        umma_tf32_ta(tmem, a_hi, db + offb, idesc, 1u);      // hi(A) . lo(B)
+                        umma_tf32_ta(tmem, a_hi, db, idesc, 1u);             // hi(A) . hi(B)
+                    } else if (X3) {
                         // lo tiles: same layout as the raw ones, LO_BASE + l * HI_BYTES - s * STAGE_BYTES further on
                         const unsigned long long off = (unsigned long long)((LO_BASE + (unsigned)l * HI_BYTES - (unsigned)s * STAGE_BYTES) >> 4);
                         umma_tf32(tmem, da + off, db, idesc, accum);         // lo(A) . hi(B)
@@ -191,14 +206,34 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int q = warp & 3;
         const int row = m0 + q * 32 + lane;
         for (int i = 0; X3 && i < nkb; ++i) {
-            const int s = i % STAGES, l = i % LO_SLOTS;
+            const int s = i % STAGES, l = i % LOS;
             mbar_wait(smem_u32(&s_full[s]), (unsigned)(i / STAGES) & 1u);               // raw tiles landed
-            mbar_wait(smem_u32(&s_loempty[l]), ((unsigned)(i / LO_SLOTS) & 1u) ^ 1u);   // the MMAs that read this lo buffer are done
+            mbar_wait(smem_u32(&s_loempty[l]), ((unsigned)(i / LOS) & 1u) ^ 1u);   // the MMAs that read this lo buffer are done
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const unsigned praw = smem_u32(smem + (size_t)s * STAGE_BYTES);
-            const unsigned plo = smem_u32(smem + LO_BASE + (size_t)l * HI_BYTES);
+            const unsigned plo = smem_u32(smem + LO_BASE + (size_t)l * LO_BYTES) - (TA ? A_BYTES : 0u);   // TA: only B has a lo tile
+            if (TA) {
+                // this thread's tile row (TMEM lane), 16 of its 32 k values: warps 2-5 take k 0..15, warps 6-9 k 16..31.
+                // Row r of the 128-byte-swizzled tile keeps its 16-byte chunk c at r * 128 + ((c ^ (r & 7)) << 4).
+                const unsigned r = (unsigned)q * 32u + (unsigned)lane, h = warp >= 6 ? 1u : 0u;
+                unsigned v[16], w[16];
+#pragma unroll
+                for (unsigned c = 0; c < 4; ++c)
+                    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                 : "=r"(v[4 * c]), "=r"(v[4 * c + 1]), "=r"(v[4 * c + 2]), "=r"(v[4 * c + 3])
+                                 : "r"(praw + r * 128u + (((4u * h + c) ^ (r & 7u)) << 4)));
+#pragma unroll
+                for (int e = 0; e < 16; ++e) w[e] = __float_as_uint(__uint_as_float(v[e]) - __uint_as_float(v[e] & 0xFFFFE000u));
+                const unsigned t_hi = tmem + (((unsigned)q * 32u) << 16) + (unsigned)BN + (unsigned)l * 64u + 16u * h;
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                             ::"r"(t_hi), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+                               "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                             ::"r"(t_hi + 32u), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]), "r"(w[8]),
+                               "r"(w[9]), "r"(w[10]), "r"(w[11]), "r"(w[12]), "r"(w[13]), "r"(w[14]), "r"(w[15]) : "memory");
+            }
 #pragma unroll 3
-            for (unsigned j = (unsigned)(warp - 2) * 32u + (unsigned)lane; j < HI_BYTES / 16; j += kConvThreads) {
+            for (unsigned j = (TA ? A_BYTES / 16 : 0u) + (unsigned)(warp - 2) * 32u + (unsigned)lane; j < HI_BYTES / 16; j += kConvThreads) {
                 // lo = x - trunc_tf32(x): exact in fp32, at most 13 significant bits; the tensor core keeps its top 11
                 unsigned vx, vy, vz, vw;
                 asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(vx), "=r"(vy), "=r"(vz), "=r"(vw) : "r"(praw + j * 16u));
@@ -207,6 +242,10 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const unsigned lz = __float_as_uint(__uint_as_float(vz) - __uint_as_float(vz & 0xFFFFE000u));
                 const unsigned lw = __float_as_uint(__uint_as_float(vw) - __uint_as_float(vw & 0xFFFFE000u));
                 asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(plo + j * 16u), "r"(lx), "r"(ly), "r"(lz), "r"(lw) : "memory");
+            }
+            if (TA) {
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core (async proxy) reads
             __syncwarp();
@@ -267,7 +306,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((unsigned)BN));
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TCOLS));
 }
 
 __global__ void i2c_reduce_kernel(float* __restrict__ dst, const float* __restrict__ ws, int splits, long long count,
@@ -299,7 +338,9 @@ int get_encode_i2c(nc_ctx* ctx) {
 template <int BN, int MODE, bool X3>
 int launch_i2c(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const I2cArgs& ia, float* C, const float* bias, int M,
                int N, int nkb, int kbps, int splits, float* partial, cudaStream_t st) {
-    const size_t smem = (size_t)(StageCount<BN, X3>::value + (X3 ? LO_SLOTS : 0)) * (BM * BK * 4 + BN * BK * 4) + 1024;
+    const bool ta = X3 && MODE != 2 && NC_TMEM_A;
+    const size_t smem = (size_t)StageCount<BN, X3>::value * (BM * BK * 4 + BN * BK * 4) +
+                        (X3 ? (ta ? (size_t)4 * BN * BK * 4 : (size_t)LO_SLOTS * (BM * BK * 4 + BN * BK * 4)) : 0) + 1024;
     auto kfn = conv_i2c_kernel<BN, MODE, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);

@@ -141,7 +141,7 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
 
     if (warp == 0) {
         // ===================== TMA producer: B tiles only =====================
-        if (lane == 0) {
+        if (elect_one()) {
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % BRING;
                 const unsigned ph = (unsigned)(i / BRING) & 1u;
@@ -163,7 +163,7 @@ conv_tf32_kernel(const __grid_constant__ ConvArgs args, const __grid_constant__ 
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                                    ((unsigned)(BN >> 3) << 17) | ((unsigned)(BM >> 4) << 24);
             for (int i = 0; i < nkb; ++i) {

@@ -30,6 +30,9 @@ constexpr unsigned kConvThreads = 256;
 // a separate pair of buffers; the ring itself stays read-only for the converter warps, so the TMA runs 4 blocks ahead.
 template <int BN, bool X3> struct StageCount { static constexpr int value = (X3 && BN == 64) ? 6 : 4; };
 constexpr int LO_SLOTS = 2;              // two: converting block i+1 overlaps the MMAs of block i
+#ifndef NC_TMEM_A
+#define NC_TMEM_A 1
+#endif
 
 // X3 = true: "3xTF32" -- every fp32 operand is split into hi = rna_tf32(x) and lo = rna_tf32(x - hi) and
 // the product is accumulated as hi.hi + lo.hi + hi.lo (three MMAs per k step), which restores fp32-class
@@ -45,9 +48,17 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr unsigned HI_BYTES = A_BYTES + B_BYTES;                 // TMA destination: raw fp32 tiles [A | B]
     constexpr unsigned STAGE_BYTES = HI_BYTES;
     constexpr unsigned LO_BASE = STAGES * STAGE_BYTES;               // 3xTF32: LO_SLOTS buffers [A_lo | B_lo] behind the ring
+    // TA: a K-major A operand of the 3xTF32 product is fed from TENSOR MEMORY instead of shared memory.  Both operands from
+    // shared memory make the three MMAs of a k step read 3 x (4 KB + BN x 32 B): at BN = 64 that alone saturates the SM's
+    // shared-memory port.  The split warps read each A row once, and park its raw (hi) and lo values in TMEM columns
+    // [BN, BN + 256): four buffers of 32 hi + 32 lo columns; lane = tile row, one fp32 per column.
+    constexpr bool TA = X3 && !A_MN && NC_TMEM_A;
+    constexpr int LOS = TA ? 4 : LO_SLOTS;                           // lo buffers in flight: the split warps may run this far ahead of the MMAs
+    constexpr unsigned LO_BYTES = TA ? B_BYTES : HI_BYTES;           // per lo buffer: [B_lo] resp. [A_lo | B_lo]
+    constexpr unsigned TCOLS = TA ? 512u : (unsigned)BN;             // TMEM columns (power of two)
     // 1024-byte aligned stage buffers (swizzle atoms are 8 rows x 128 B)
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[LO_SLOTS], s_loempty[LO_SLOTS], s_tmem_full;
+    __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[4], s_loempty[4], s_tmem_full;
     __shared__ unsigned s_tmem_base;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -61,7 +72,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_init(smem_u32(&s_full[s]), 1);
             mbar_init(smem_u32(&s_empty[s]), 1);
         }
-        for (int s = 0; s < LO_SLOTS; ++s) {
+        for (int s = 0; s < 4; ++s) {
             mbar_init(smem_u32(&s_ready[s]), kConvThreads / 32);       // one arrive per converter warp
             mbar_init(smem_u32(&s_loempty[s]), 1);
         }
@@ -69,7 +80,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {   // TMEM: BN fp32 accumulator columns (power of two >= 32)
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem_base)), "r"((unsigned)BN));
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem_base)), "r"(TCOLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -79,7 +90,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
                 const unsigned ph = (unsigned)(i / STAGES) & 1u;
@@ -105,15 +116,15 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        if (elect_one()) {
             // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32, A = B = TF32, majors, N >> 3, M >> 4
             const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                                    ((unsigned)(BN >> 3) << 17) | ((unsigned)(BM >> 4) << 24);
             for (int i = 0; i < nkb; ++i) {
                 const int s = i % STAGES;
                 const unsigned ph = (unsigned)(i / STAGES) & 1u;
-                const int l = i % LO_SLOTS;
-                if (X3) mbar_wait(smem_u32(&s_ready[l]), (unsigned)(i / LO_SLOTS) & 1u);   // raw tile landed AND its lo part is written
+                const int l = i % LOS;
+                if (X3) mbar_wait(smem_u32(&s_ready[l]), (unsigned)(i / LOS) & 1u);   // raw tile landed AND its lo part is written
                 else mbar_wait(smem_u32(&s_full[s]), ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const unsigned sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
@@ -127,8 +138,14 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const unsigned long long da = A_MN ? umma_desc(sa + kk * 1024, 4096, 512, 1) : umma_desc(sa + kk * 32, 16, 1024);
                     const unsigned long long db = B_MN ? umma_desc(sb + kk * 1024, 4096, 512, 1) : umma_desc(sb + kk * 32, 16, 1024);
                     const unsigned accum = (i > 0 || kk > 0) ? 1u : 0u;
-                    if (X3) {
-                        // lo parts live HI_BYTES further on in the stage: same layout, same descriptors + offset
+                    if (TA) {
+                        // A from tensor memory (8 columns per k step), B and B_lo from shared memory
+                        const unsigned a_hi = tmem + (unsigned)BN + (unsigned)l * 64u + (unsigned)kk * 8u, a_lo = a_hi + 32u;
+                        const unsigned long long offb = (unsigned long long)((LO_BASE + (unsigned)l * LO_BYTES - ((unsigned)s * STAGE_BYTES + A_BYTES)) >> 4);
+                        umma_tf32_ta(tmem, a_lo, db, idesc, accum);          // lo(A) . hi(B)
+                        umma_tf32_ta(tmem, a_hi, db + offb, idesc, 1u);      // hi(A) . lo(B)
+                        umma_tf32_ta(tmem, a_hi, db, idesc, 1u);             // hi(A) . hi(B)
+                    } else if (X3) {
                         // lo tiles: same layout as the raw ones, LO_BASE + l * HI_BYTES - s * STAGE_BYTES further on
                         const unsigned long long off = (unsigned long long)((LO_BASE + (unsigned)l * HI_BYTES - (unsigned)s * STAGE_BYTES) >> 4);
                         umma_tf32(tmem, da + off, db, idesc, accum);         // lo(A) . hi(B)
@@ -153,14 +170,34 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // 3xTF32: during the main loop these four warps write lo = x - trunc(x) of every staged operand; the raw tile
         // itself is the hi part.
         for (int i = 0; X3 && i < nkb; ++i) {
-            const int s = i % STAGES, l = i % LO_SLOTS;
+            const int s = i % STAGES, l = i % LOS;
             mbar_wait(smem_u32(&s_full[s]), (unsigned)(i / STAGES) & 1u);               // raw tiles landed
-            mbar_wait(smem_u32(&s_loempty[l]), ((unsigned)(i / LO_SLOTS) & 1u) ^ 1u);   // the MMAs that read this lo buffer are done
+            mbar_wait(smem_u32(&s_loempty[l]), ((unsigned)(i / LOS) & 1u) ^ 1u);   // the MMAs that read this lo buffer are done
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const unsigned praw = smem_u32(smem + (size_t)s * STAGE_BYTES);
-            const unsigned plo = smem_u32(smem + LO_BASE + (size_t)l * HI_BYTES);
+            const unsigned plo = smem_u32(smem + LO_BASE + (size_t)l * LO_BYTES) - (TA ? A_BYTES : 0u);   // TA: only B has a lo tile
+            if (TA) {
+                // this thread's tile row (TMEM lane), 16 of its 32 k values: warps 2-5 take k 0..15, warps 6-9 k 16..31.
+                // Row r of the 128-byte-swizzled tile keeps its 16-byte chunk c at r * 128 + ((c ^ (r & 7)) << 4).
+                const unsigned r = (unsigned)q * 32u + (unsigned)lane, h = warp >= 6 ? 1u : 0u;
+                unsigned v[16], w[16];
+#pragma unroll
+                for (unsigned c = 0; c < 4; ++c)
+                    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                                 : "=r"(v[4 * c]), "=r"(v[4 * c + 1]), "=r"(v[4 * c + 2]), "=r"(v[4 * c + 3])
+                                 : "r"(praw + r * 128u + (((4u * h + c) ^ (r & 7u)) << 4)));
+#pragma unroll
+                for (int e = 0; e < 16; ++e) w[e] = __float_as_uint(__uint_as_float(v[e]) - __uint_as_float(v[e] & 0xFFFFE000u));
+                const unsigned t_hi = tmem + (((unsigned)q * 32u) << 16) + (unsigned)BN + (unsigned)l * 64u + 16u * h;
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                             ::"r"(t_hi), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+                               "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+                asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                             ::"r"(t_hi + 32u), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]), "r"(w[8]),
+                               "r"(w[9]), "r"(w[10]), "r"(w[11]), "r"(w[12]), "r"(w[13]), "r"(w[14]), "r"(w[15]) : "memory");
+            }
 #pragma unroll 3
-            for (unsigned j = (unsigned)(warp - 2) * 32u + (unsigned)lane; j < HI_BYTES / 16; j += kConvThreads) {
+            for (unsigned j = (TA ? A_BYTES / 16 : 0u) + (unsigned)(warp - 2) * 32u + (unsigned)lane; j < HI_BYTES / 16; j += kConvThreads) {
                 // lo = x - trunc_tf32(x): exact in fp32, at most 13 significant bits; the tensor core keeps its top 11
                 unsigned vx, vy, vz, vw;
                 asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(vx), "=r"(vy), "=r"(vz), "=r"(vw) : "r"(praw + j * 16u));
@@ -169,6 +206,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const unsigned lz = __float_as_uint(__uint_as_float(vz) - __uint_as_float(vz & 0xFFFFE000u));
                 const unsigned lw = __float_as_uint(__uint_as_float(vw) - __uint_as_float(vw & 0xFFFFE000u));
                 asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(plo + j * 16u), "r"(lx), "r"(ly), "r"(lz), "r"(lw) : "memory");
+            }
+            if (TA) {
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core (async proxy) reads
             __syncwarp();
@@ -220,7 +261,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 1) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((unsigned)BN));
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TCOLS));
     }
 }
 
@@ -241,7 +282,9 @@ __global__ void tc_reduce_kernel(float* __restrict__ dst, const float* __restric
 template <int BN, bool A_MN, bool B_MN, bool X3>
 int launch(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, float* C, const float* bias, int M, int N, int K,
            int kbps, int splits, int act, float slope, float* partial, cudaStream_t st) {
-    const size_t smem = (size_t)(StageCount<BN, X3>::value + (X3 ? LO_SLOTS : 0)) * (BM * BK * 4 + BN * BK * 4) + 1024;
+    const bool ta = X3 && !A_MN && NC_TMEM_A;
+    const size_t smem = (size_t)StageCount<BN, X3>::value * (BM * BK * 4 + BN * BK * 4) +
+                        (X3 ? (ta ? (size_t)4 * BN * BK * 4 : (size_t)LO_SLOTS * (BM * BK * 4 + BN * BK * 4)) : 0) + 1024;
     auto kfn = gemm_tf32_kernel<BN, A_MN, B_MN, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);

@@ -478,17 +478,21 @@ static int run_gemm(nc_net* net, int M, int N, int K, AF A, BF B, float* C, cons
 }
 
 static int run_colsum(nc_net* net, const float* y, int rows, int cols, float* out, cudaStream_t st) {
-    int splits = (rows + 255) / 256;            // enough CTAs to stream dY at full bandwidth
+    // enough CTAs to stream dY at full bandwidth: about four per SM over (column blocks x row splits)
+    const int cblocks = (cols + 31) / 32;
+    int splits = (net->ctx->sm_count * 4 + cblocks - 1) / cblocks;
+    if (splits > (rows + 63) / 64) splits = (rows + 63) / 64;     // at least 64 rows per split
     if (splits < 1) splits = 1;
-    if (splits > 64) splits = 64;                // the final fixed-order sum over the splits is serial per column
+    if (splits > 512) splits = 512;
     const int rps = (rows + splits - 1) / splits;
     splits = (rows + rps - 1) / rps;
     int rc = reserve_ws(net, (size_t)splits * cols * sizeof(float));
     if (rc != NC_OK) return rc;
-    dim3 grid((cols + 31) / 32, splits);
+    dim3 grid(cblocks, splits);
     colsum_partial_kernel<<<grid, 256, 0, st>>>(y, rows, cols, rps, net->ws);
     NET_LAUNCH(net);
-    reduce_partials_kernel<<<grid_for(cols, net->ctx->sm_count), 256, 0, st>>>(out, net->ws, splits, cols, nullptr, cols);
+    // fixed-order sum of the splits: a warp per column, lanes stride the splits, then a shuffle tree
+    reduce_partials_warp_kernel<<<(cols + 7) / 8, 256, 0, st>>>(out, net->ws, splits, cols);
     NET_LAUNCH(net);
     return NC_OK;
 }
@@ -631,6 +635,14 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
             bool done;
             rc = tc_try(net, in, W, out, Bp, M, N, K, false, true, st, &done);       // Y = X . W[in][out] + b
             if (rc != NC_OK) return rc;
+            if (!done && N <= 32 && (size_t)K * N * sizeof(float) <= 48 * 1024) {      // the narrow output layer
+                const int blocks = (M + 7) / 8 < sms * 2 ? (M + 7) / 8 : sms * 2;
+                const size_t smem = (size_t)K * N * sizeof(float);
+                if (N <= 16) skinny_fwd_kernel<16><<<blocks, 256, smem, st>>>(in, W, Bp, out, M, N, K);
+                else skinny_fwd_kernel<32><<<blocks, 256, smem, st>>>(in, W, Bp, out, M, N, K);
+                NET_LAUNCH(net);
+                done = true;
+            }
             if (!done) rc = run_gemm<true, true>(net, M, N, K, RowMajor{in, K}, RowMajor{W, N}, out, Bp, st);
             if (rc != NC_OK) return rc;
             break;
@@ -783,6 +795,24 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             bool done;
             rc = tc_try(net, in, d, dW, nullptr, K, N, M, true, true, st, &done, true);
             if (rc != NC_OK) return rc;
+            if (!done && N <= 32) {                                                     // the narrow output layer
+                int slices = (sms * 2 + (K + 255) / 256 - 1) / ((K + 255) / 256);
+                if (slices > (M + 15) / 16) slices = (M + 15) / 16;
+                if (slices < 1) slices = 1;
+                int rps = (M + slices - 1) / slices;
+                while ((size_t)rps * N * sizeof(float) > 48 * 1024) { slices *= 2; rps = (M + slices - 1) / slices; }
+                slices = (M + rps - 1) / rps;
+                rc = reserve_ws(net, (size_t)slices * K * N * sizeof(float));
+                if (rc != NC_OK) return rc;
+                dim3 grid((K + 255) / 256, slices);
+                const size_t smem = (size_t)rps * N * sizeof(float);
+                if (N <= 16) skinny_wgrad_kernel<16><<<grid, 256, smem, st>>>(in, d, net->ws, M, N, K, rps);
+                else skinny_wgrad_kernel<32><<<grid, 256, smem, st>>>(in, d, net->ws, M, N, K, rps);
+                NET_LAUNCH(net);
+                reduce_partials_kernel<<<grid_for((long long)K * N, sms), 256, 0, st>>>(dW, net->ws, slices, (long long)K * N, nullptr, N);
+                NET_LAUNCH(net);
+                done = true;
+            }
             if (!done) rc = run_gemm<false, true>(net, K, N, M, ColMajor{in, K}, RowMajor{d, N}, dW, nullptr, st);
             if (rc != NC_OK) return rc;
             rc = run_colsum(net, d, M, N, dB, st);

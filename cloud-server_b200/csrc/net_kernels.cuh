@@ -167,14 +167,118 @@ __global__ void reduce_partials_warp_kernel(float* __restrict__ dst, const float
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// the output layer: tf.matmul(h, W) + b with W[K][N], N = classes (10) -- construct_distribute.py:264.
+// Far too narrow for a 64-wide GEMM tile; W (K*N floats) fits shared memory instead.
+//   forward  one warp per row: lanes stride K (coalesced), NMAX accumulators per lane, shuffle-tree reduction
+//   wgrad    one thread per k: dW[k][:] += x[m][k] * dy[m][:] over a slice of the batch, dy rows broadcast from shared
+//            memory; slices are summed in fixed order by reduce_partials_kernel
+// ---------------------------------------------------------------------------------------------
+template <int NMAX>
+__global__ void __launch_bounds__(256)
+skinny_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias, float* __restrict__ y,
+                  int M, int N, int K) {
+    extern __shared__ __align__(16) float sw[];      // W[K][N]
+    {
+        // staged with 16-byte loads, eight in flight per thread (a scalar loop here is one L2 round trip per element)
+        const int total = K * N, total4 = ((reinterpret_cast<uintptr_t>(w) & 15) == 0) ? total / 4 : 0;
+        const float4* w4 = reinterpret_cast<const float4*>(w);
+        float4* s4 = reinterpret_cast<float4*>(sw);
+        int i = threadIdx.x;
+        for (; i + 7 * 256 < total4; i += 8 * 256) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldg(w4 + i + u * 256);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) s4[i + u * 256] = v[u];
+        }
+        for (; i < total4; i += 256) s4[i] = __ldg(w4 + i);
+        for (int j = total4 * 4 + threadIdx.x; j < total; j += 256) sw[j] = __ldg(w + j);
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int m = blockIdx.x * 8 + warp; m < M; m += gridDim.x * 8) {
+        float acc[NMAX];
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) acc[n] = 0.0f;
+        const float* xr = x + (long long)m * K;
+        int k = lane;
+        for (; k + 224 < K; k += 256) {               // eight independent global loads in flight per lane
+            float xv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) xv[u] = __ldg(xr + k + 32 * u);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float* wr = sw + (k + 32 * u) * N;
+#pragma unroll
+                for (int n = 0; n < NMAX; ++n)
+                    if (n < N) acc[n] = fmaf(xv[u], wr[n], acc[n]);
+            }
+        }
+        for (; k < K; k += 32) {
+            const float xv = __ldg(xr + k);
+            const float* wr = sw + k * N;
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n)
+                if (n < N) acc[n] = fmaf(xv, wr[n], acc[n]);
+        }
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) {
+            if (n < N) {
+                float v = acc[n];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) y[(long long)m * N + n] = v + (bias ? __ldg(bias + n) : 0.0f);
+            }
+        }
+    }
+}
+
+// partial[slice][K][N]; grid = (ceil(K / 256), slices); rows_per_slice rows of the batch per slice
+template <int NMAX>
+__global__ void __launch_bounds__(256)
+skinny_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partial, int M, int N, int K,
+                    int rows_per_slice) {
+    extern __shared__ float sdy[];                   // dy[rows of this slice][N]
+    const int m0 = blockIdx.y * rows_per_slice, m1 = min(M, m0 + rows_per_slice);
+    for (int i = threadIdx.x; i < (m1 - m0) * N; i += blockDim.x) sdy[i] = __ldg(dy + (long long)m0 * N + i);
+    __syncthreads();
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    if (k >= K) return;
+    float acc[NMAX];
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n) acc[n] = 0.0f;
+    for (int m = m0; m < m1; ++m) {
+        const float xv = __ldg(x + (long long)m * K + k);
+        const float* dr = sdy + (m - m0) * N;
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n)
+            if (n < N) acc[n] = fmaf(xv, dr[n], acc[n]);
+    }
+    float* out = partial + ((long long)blockIdx.y * K + k) * N;
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n)
+        if (n < N) out[n] = acc[n];
+}
+
 // column sums of Y[rows][cols] (bias gradients): partial[split][col]
 __global__ void colsum_partial_kernel(const float* __restrict__ y, int rows, int cols, int rows_per_split, float* __restrict__ ws) {
     const int col = blockIdx.x * 32 + (threadIdx.x & 31);
     const int lane_row = threadIdx.x >> 5;            // 8 row lanes
     const int r0 = blockIdx.y * rows_per_split, r1 = min(rows, r0 + rows_per_split);
     float s = 0.0f;
-    if (col < cols)
-        for (int r = r0 + lane_row; r < r1; r += 8) s += __ldg(y + (long long)r * cols + col);
+    if (col < cols) {
+        int r = r0 + lane_row;
+        float p[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) p[u] = 0.0f;
+        for (; r + 56 < r1; r += 64) {               // eight independent loads in flight per thread
+#pragma unroll
+            for (int u = 0; u < 8; ++u) p[u] += __ldg(y + (long long)(r + 8 * u) * cols + col);
+        }
+        for (; r < r1; r += 8) s += __ldg(y + (long long)r * cols + col);
+        s += ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]));
+    }
     __shared__ float sh[8][33];
     sh[lane_row][threadIdx.x & 31] = s;
     __syncthreads();

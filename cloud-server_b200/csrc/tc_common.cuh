@@ -8,6 +8,18 @@ namespace {
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 
+// one lane of a fully active warp, chosen by the hardware.  Code under `if (elect_one())` is known to ptxas to run in a
+// single thread, so tcgen05.mma / commit are emitted back to back; under `if (lane == 0)` every one of them is wrapped in
+// an elect-and-branch loop.
+__device__ __forceinline__ bool elect_one() {
+    unsigned pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(pred));
+    return pred != 0;
+}
+
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
@@ -51,6 +63,15 @@ __device__ __forceinline__ void umma_tf32(unsigned tmem, unsigned long long da, 
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
         ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(accum) : "memory");
+}
+
+// the same product with the A operand in tensor memory: [a_tmem] addresses 128 lanes (rows) x 8 columns (k)
+__device__ __forceinline__ void umma_tf32_ta(unsigned tmem, unsigned a_tmem, unsigned long long db, unsigned idesc, unsigned accum) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}\n"
+        ::"r"(tmem), "r"(a_tmem), "l"(db), "r"(idesc), "r"(accum) : "memory");
 }
 
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
