@@ -31,6 +31,10 @@ ALG_BYTES_TRAIN_CHAIN = 28 * 28 * 16 * 3 + 784 + 3136          # 41 552 B / pict
 ALG_BYTES_PREDICT_CHAIN = H * W * C + 3136                      # 2 362 432 B / picture
 
 
+def _emit(line):
+    print(json.dumps(line), flush=True)
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -178,7 +182,7 @@ def run_reference(args, rank, world):
                                    % per_step},
         "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ------------------------------------------------------------------------------------------
@@ -490,7 +494,7 @@ def run_ours(args, rank, local_rank, world):
                       "Pillow calls for both chains (preprocess.py:29,40; construct_inference.py:312-330) in memory, IPP off, "
                       "one worker process per core" % (dt, done)}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if dist_on:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
@@ -510,6 +514,16 @@ def main():
     ap.add_argument("--math", type=int, default=3, help="CNN math: 0 fp32 SIMT, 1 tcgen05 3xTF32, 2 tcgen05 1xTF32, 3 (default) 3xTF32 forward + 1xTF32 gradients")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    # The contract is ONE JSON line on stdout.  Libraries write banners to fd 1 behind Python's back (NCCL prints its
+    # version line there on the first communicator): park the real stdout, point fd 1 at stderr for the whole run, and
+    # print the result line to the parked descriptor.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    global _emit
+
+    def _emit(line):
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
