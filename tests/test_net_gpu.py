@@ -21,6 +21,13 @@ CONFIGS = {
         {"layer": "active", "active_func": "relu"},
         {"layer": "connect", "hidden": 16}, {"layer": "norm"}, {"layer": "active"}]}, 13, 11, 2, 6),
     "deep": (tfref.DEEPNET, 32, 32, 3, 8),
+    # even filter sizes: SAME padding is asymmetric (extra row / column at the bottom / right), which the TMA im2col walk
+    # has to mirror in its window origin, forward and (mirrored) in dgrad; odd picture size -> partial last tiles
+    "even_filters": ({"middle_layer": [
+        {"layer": "conv", "filter": [3, 3, 32], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
+        {"layer": "conv", "filter": [2, 2, 32], "isBias": "True"}, {"layer": "active", "active_func": "leaky_relu"},
+        {"layer": "conv", "filter": [4, 3, 64]}, {"layer": "active", "active_func": "relu"}, {"layer": "pool"},
+        {"layer": "connect", "hidden": 24}]}, 13, 9, 1, 5),
     "dense_only": ({"middle_layer": [{"layer": "connect", "hidden": 64}, {"layer": "active", "active_func": "relu"}]}, 28, 28, 1, 33),
     "overlap_pool": ({"middle_layer": [{"layer": "conv", "filter": [3, 3, 8], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
                                        {"layer": "pool", "kernel": [3, 3], "stride": [1, 1]}, {"layer": "pool", "kernel": [2, 2], "stride": [2, 2], "padding": "VALID"}]},
@@ -134,7 +141,7 @@ def test_optimizer_arithmetic(ctx, opt, lr):
         assert rel_err(st[:w.size], o.m) < 1e-5 and rel_err(st[w.size:], o.v) < 1e-5
 
 
-@pytest.mark.parametrize("name", ["lenet", "dense_only", "deep", "api_example"])
+@pytest.mark.parametrize("name", ["lenet", "dense_only", "deep", "api_example", "even_filters"])
 @pytest.mark.parametrize("math,tol", [(1, 1e-4), (3, 1e-4), (2, 5e-2)])
 def test_tensor_core_math_within_tolerance(ctx, name, math, tol):
     """math 1 (tcgen05 tiles, 3xTF32, fp32 accumulate): logits, loss, gradients and post-step weights
@@ -243,7 +250,7 @@ def test_library_communicator_world1_is_identity(ctx):
     a.close(); b.close()
 
 
-@pytest.mark.parametrize("name", ["lenet", "deep"])
+@pytest.mark.parametrize("name", ["lenet", "deep", "even_filters"])
 def test_conv_im2col_tma_kernel_agrees_with_gather_kernel(ctx, name, monkeypatch):
     """Stride-1 SAME convolutions with Cin % 32 == 0 take the TMA-im2col kernel (conv_im2col.cu) for forward and
     dgrad; NC_CONV_NO_IM2COL=1 forces the register-gather kernel (conv_tcgen05.cu).  Same products in the same order
