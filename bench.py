@@ -243,7 +243,9 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
     ys = torch.nn.functional.one_hot(torch.randint(0, 10, (n_img,), device=device, generator=g), 10).float()
     net = Net(LENET, ctx, seed=2)
     net.set_math(args.math)
-    dp = DataParallel(net)
+    # N > 1: the gradient exchange runs in the library (its own NCCL communicator, tail of the buffer overlapped with the
+    # rest of backward) unless --dp torch asks for torch.distributed's all-reduce after backward
+    dp = DataParallel(net, in_library=(args.dp == "library"))
     steps = max(10, args.steps)
 
     def bench_train(global_batch, key):
@@ -281,6 +283,8 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
             "value": global_batch * steps / (ms * 1e-3), "unit": "images/s", "ms_per_step": per, "global_batch": global_batch,
             "per_gpu_batch": local, "optimizer": "Adagrad(1e-4) (what the reference runs)", "gpu_launches_per_step": cnt[0] / steps,
             "cuda_graph": graph is not None, "ms_per_step_eager": eager_per,
+            "gradient_exchange": None if world == 1 else ("library NCCL communicator, dense-layer gradients overlapped with the "
+                                                          "convolution backward" if dp.in_library else "torch.distributed all-reduce after backward"),
             "math": {0: "fp32 simt", 1: "tcgen05 3xTF32 (fp32-class accuracy)", 2: "tcgen05 1xTF32", 3: "tcgen05 3xTF32 forward + 1xTF32 gradients"}[args.math],
             "roofline": {"bound": "hbm", "achieved": byts / (per * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": byts / (per * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts,
@@ -329,7 +333,7 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
     y5 = torch.nn.functional.one_hot(torch.randint(0, 10, (n5,), device=device, generator=g), 10).float()
     net5 = Net(DEEPNET, ctx, 32, 32, 3, seed=3)
     net5.set_math(args.math)
-    dp5 = DataParallel(net5)
+    dp5 = DataParallel(net5, in_library=(args.dp == "library"))
     gb5 = 512
     loc5 = gb5 // world
     st5 = {"i": 0}
@@ -510,6 +514,7 @@ def main():
     ap.add_argument("--e2e-batch", type=int, default=1024, help="uploads per e2e step (host pinned)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dp", default="library", choices=["library", "torch"], help="who sums the gradients when N > 1")
     ap.add_argument("--no-graph", action="store_true", help="time the train step eagerly only (default: eager and CUDA-graph replay)")
     ap.add_argument("--math", type=int, default=3, help="CNN math: 0 fp32 SIMT, 1 tcgen05 3xTF32, 2 tcgen05 1xTF32, 3 (default) 3xTF32 forward + 1xTF32 gradients")
     args = ap.parse_args()

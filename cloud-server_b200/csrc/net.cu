@@ -146,6 +146,12 @@ struct nc_net {
     bool fuse_first = false;    // layers 0..2 are conv (few channels, stride 1) -> relu -> pool 2x2/2: one kernel each way
     void* comm = nullptr; int rank = 0, world = 1;
     float* dp_buf = nullptr;
+    // overlap of the gradient exchange with the rest of backward: the tail of the flat gradient buffer (the dense layers
+    // at the end of the net: 98 % of LeNet's parameters) is final as soon as backward has passed layer `split_layer`;
+    // it is all-reduced on comm_stream while the convolution gradients are still being computed
+    cudaStream_t comm_stream = nullptr; cudaEvent_t ev_tail_ready = nullptr, ev_tail_done = nullptr;
+    int split_layer = -1; int64_t split_off = 0; bool tail_in_flight = false;
+    bool dp_step = false;       // set by nc_net_train_step around its backward pass: the exchange may start early
     std::string err;
 };
 
@@ -334,6 +340,9 @@ static double trunc_normal(uint64_t& s) {
 static void free_net(nc_net* net) {
     if (!net) return;
     if (net->comm) { nc_nccl_comm_destroy(net->comm); net->comm = nullptr; }
+    if (net->comm_stream) cudaStreamDestroy(net->comm_stream);
+    if (net->ev_tail_ready) cudaEventDestroy(net->ev_tail_ready);
+    if (net->ev_tail_done) cudaEventDestroy(net->ev_tail_done);
     cudaFree(net->dp_buf);
     cudaFree(net->params); cudaFree(net->grads); cudaFree(net->st_adagrad); cudaFree(net->st_adam);
     cudaFree(net->act); cudaFree(net->aux); cudaFree(net->stat); cudaFree(net->dbuf0); cudaFree(net->dbuf1); cudaFree(net->ws); cudaFree(net->col);
@@ -934,6 +943,15 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         }
         }
         if (need_dx) { float* t = d; d = dn; dn = t; }
+        if (net->dp_step && net->world > 1 && li == net->split_layer && net->comm_stream) {
+            // everything from this layer to the end of the flat gradient buffer is final: send it while backward goes on
+            NET_CUDA(net, cudaEventRecord(net->ev_tail_ready, st));
+            NET_CUDA(net, cudaStreamWaitEvent(net->comm_stream, net->ev_tail_ready, 0));
+            rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads + net->split_off, (size_t)(net->nparams - net->split_off), net->comm_stream);
+            if (rc != NC_OK) return rc;
+            NET_CUDA(net, cudaEventRecord(net->ev_tail_done, net->comm_stream));
+            net->tail_in_flight = true;
+        }
     }
     return NC_OK;
 }
@@ -987,8 +1005,10 @@ extern "C" int nc_net_train_step(nc_net* net, const float* x, const float* y_one
                                  float* loss_out, int32_t* correct_out, void* stream) {
     if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
     // attached to a communicator: this rank's slice of the global batch; the loss is a batch mean, so scale by 1/world and sum
+    net->dp_step = net->world > 1;
     int rc = nc_net_backward(net, x, y_onehot, n, loss_name, 1.0f / (float)net->world, loss_out, correct_out, stream);
-    if (rc != NC_OK) return rc;
+    net->dp_step = false;
+    if (rc != NC_OK) { net->tail_in_flight = false; return rc; }
     if (net->world > 1) { rc = nc_net_allreduce_grads(net, stream); if (rc != NC_OK) return rc; }
     return nc_net_apply(net, opt, lr, stream);
 }
@@ -1046,6 +1066,21 @@ extern "C" int nc_net_attach_nccl(nc_net* net, const char* libnccl_path, const u
     rc = nc_nccl_comm_init(net->ctx, &net->comm, id, rank, world);
     if (rc != NC_OK) return rc;
     net->rank = rank; net->world = world;
+    // split point: the first layer (in forward order, not layer 0) from which on the parameters are at least half of all
+    net->split_layer = -1;
+    if (world > 1 && !getenv("NC_DP_NO_OVERLAP")) {
+        for (int li = 1; li < (int)net->layers.size(); ++li) {
+            const Layer& L = net->layers[li];
+            if (L.w_off < 0) continue;
+            if (2 * (net->nparams - L.w_off) >= net->nparams) { net->split_layer = li; net->split_off = L.w_off; }
+            else break;
+        }
+        if (net->split_layer >= 0 && !net->comm_stream) {
+            NET_CUDA(net, cudaStreamCreateWithFlags(&net->comm_stream, cudaStreamNonBlocking));
+            NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_tail_ready, cudaEventDisableTiming));
+            NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_tail_done, cudaEventDisableTiming));
+        }
+    }
     return NC_OK;
 }
 
@@ -1066,5 +1101,15 @@ extern "C" int nc_net_allreduce_grads(nc_net* net, void* stream) {
     if (!net->comm) return net_err(net, NC_EINVAL, "net is not attached to a communicator (nc_net_attach_nccl)");
     if (net->world == 1) return NC_OK;
     NET_CUDA(net, cudaSetDevice(net->ctx->device));
-    return nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads, (size_t)net->nparams, (cudaStream_t)stream);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (net->tail_in_flight) {
+        // the tail went out during backward: only the head is left, then the step continues once both have landed
+        net->tail_in_flight = false;
+        int rc = NC_OK;
+        if (net->split_off > 0) rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads, (size_t)net->split_off, st);
+        if (rc != NC_OK) return rc;
+        NET_CUDA(net, cudaStreamWaitEvent(st, net->ev_tail_done, 0));
+        return NC_OK;
+    }
+    return nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads, (size_t)net->nparams, st);
 }

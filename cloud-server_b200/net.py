@@ -141,9 +141,21 @@ class Net:
         """One sess.run(train_op) (construct_distribute.py:413).  On a net attached to a communicator
         (attach_nccl) x, y are this rank's slice of the global batch and every rank ends with the
         weights of the global-batch step; the returned loss / hit count stay per-rank."""
-        r = self.backward(x, y, loss_name, 1.0 / self.world)
         if self.world > 1:
-            self.allreduce_grads()
+            # one C call: backward with dLoss / world, the tail of the gradient buffer (the dense layers) all-reduced on a
+            # side stream while the convolution gradients are still being computed, the head after, then the update
+            x = self._x(x)
+            y = y.reshape(x.shape[0], -1).contiguous()
+            if y.dtype != torch.float32 or y.shape[1] != self.classes:
+                raise ValueError("y must be float32 one-hot [N, %d]" % self.classes)
+            if loss_name not in LOSS:
+                raise ValueError("loss_function returns None for %r" % (loss_name,))
+            oid, lr = (0, 1e-4) if opt == "compat" else (OPT[opt] if isinstance(opt, str) else int(opt), lr)
+            _lib.check(self.ctx.handle, _lib.lib().nc_net_train_step(
+                self.handle, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()), x.shape[0], LOSS[loss_name], oid, C.c_float(lr),
+                C.c_void_p(self._loss.data_ptr()), C.c_void_p(self._correct.data_ptr()), self.ctx._stream()))
+            return self._loss, self._correct
+        r = self.backward(x, y, loss_name, 1.0)
         self.apply(opt, lr)
         return r
 

@@ -228,6 +228,9 @@ int nc_net_advance_step(nc_net* net, int64_t k);
  *     keep using the statistics of the batch they are given (they are per-rank replica calls);
  *   - nc_net_train_step scales dLoss by 1/world, sums the flat gradient buffer over the ranks and
  *     applies the update, so every rank ends the step with the weights of the global-batch step;
+ *     the tail of the buffer (the dense layers: most of the bytes) is exchanged on a side stream
+ *     while the convolution gradients are still being computed (NC_DP_NO_OVERLAP in the
+ *     environment at attach time turns that off);
  *   - nc_net_allreduce_grads does that sum alone (between nc_net_backward(grad_scale = 1/world)
  *     and nc_net_apply).
  *   All ranks must make the same calls in the same order (they contain collectives).
