@@ -2,8 +2,9 @@
 // (cp.async.bulk.tensor.4d ... .im2col): the hardware walks 128 consecutive output pixels of the NHWC
 // tensor, applies the filter-tap offset, zero-fills the padding and writes the 128 x 32-channel
 // tile into shared memory already in the 128-byte-swizzled K-major layout tcgen05.mma reads.  No
-// thread gathers anything: warp 0 issues TMA, warp 1 issues MMA, warps 2-5 split operands into
-// hi/lo TF32 parts (3xTF32 only) and run the epilogue.
+// thread gathers anything: warp 0 issues TMA, warp 1 issues MMA (one elect.sync thread each),
+// warps 2-9 split operands into hi/lo TF32 parts (3xTF32 only; the A operand goes to tensor
+// memory) and run the epilogue.
 //
 // Covers tf.nn.conv2d(x, W, strides=[1,1,1,1], padding='SAME') of conv2d()
 // (apps/construction/util/construct_distribute.py:91-95) and its input gradient, for channel
@@ -202,7 +203,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_tmem_full)) : "memory");
         }
     } else {
-        // ===================== warps 2..5: hi/lo split (3xTF32), then the epilogue =====================
+        // ===================== warps 2..9: hi/lo split (3xTF32), then the epilogue =====================
         const int q = warp & 3;
         const int row = m0 + q * 32 + lane;
         for (int i = 0; X3 && i < nkb; ++i) {

@@ -12,10 +12,11 @@
 //   dgrad     dX[n][in]  = dY[n][out] . W[in][out]^T      A K-major, B K-major
 //   wgrad     dW[in][out] = X[n][in]^T . dY[n][out]       A MN-major, B MN-major (reduction over the batch)
 //
-// Tile: 128 x BN x 32 (BN = 64 or 128), 4 stages, one CTA per output tile and K slice (deterministic
-// split-K through a workspace, summed in slice order).  Warp roles: warp 0 = TMA producer (one
-// elected lane), warp 1 = MMA issuer (one lane) and TMEM allocator, warps 2-5 = epilogue
-// (tcgen05.ld 32 lanes x 32 columns per warp -> bias / activation -> global).
+// Tile: 128 x BN x 32 (BN = 64 or 128), a 4-6 deep TMA ring, one CTA per output tile and K slice (deterministic
+// split-K through a workspace, summed in slice order).  Warp roles (320 threads): warp 0 = TMA producer and warp 1 =
+// MMA issuer + TMEM allocator, each running its loop in ONE thread chosen by elect.sync (so ptxas emits the UTCHMMAs
+// back to back); warps 2-9 = 3xTF32 split (lo = x - trunc(x) into shared memory, or hi / lo of a K-major A into tensor
+// memory), then the epilogue (tcgen05.ld 32 lanes x 32 columns per warp -> bias / activation -> global).
 #include "nc_internal.h"
 #include "tc_gemm.h"
 #include "tc_common.cuh"
@@ -162,7 +163,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_tmem_full)) : "memory");
         }
     } else {
-        // ===================== epilogue: warps 2..5 own TMEM lanes 32*(warp%4) .. +32 =====================
+        // ===================== warps 2..9: 3xTF32 split, then the epilogue; a warp owns TMEM lanes 32*(warp%4) .. +32 =====================
         const int q = warp & 3;
         const int row = m0 + q * 32 + lane;
         // kind::tf32 TRUNCATES the 13 low mantissa bits of its fp32 operands: alone that is a one-sided error of ~1e-3 per
