@@ -856,16 +856,50 @@ first_conv_wgrad_from_pool_c1_kernel(const float* __restrict__ x, const float* _
     for (int img = blockIdx.x; img < n; img += gridDim.x) {
         __syncthreads();
         first_load_tile(tile, x + (long long)img * g.ih * g.iw, g);
-        for (int e = threadIdx.x; e < npool * 32; e += 256) {
-            const int pp = e >> 5, c = ob * 32 + (e & 31);
-            float gv = 0.0f; uint8_t a = 0;
-            if (c < g.oc) {
-                const long long o = ((long long)img * npool + pp) * g.oc + c;
-                gv = __ldg(dpool + o);
-                if (!(__ldg(pooled + o) > 0.0f)) gv = 0.0f;          // relu under the pool
-                a = arg[o];
+        if ((g.oc & 3) == 0 && ob * 32 + 32 <= g.oc &&
+            ((reinterpret_cast<uintptr_t>(dpool) | reinterpret_cast<uintptr_t>(pooled)) & 15) == 0 && (reinterpret_cast<uintptr_t>(arg) & 3) == 0) {
+            // four channels per thread and four such loads in flight: the staging is one exposed memory latency per batch of
+            // 16 values instead of one per value
+            const int total4 = npool * 8;
+            const long long base = (long long)img * npool * g.oc + ob * 32;
+            for (int e0 = threadIdx.x; e0 < total4; e0 += 4 * 256) {
+                float4 gv[4], pv[4]; uchar4 av[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int e = e0 + u * 256;
+                    if (e < total4) {
+                        const long long o = base + (long long)(e >> 3) * g.oc + (e & 7) * 4;
+                        gv[u] = __ldg(reinterpret_cast<const float4*>(dpool + o));
+                        pv[u] = __ldg(reinterpret_cast<const float4*>(pooled + o));
+                        av[u] = *reinterpret_cast<const uchar4*>(arg + o);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int e = e0 + u * 256;
+                    if (e < total4) {
+                        float4 m = gv[u];                                  // relu under the pool
+                        if (!(pv[u].x > 0.0f)) m.x = 0.0f;
+                        if (!(pv[u].y > 0.0f)) m.y = 0.0f;
+                        if (!(pv[u].z > 0.0f)) m.z = 0.0f;
+                        if (!(pv[u].w > 0.0f)) m.w = 0.0f;
+                        reinterpret_cast<float4*>(gm)[e] = m;
+                        reinterpret_cast<uchar4*>(am)[e] = av[u];
+                    }
+                }
             }
-            gm[e] = gv; am[e] = a;
+        } else {
+            for (int e = threadIdx.x; e < npool * 32; e += 256) {
+                const int pp = e >> 5, c = ob * 32 + (e & 31);
+                float gv = 0.0f; uint8_t a = 0;
+                if (c < g.oc) {
+                    const long long o = ((long long)img * npool + pp) * g.oc + c;
+                    gv = __ldg(dpool + o);
+                    if (!(__ldg(pooled + o) > 0.0f)) gv = 0.0f;          // relu under the pool
+                    a = arg[o];
+                }
+                gm[e] = gv; am[e] = a;
+            }
         }
         __syncthreads();
         for (int pp = warp; pp < npool; pp += 8) {
