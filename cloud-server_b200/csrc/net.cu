@@ -121,6 +121,7 @@ struct Layer {
     int64_t stat_off = -1;                                  // norm: inv-std per channel (floats, absolute)
     bool in_is_4d = true;
     bool relu_into_pool = false;    // ACT(relu) whose only consumer is the next POOL: applied inside the pool kernels
+    bool act_fused = false;         // CONNECT whose relu / sigmoid successor was applied in the GEMM epilogue of the last forward
 };
 
 struct TensorInfo { int64_t off, size; int ndim; int64_t dims[4]; int init; double arg; };
@@ -510,14 +511,14 @@ static int run_colsum(nc_net* net, const float* y, int rows, int cols, float* ou
 static inline bool x3_for(const nc_net* net, bool backward) { return net->math == 1 || (net->math == 3 && !backward); }
 
 static int tc_try(nc_net* net, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
-                  bool b_mn, cudaStream_t st, bool* done, bool backward = false) {
+                  bool b_mn, cudaStream_t st, bool* done, bool backward = false, int act = 0) {
     *done = false;
     if (net->math == 0 || !nc_tc_gemm_supported(A, B, M, N, K, a_mn, b_mn)) return NC_OK;
     const size_t need = nc_tc_gemm_workspace(net->ctx->sm_count, M, N, K, nullptr, nullptr);
     int rc = reserve_ws(net, need);
     if (rc != NC_OK) return rc;
     const int64_t before = net->ctx->launches;
-    rc = nc_tc_gemm(net->ctx, A, B, C, bias, M, N, K, a_mn, b_mn, 0, 0.0f, net->ws, net->ws_bytes, st, x3_for(net, backward));
+    rc = nc_tc_gemm(net->ctx, A, B, C, bias, M, N, K, a_mn, b_mn, act, 0.0f, net->ws, net->ws_bytes, st, x3_for(net, backward));
     (void)before;
     if (rc == NC_OK) *done = true;
     return rc;
@@ -590,6 +591,7 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
         ++li;
         if (L.kind == L_ACT && L.relu_into_pool) { pending_relu = true; continue; }   // `in` stays the pre-activation
         if (net->fuse_first && li == 0) continue;                                     // computed inside the pool launch below
+        if (L.kind == L_ACT && li > 0 && net->layers[li - 1].kind == L_CONNECT && net->layers[li - 1].act_fused) continue;   // done in the GEMM epilogue
         float* out = act_ptr(net, L);
         if (net->fuse_first && li == 2) {
             const Layer& c = net->layers[0];
@@ -642,6 +644,17 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
         case L_CONNECT: {
             const int M = n, N = L.oc, K = (int)L.in_size;
             bool done;
+            // a relu / sigmoid right behind the dense layer rides the GEMM epilogue (tensor path only): the result goes
+            // straight into the activation layer's buffer and that layer is skipped; its backward works from y alone
+            L.act_fused = false;
+            const Layer* nx = li + 1 < (int)net->layers.size() ? &net->layers[li + 1] : nullptr;
+            const bool can_fuse = nx && nx->kind == L_ACT && !nx->relu_into_pool && (nx->act == ACT_RELU || nx->act == ACT_SIGMOID) &&
+                                  nx->out_size == L.out_size;
+            if (can_fuse) {
+                rc = tc_try(net, in, W, act_ptr(net, *nx), Bp, M, N, K, false, true, st, &done, false, nx->act == ACT_RELU ? 1 : 2);
+                if (rc != NC_OK) return rc;
+                if (done) { L.act_fused = true; in = act_ptr(net, *nx); continue; }
+            }
             rc = tc_try(net, in, W, out, Bp, M, N, K, false, true, st, &done);       // Y = X . W[in][out] + b
             if (rc != NC_OK) return rc;
             if (!done && N <= 32 && (size_t)K * N * sizeof(float) <= 48 * 1024) {      // the narrow output layer
@@ -920,7 +933,8 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         case L_ACT:
             if (need_dx) {
                 const long long total = (long long)n * L.out_size;
-                act_bwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(in, out, d, dn, total, L.act, L.slope);
+                const bool fused = li > 0 && net->layers[li - 1].kind == L_CONNECT && net->layers[li - 1].act_fused;
+                act_bwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(fused ? out : in, out, d, dn, total, L.act, L.slope);   // relu: y > 0 <=> x > 0
                 NET_LAUNCH(net);
             }
             break;

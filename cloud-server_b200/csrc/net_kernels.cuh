@@ -1205,14 +1205,26 @@ __global__ void argmax_kernel(const float* __restrict__ z, int n, int classes, i
 // ---------------------------------------------------------------------------------------------
 // optimizers on the flat buffers (ApplyAdagrad / ApplyGradientDescent / ApplyAdam, TF 1.x)
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void adagrad_one(float& w, float g, float& acc, float lr) {
+    const float a = acc + g * g;
+    acc = a;
+    w -= lr * g * rsqrtf(a);
+}
+// the flat buffers come from cudaMalloc (256-byte aligned): 16-byte accesses for the body, scalars for the last count % 4
 __global__ void adagrad_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ acc, long long count, float lr) {
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
-        const float gi = g[i];
-        const float a = acc[i] + gi * gi;
-        acc[i] = a;
-        w[i] -= lr * gi * rsqrtf(a);
+    const long long stride = (long long)gridDim.x * blockDim.x, tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long n4 = count >> 2;
+    float4* w4 = reinterpret_cast<float4*>(w);
+    float4* a4 = reinterpret_cast<float4*>(acc);
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    for (long long i = tid; i < n4; i += stride) {
+        float4 wv = w4[i], av = a4[i];
+        const float4 gv = g4[i];
+        adagrad_one(wv.x, gv.x, av.x, lr); adagrad_one(wv.y, gv.y, av.y, lr);
+        adagrad_one(wv.z, gv.z, av.z, lr); adagrad_one(wv.w, gv.w, av.w, lr);
+        a4[i] = av; w4[i] = wv;
     }
+    for (long long i = (n4 << 2) + tid; i < count; i += stride) adagrad_one(w[i], g[i], acc[i], lr);
 }
 __global__ void sgd_kernel(float* __restrict__ w, const float* __restrict__ g, long long count, float lr) {
     const long long stride = (long long)gridDim.x * blockDim.x;
