@@ -53,7 +53,7 @@ template <int BN, int MODE, bool X3>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const I2cArgs ia,
                 float* __restrict__ C, const float* __restrict__ bias, int M, int N, int nkb_total, int kb_per_slice,
-                float* __restrict__ partial) {
+                float* __restrict__ partial, int act) {
     constexpr bool DGRAD = MODE == 1, WGRAD = MODE == 2;
     constexpr bool A_MN = WGRAD;                 // wgrad: the im2col rows are k-rows (pixels) of an MN-major tile
     constexpr bool B_MN = !DGRAD;
@@ -289,6 +289,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                             const float4 bv = __ldg(reinterpret_cast<const float4*>(bias + n0 + c0 + j));
                             v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
                         }
+                        if (!partial && act == 1) { v.x = fmaxf(v.x, 0.0f); v.y = fmaxf(v.y, 0.0f); v.z = fmaxf(v.z, 0.0f); v.w = fmaxf(v.w, 0.0f); }
                         *reinterpret_cast<float4*>(po + j) = v;
                     }
                 } else {
@@ -298,6 +299,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         if (col < N) {
                             float v = __uint_as_float(r[j]);
                             if (!partial && bias) v += __ldg(bias + col);
+                            if (!partial && act == 1) v = fmaxf(v, 0.0f);
                             po[j] = v;
                         }
                     }
@@ -311,12 +313,13 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 }
 
 __global__ void i2c_reduce_kernel(float* __restrict__ dst, const float* __restrict__ ws, int splits, long long count,
-                                  const float* __restrict__ bias, int ncols) {
+                                  const float* __restrict__ bias, int ncols, int act) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
         float s = 0.0f;
         for (int k = 0; k < splits; ++k) s += ws[(long long)k * count + i];
         if (bias) s += __ldg(bias + (int)(i % ncols));
+        if (act == 1) s = fmaxf(s, 0.0f);
         dst[i] = s;
     }
 }
@@ -338,14 +341,14 @@ int get_encode_i2c(nc_ctx* ctx) {
 
 template <int BN, int MODE, bool X3>
 int launch_i2c(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const I2cArgs& ia, float* C, const float* bias, int M,
-               int N, int nkb, int kbps, int splits, float* partial, cudaStream_t st) {
+               int N, int nkb, int kbps, int splits, float* partial, cudaStream_t st, int act) {
     const bool ta = X3 && MODE != 2 && NC_TMEM_A;
     const size_t smem = (size_t)StageCount<BN, X3>::value * (BM * BK * 4 + BN * BK * 4) +
                         (X3 ? (ta ? (size_t)4 * BN * BK * 4 : (size_t)LO_SLOTS * (BM * BK * 4 + BN * BK * 4)) : 0) + 1024;
     auto kfn = conv_i2c_kernel<BN, MODE, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);
-    kfn<<<grid, kThreads, smem, st>>>(ma, mb, ia, C, bias, M, N, nkb, kbps, partial);
+    kfn<<<grid, kThreads, smem, st>>>(ma, mb, ia, C, bias, M, N, nkb, kbps, partial, act);
     NC_LAUNCH_CHECK(ctx);
     return NC_OK;
 }
@@ -367,7 +370,7 @@ bool nc_tc_conv_i2c_supported(int mode, const nck::ConvGeom& g, const float* src
 
 // mode 0: src = x, wmat = W, out = y;  1: src = dy, wmat = W, out = dx;  2: src = x, wmat = dy, out = dW
 int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, const float* src, const float* wmat, float* out,
-                   const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3) {
+                   const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3, int act) {
     int rc = get_encode(ctx);
     if (rc != NC_OK) return rc;
     rc = get_encode_i2c(ctx);
@@ -412,8 +415,8 @@ int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, con
     const int nkb = (K + BK - 1) / BK;
     float* partial = splits > 1 ? ws : nullptr;
 #define NC_I2C(BN_, MODE_)                                                                                        \
-    rc = x3 ? launch_i2c<BN_, MODE_, true>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st)       \
-            : launch_i2c<BN_, MODE_, false>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st)
+    rc = x3 ? launch_i2c<BN_, MODE_, true>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act)  \
+            : launch_i2c<BN_, MODE_, false>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act)
     if (BN == 64) { if (mode == 0) NC_I2C(64, 0); else if (mode == 1) NC_I2C(64, 1); else NC_I2C(64, 2); }
     else { if (mode == 0) NC_I2C(128, 0); else if (mode == 1) NC_I2C(128, 1); else NC_I2C(128, 2); }
 #undef NC_I2C
@@ -422,7 +425,7 @@ int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, con
         const long long count = (long long)M * N;
         long long blocks = (count + 255) / 256;
         if (blocks > (long long)ctx->sm_count * 8) blocks = (long long)ctx->sm_count * 8;
-        i2c_reduce_kernel<<<(int)blocks, 256, 0, st>>>(out, ws, splits, count, bias, N);
+        i2c_reduce_kernel<<<(int)blocks, 256, 0, st>>>(out, ws, splits, count, bias, N, act);
         NC_LAUNCH_CHECK(ctx);
     }
     return NC_OK;

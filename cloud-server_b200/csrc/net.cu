@@ -121,7 +121,7 @@ struct Layer {
     int64_t stat_off = -1;                                  // norm: inv-std per channel (floats, absolute)
     bool in_is_4d = true;
     bool relu_into_pool = false;    // ACT(relu) whose only consumer is the next POOL: applied inside the pool kernels
-    bool act_fused = false;         // CONNECT whose relu / sigmoid successor was applied in the GEMM epilogue of the last forward
+    bool act_fused = false;         // CONNECT / CONV whose relu (sigmoid) successor was applied in its epilogue in the last forward
 };
 
 struct TensorInfo { int64_t off, size; int ndim; int64_t dims[4]; int init; double arg; };
@@ -591,7 +591,7 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
         ++li;
         if (L.kind == L_ACT && L.relu_into_pool) { pending_relu = true; continue; }   // `in` stays the pre-activation
         if (net->fuse_first && li == 0) continue;                                     // computed inside the pool launch below
-        if (L.kind == L_ACT && li > 0 && net->layers[li - 1].kind == L_CONNECT && net->layers[li - 1].act_fused) continue;   // done in the GEMM epilogue
+        if (L.kind == L_ACT && li > 0 && net->layers[li - 1].act_fused) continue;   // done in the producer's epilogue
         float* out = act_ptr(net, L);
         if (net->fuse_first && li == 2) {
             const Layer& c = net->layers[0];
@@ -618,6 +618,24 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
         case L_CONV: {
             const int M = n * L.oh * L.ow, N = L.oc, K = L.fh * L.fw * L.ic;
             bool done;
+            // a relu right behind the convolution (and not folded into a pool) rides the epilogue of the im2col kernel
+            L.act_fused = false;
+            {
+                const Layer* nx = li + 1 < (int)net->layers.size() ? &net->layers[li + 1] : nullptr;
+                const ConvGeom cg = geom(L);
+                if (net->math != 0 && nx && nx->kind == L_ACT && nx->act == ACT_RELU && !nx->relu_into_pool &&
+                    nx->out_size == L.out_size && nc_tc_conv_i2c_supported(0, cg, in, W)) {
+                    int Md, Nd, Kd;
+                    nc_tc_conv_dims(0, cg, n, &Md, &Nd, &Kd);
+                    rc = reserve_ws(net, nc_tc_gemm_workspace(sms, Md, Nd, Kd, nullptr, nullptr));
+                    if (rc != NC_OK) return rc;
+                    rc = nc_tc_conv_i2c(net->ctx, 0, cg, n, in, W, act_ptr(net, *nx), Bp, net->ws, net->ws_bytes, st, x3_for(net, false), 1);
+                    if (rc != NC_OK) return rc;
+                    L.act_fused = true;
+                    in = act_ptr(net, *nx);
+                    continue;
+                }
+            }
             rc = tc_conv_try(net, 0, L, n, in, W, out, Bp, st, &done);
             if (rc != NC_OK) return rc;
             (void)training;
@@ -933,7 +951,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         case L_ACT:
             if (need_dx) {
                 const long long total = (long long)n * L.out_size;
-                const bool fused = li > 0 && net->layers[li - 1].kind == L_CONNECT && net->layers[li - 1].act_fused;
+                const bool fused = li > 0 && net->layers[li - 1].act_fused;
                 act_bwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(fused ? out : in, out, d, dn, total, L.act, L.slope);   // relu: y > 0 <=> x > 0
                 NET_LAUNCH(net);
             }

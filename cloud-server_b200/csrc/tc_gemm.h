@@ -29,5 +29,6 @@ int nc_tc_conv(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, const f
 // the same forward / dgrad products with the A operand loaded by TMA in im2col mode (conv_im2col.cu):
 // stride 1, output size == input size, reduced channel count a multiple of 32
 bool nc_tc_conv_i2c_supported(int mode, const nck::ConvGeom& g, const float* src, const float* wmat);
+// act: 0 none, 1 relu applied to the result (after the bias)
 int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, const float* src, const float* wmat, float* out,
-                   const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3);
+                   const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3, int act = 0);
