@@ -28,7 +28,7 @@ constexpr int kThreads = 320;             // 10 warps: TMA, MMA, 8 x (lo split +
 constexpr unsigned kConvThreads = 256;
 // operand ring: 4 raw stages (1x: 96 KB at BN = 64, two CTAs per SM); 3xTF32 adds two lo buffers (see gemm_tcgen05.cu:
 // the raw tile is the hi part) and, owning the SM anyway, runs the ring 6 deep at BN = 64 (192 KB)
-template <int BN, bool X3> struct StageCount { static constexpr int value = (X3 && BN == 64) ? 6 : 4; };
+template <int BN, bool X3> struct StageCount { static constexpr int value = (X3 && BN <= 64) ? 6 : 4; };
 constexpr int LO_SLOTS = 2;              // two: converting block i+1 overlaps the MMAs of block i
 #ifndef NC_TMEM_A
 #define NC_TMEM_A 1
@@ -381,7 +381,7 @@ int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, con
     int M, N, K;
     if (wgrad) { M = g.fh * g.fw * g.ic; N = g.oc; K = pixels; }
     else { M = pixels; N = dgrad ? g.ic : g.oc; K = g.fh * g.fw * cwalk; }
-    const int BN = N <= 64 ? 64 : 128;
+    const int BN = (N <= 32 && !getenv("NC_CONV_NO_BN32")) ? 32 : N <= 64 ? 64 : 128;   // 32: Cout = 32 forward, Cin = 32 dgrad
     int splits, kbps;
     const size_t need = nc_tc_gemm_workspace(ctx->sm_count, M, N, K, &splits, &kbps);
     if (need > ws_bytes) return nc_set_error(ctx, NC_EINVAL, "tcgen05 conv: workspace %zu < %zu", ws_bytes, need);
@@ -417,7 +417,8 @@ int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, con
 #define NC_I2C(BN_, MODE_)                                                                                        \
     rc = x3 ? launch_i2c<BN_, MODE_, true>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act)  \
             : launch_i2c<BN_, MODE_, false>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act)
-    if (BN == 64) { if (mode == 0) NC_I2C(64, 0); else if (mode == 1) NC_I2C(64, 1); else NC_I2C(64, 2); }
+    if (BN == 32) { if (mode == 0) NC_I2C(32, 0); else if (mode == 1) NC_I2C(32, 1); else NC_I2C(32, 2); }
+    else if (BN == 64) { if (mode == 0) NC_I2C(64, 0); else if (mode == 1) NC_I2C(64, 1); else NC_I2C(64, 2); }
     else { if (mode == 0) NC_I2C(128, 0); else if (mode == 1) NC_I2C(128, 1); else NC_I2C(128, 2); }
 #undef NC_I2C
     if (rc != NC_OK) return rc;

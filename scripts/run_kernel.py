@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Run one hot-path kernel a few times (for ncu captures): python scripts/run_kernel.py <name> [batch]
-names: train_chain, predict_chain, lenet_train, lenet_predict"""
+names: train_chain, predict_chain, lenet_train, lenet_predict, deep_train"""
 import os
 import sys
 
@@ -22,13 +22,14 @@ if name in ("train_chain", "predict_chain"):
             ctx.predict_chain(x, channel_order="BGR")
 else:
     from cloud_server_b200.net import Net
-    from cloud_server_b200.configs import LENET
-    net = Net(LENET, ctx)
+    from cloud_server_b200.configs import LENET, DEEPNET
+    deep = name.startswith("deep")
+    net = Net(DEEPNET, ctx, 32, 32, 3) if deep else Net(LENET, ctx)
     net.set_math(math)
-    x = torch.rand((n, 784), device="cuda", generator=g)
+    x = torch.rand((n, 32 * 32 * 3 if deep else 784), device="cuda", generator=g)
     y = torch.nn.functional.one_hot(torch.randint(0, 10, (n,), device="cuda", generator=g), 10).float()
     for _ in range(4):
-        if name == "lenet_train":
+        if name in ("lenet_train", "deep_train"):
             net.train_step(x, y)
         else:
             net.predict(x)
