@@ -642,10 +642,16 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
             if (!done && L.ic <= 4 && K <= 32) {                       // first layer: tile kernel, lane = output channel
                 const long long ntiles = ((long long)M + 63) / 64;
                 const int blocks = (int)(ntiles < (long long)sms * 8 ? ntiles : (long long)sms * 8);
+                // first layer followed by a relu that no pool absorbs: applied on the way out, written into the relu's buffer
+                const Layer* nx = li + 1 < (int)net->layers.size() ? &net->layers[li + 1] : nullptr;
+                const bool fuse_relu = li == 0 && nx && nx->kind == L_ACT && nx->act == ACT_RELU && !nx->relu_into_pool &&
+                                       nx->out_size == L.out_size;
+                float* dst = fuse_relu ? act_ptr(net, *nx) : out;
                 for (int ob = 0; ob < (N + 31) / 32; ++ob) {
-                    conv_smallc_fwd_tile_kernel<<<blocks, 256, 0, st>>>(in, W, Bp, out, geom(L), M, ob);
+                    conv_smallc_fwd_tile_kernel<<<blocks, 256, 0, st>>>(in, W, Bp, dst, geom(L), M, ob, fuse_relu ? 1 : 0);
                     NET_LAUNCH(net);
                 }
+                if (fuse_relu) { L.act_fused = true; in = dst; continue; }
                 done = true;
             }
             const size_t smallc_smem = (size_t)K * ((N + 31) / 32 * 32) * sizeof(float);
@@ -785,6 +791,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
     loss_kernel<<<1, 1024, 0, st>>>(act_ptr(net, net->layers.back()), y_onehot, d, n, net->classes, loss_name, grad_scale, loss_out, (int*)correct_out);
     NET_LAUNCH(net);
     bool skip_fused_relu = false;
+    const float* first_relu_y = nullptr;
     for (int li = (int)net->layers.size() - 1; li >= 0; --li) {
         Layer& L = net->layers[li];
         if (L.kind == L_ACT && L.relu_into_pool && skip_fused_relu) { skip_fused_relu = false; continue; }   // done inside the pool backward
@@ -795,6 +802,12 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         float* dW = L.w_off >= 0 ? net->grads + L.w_off : nullptr;
         float* dB = L.b_off >= 0 ? net->grads + L.b_off : nullptr;
         bool need_dx = li > 0;
+        if (li == 1 && L.kind == L_ACT && net->layers[0].kind == L_CONV && net->layers[0].act_fused && net->layers[0].ic <= 4 &&
+            net->layers[0].fh * net->layers[0].fw * net->layers[0].ic <= 32) {
+            // the first layer's weight-gradient kernel masks dy with this relu's output itself (no dx is needed below it)
+            first_relu_y = act_ptr(net, L);
+            continue;
+        }
         if (net->fuse_first && li == 2) {
             // fused first block: `d` (gradient of the pooled output) goes straight to the conv weight gradient below
             skip_fused_relu = true;
@@ -880,7 +893,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                 float* pw = net->ws;
                 float* pb = net->ws + (size_t)blocks * K * N;
                 for (int ob = 0; ob < (N + 31) / 32; ++ob) {
-                    conv_smallc_wgrad_tile_kernel<<<blocks, 256, 0, st>>>(in, d, pw, pb, geom(L), M, ob);
+                    conv_smallc_wgrad_tile_kernel<<<blocks, 256, 0, st>>>(in, d, pw, pb, geom(L), M, ob, first_relu_y);
                     NET_LAUNCH(net);
                 }
                 reduce_partials_warp_kernel<<<(K * N + 7) / 8, 256, 0, st>>>(dW, pw, blocks, (long long)K * N);

@@ -372,7 +372,7 @@ __device__ __forceinline__ float smallc_fetch(const SmallcTile& S, const ConvGeo
 
 __global__ void __launch_bounds__(256)
 conv_smallc_fwd_tile_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                            float* __restrict__ y, ConvGeom g, long long M, int ob) {
+                            float* __restrict__ y, ConvGeom g, long long M, int ob, int relu) {
     __shared__ SmallcTile S;
     __shared__ __align__(16) float colT[32][64];        // [tap][position]
     const int T = g.fh * g.fw * g.ic;
@@ -408,7 +408,7 @@ conv_smallc_fwd_tile_kernel(const float* __restrict__ x, const float* __restrict
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 const long long m = m0 + warp * 8 + k;
-                if (m < M) y[m * g.oc + co] = acc[k] + bv;
+                if (m < M) { const float v = acc[k] + bv; y[m * g.oc + co] = relu ? fmaxf(v, 0.0f) : v; }
             }
         }
     }
@@ -417,7 +417,7 @@ conv_smallc_fwd_tile_kernel(const float* __restrict__ x, const float* __restrict
 // partial_w[block][T*oc] and partial_b[block][oc] hold this CTA's sums for output-channel block `ob`
 __global__ void __launch_bounds__(256)
 conv_smallc_wgrad_tile_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ partial_w,
-                              float* __restrict__ partial_b, ConvGeom g, long long M, int ob) {
+                              float* __restrict__ partial_b, ConvGeom g, long long M, int ob, const float* __restrict__ relu_y) {
     __shared__ SmallcTile S;
     __shared__ __align__(16) float col[64][32];         // [position][tap]
     __shared__ float red[8][33];
@@ -440,7 +440,10 @@ conv_smallc_wgrad_tile_kernel(const float* __restrict__ x, const float* __restri
         for (int k = 0; k < 8; ++k) {
             const int p = warp * 8 + k;
             const long long m = m0 + p;
-            const float gv = (m < M && co < g.oc) ? __ldg(dy + m * g.oc + co) : 0.0f;
+            float gv = (m < M && co < g.oc) ? __ldg(dy + m * g.oc + co) : 0.0f;
+            // relu_y: the relu behind this convolution was applied in its epilogue and has no backward launch of its own;
+            // dy is then the gradient of the relu's output and the mask comes from that output
+            if (relu_y && m < M && co < g.oc && !(__ldg(relu_y + m * g.oc + co) > 0.0f)) gv = 0.0f;
             accb += gv;
 #pragma unroll
             for (int t4 = 0; t4 < 8; ++t4) {
