@@ -28,11 +28,19 @@ constexpr int kThreads = 320;             // 10 warps: TMA, MMA, 8 x (lo split +
 constexpr unsigned kConvThreads = 256;
 // operand ring: 4 raw stages (1x: 96 KB at BN = 64, two CTAs per SM); 3xTF32 adds two lo buffers (see gemm_tcgen05.cu:
 // the raw tile is the hi part) and, owning the SM anyway, runs the ring 6 deep at BN = 64 (192 KB)
-template <int BN, bool X3> struct StageCount { static constexpr int value = (X3 && BN <= 64) ? 6 : 4; };
 constexpr int LO_SLOTS = 2;              // two: converting block i+1 overlaps the MMAs of block i
 #ifndef NC_TMEM_A
 #define NC_TMEM_A 1
 #endif
+// 3xTF32 at BN <= 64: ring depth and number of lo / TMEM-A buffers.  6 + 4 owns the SM (192 KB, 512 TMEM columns);
+// 3 + 2 (88 KB, 256 columns) lets two CTAs share it, which hides the per-CTA prologue and epilogue of short-K tiles.
+#ifndef NC_I2C_X3_STAGES
+#define NC_I2C_X3_STAGES 3
+#endif
+#ifndef NC_I2C_X3_LOS
+#define NC_I2C_X3_LOS 2
+#endif
+template <int BN, bool X3> struct StageCount { static constexpr int value = (X3 && BN <= 64) ? NC_I2C_X3_STAGES : 4; };
 
 struct I2cArgs {
     int W, H;              // spatial size (input == output: stride 1, SAME)
@@ -50,7 +58,7 @@ __device__ __forceinline__ void tma_load_im2col(unsigned dst, const CUtensorMap*
 }
 
 template <int BN, int MODE, bool X3>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, BN <= 64 ? 2 : 1)
 conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const I2cArgs ia,
                 float* __restrict__ C, const float* __restrict__ bias, int M, int N, int nkb_total, int kb_per_slice,
                 float* __restrict__ partial, int act) {
@@ -66,9 +74,9 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // TA: the K-major A operand of the 3xTF32 product lives in tensor memory (see gemm_tcgen05.cu): hi and lo values of a
     // row are parked in TMEM columns [BN, BN + 256) by the split warps, only B and B_lo are read from shared memory
     constexpr bool TA = X3 && !A_MN && NC_TMEM_A;
-    constexpr int LOS = TA ? 4 : LO_SLOTS;                           // lo buffers in flight: the split warps may run this far ahead of the MMAs
+    constexpr int LOS = TA ? (BN <= 64 ? NC_I2C_X3_LOS : 4) : LO_SLOTS;   // lo buffers in flight: the split warps may run this far ahead of the MMAs
     constexpr unsigned LO_BYTES = TA ? B_BYTES : HI_BYTES;
-    constexpr unsigned TCOLS = TA ? 512u : (unsigned)BN;
+    constexpr unsigned TCOLS = TA ? ((unsigned)BN + 64u * LOS <= 256u ? 256u : 512u) : (unsigned)BN;
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) unsigned long long s_full[STAGES], s_empty[STAGES], s_ready[4], s_loempty[4], s_tmem_full;
     __shared__ unsigned s_tmem_base;
@@ -344,7 +352,7 @@ int launch_i2c(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const 
                int N, int nkb, int kbps, int splits, float* partial, cudaStream_t st, int act) {
     const bool ta = X3 && MODE != 2 && NC_TMEM_A;
     const size_t smem = (size_t)StageCount<BN, X3>::value * (BM * BK * 4 + BN * BK * 4) +
-                        (X3 ? (ta ? (size_t)4 * BN * BK * 4 : (size_t)LO_SLOTS * (BM * BK * 4 + BN * BK * 4)) : 0) + 1024;
+                        (X3 ? (ta ? (size_t)(BN <= 64 ? NC_I2C_X3_LOS : 4) * BN * BK * 4 : (size_t)LO_SLOTS * (BM * BK * 4 + BN * BK * 4)) : 0) + 1024;
     auto kfn = conv_i2c_kernel<BN, MODE, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);
