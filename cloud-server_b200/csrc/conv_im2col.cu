@@ -26,8 +26,8 @@ namespace {
 constexpr int BM = 128, BK = 32;
 constexpr int kThreads = 320;             // 10 warps: TMA, MMA, 8 x (lo split + epilogue)
 constexpr unsigned kConvThreads = 256;
-// operand ring: 4 raw stages (1x: 96 KB at BN = 64, two CTAs per SM); 3xTF32 adds two lo buffers (see gemm_tcgen05.cu:
-// the raw tile is the hi part) and, owning the SM anyway, runs the ring 6 deep at BN = 64 (192 KB)
+// operand ring: 4 raw stages (1x: 96 KB at BN = 64, two CTAs per SM); 3xTF32 (see gemm_tcgen05.cu: the raw tile is the hi
+// part, A's hi / lo live in tensor memory) runs 3 stages + 2 B_lo buffers at BN <= 64 so that two CTAs still share an SM
 constexpr int LO_SLOTS = 2;              // two: converting block i+1 overlaps the MMAs of block i
 #ifndef NC_TMEM_A
 #define NC_TMEM_A 1
