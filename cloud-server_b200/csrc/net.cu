@@ -577,6 +577,25 @@ static FirstGeom first_geom(const Layer& c, const Layer& p) {
     return g;
 }
 
+// first layer without a pool behind it: the register-patch kernels take 3x3 / 5x5 filters on 1 or 3 channels, stride 1
+static bool patch_geom(const Layer& c, PatchGeom* g, size_t* smem) {
+    if (c.kind != L_CONV || c.sh != 1 || c.sw != 1 || c.fh != c.fw || (c.fh != 3 && c.fh != 5) || (c.ic != 1 && c.ic != 3)) return false;
+    if (getenv("NC_NO_FIRST_PATCH")) return false;
+    const int gpr = (c.ow + 3) / 4, seg = ((c.fw + 3) * c.ic + 3) / 4 * 4;
+    g->ih = c.ih; g->iw = c.iw; g->pt = c.pt; g->pl = c.pl; g->oh = c.oh; g->ow = c.ow; g->oc = c.oc;
+    g->th = c.oh + c.fh - 1;
+    g->tws = (4 * gpr * c.ic + seg + 3) / 4 * 4;
+    *smem = (size_t)g->th * g->tws * sizeof(float);
+    return *smem <= 48 * 1024;
+}
+#define NC_PATCH_DISPATCH(KERNEL, c, ...)                                                         \
+    do {                                                                                          \
+        if ((c).fh == 3 && (c).ic == 3) KERNEL<3, 3, 3> __VA_ARGS__;                               \
+        else if ((c).fh == 3) KERNEL<3, 3, 1> __VA_ARGS__;                                         \
+        else if ((c).ic == 3) KERNEL<5, 5, 3> __VA_ARGS__;                                         \
+        else KERNEL<5, 5, 1> __VA_ARGS__;                                                          \
+    } while (0)
+
 // ------------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------------
@@ -647,8 +666,15 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
                 const bool fuse_relu = li == 0 && nx && nx->kind == L_ACT && nx->act == ACT_RELU && !nx->relu_into_pool &&
                                        nx->out_size == L.out_size;
                 float* dst = fuse_relu ? act_ptr(net, *nx) : out;
+                PatchGeom pg; size_t psmem = 0;
+                const bool patch = li == 0 && patch_geom(L, &pg, &psmem);
                 for (int ob = 0; ob < (N + 31) / 32; ++ob) {
-                    conv_smallc_fwd_tile_kernel<<<blocks, 256, 0, st>>>(in, W, Bp, dst, geom(L), M, ob, fuse_relu ? 1 : 0);
+                    if (patch) {
+                        const int pblocks = n < sms * 4 ? n : sms * 4;
+                        NC_PATCH_DISPATCH(first_conv_patch_fwd_kernel, L, <<<pblocks, 256, psmem, st>>>(in, W, Bp, dst, pg, n, ob, fuse_relu ? 1 : 0));
+                    } else {
+                        conv_smallc_fwd_tile_kernel<<<blocks, 256, 0, st>>>(in, W, Bp, dst, geom(L), M, ob, fuse_relu ? 1 : 0);
+                    }
                     NET_LAUNCH(net);
                 }
                 if (fuse_relu) { L.act_fused = true; in = dst; continue; }

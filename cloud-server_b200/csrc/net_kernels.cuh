@@ -932,6 +932,75 @@ first_conv_wgrad_from_pool_c1_kernel(const float* __restrict__ x, const float* _
     }
 }
 
+// ---- first layer NOT followed by a pool (conv -> relu -> conv ..., the C5 style): same picture-tile scheme, compile-time
+// filter.  A warp computes 4 horizontally adjacent outputs from FH row segments of (FW + 3) * IC floats read with 16-byte
+// shared loads; lane = output channel.  The 64-position im2col tiles of conv_smallc_*_tile_kernel spend two thirds of
+// their instructions building the im2col; here that is one coalesced tile load per picture.  (Forward only: the same
+// scheme for the weight gradient measured slower than conv_smallc_wgrad_tile_kernel -- 188 vs 120 us on C5 -- and was dropped.)
+struct PatchGeom {
+    int ih, iw, pt, pl;      // input, padding before
+    int oh, ow, oc;          // output (stride 1)
+    int th, tws;             // tile rows, tile row stride in floats (multiple of 4, >= (ow + FW + 3) * IC)
+};
+
+template <int IC>
+__device__ __forceinline__ void patch_load_tile(float* tile, const float* __restrict__ xi, const PatchGeom& g) {
+    const int total = g.th * g.tws;
+    for (int e = threadIdx.x; e < total; e += blockDim.x) {
+        const int r = e / g.tws, q = e - r * g.tws;
+        const int c = q / IC, ch = q - c * IC;
+        const int iy = r - g.pt, ix = c - g.pl;
+        tile[e] = (iy >= 0 && iy < g.ih && ix >= 0 && ix < g.iw) ? __ldg(xi + ((long long)iy * g.iw + ix) * IC + ch) : 0.0f;
+    }
+}
+
+template <int FH, int FW, int IC>
+__global__ void __launch_bounds__(256)
+first_conv_patch_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                            float* __restrict__ y, PatchGeom g, int n, int ob, int relu) {
+    extern __shared__ __align__(16) float tile[];
+    constexpr int T = FH * FW * IC, SEG = ((FW + 3) * IC + 3) / 4 * 4;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    float wreg[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) wreg[t] = co < g.oc ? __ldg(w + (long long)t * g.oc + co) : 0.0f;
+    const float bv = (bias && co < g.oc) ? __ldg(bias + co) : 0.0f;
+    const int gpr = (g.ow + 3) >> 2, ngroups = g.oh * gpr;
+    for (int img = blockIdx.x; img < n; img += gridDim.x) {
+        __syncthreads();
+        patch_load_tile<IC>(tile, x + (long long)img * g.ih * g.iw * IC, g);
+        __syncthreads();
+        for (int gi = warp; gi < ngroups; gi += 8) {
+            const int oy = gi / gpr, ox0 = (gi - oy * gpr) * 4;
+            float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+            for (int r = 0; r < FH; ++r) {
+                float seg[SEG];
+                const float4* sp = reinterpret_cast<const float4*>(tile + (oy + r) * g.tws + ox0 * IC);
+#pragma unroll
+                for (int v = 0; v < SEG / 4; ++v) { const float4 q = sp[v]; seg[4 * v] = q.x; seg[4 * v + 1] = q.y; seg[4 * v + 2] = q.z; seg[4 * v + 3] = q.w; }
+#pragma unroll
+                for (int c = 0; c < FW; ++c)
+#pragma unroll
+                    for (int ch = 0; ch < IC; ++ch) {
+                        const float wv = wreg[(r * FW + c) * IC + ch];
+#pragma unroll
+                        for (int p = 0; p < 4; ++p) acc[p] = fmaf(seg[(p + c) * IC + ch], wv, acc[p]);
+                    }
+            }
+            if (co < g.oc) {
+#pragma unroll
+                for (int p = 0; p < 4; ++p)
+                    if (ox0 + p < g.ow) {
+                        const float v = acc[p] + bv;
+                        y[(((long long)img * g.oh + oy) * g.ow + ox0 + p) * g.oc + co] = relu ? fmaxf(v, 0.0f) : v;
+                    }
+            }
+        }
+    }
+}
+
 // partial_w[block][T*oc] / partial_b[block][oc] for output-channel block `ob` (summed by reduce_partials_warp_kernel)
 __global__ void __launch_bounds__(256)
 first_conv_wgrad_from_pool_kernel(const float* __restrict__ x, const float* __restrict__ dpool, const uint8_t* __restrict__ arg,

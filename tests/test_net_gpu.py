@@ -21,6 +21,11 @@ CONFIGS = {
         {"layer": "active", "active_func": "relu"},
         {"layer": "connect", "hidden": 16}, {"layer": "norm"}, {"layer": "active"}]}, 13, 11, 2, 6),
     "deep": (tfref.DEEPNET, 32, 32, 3, 8),
+    # first layers that no pool follows take the register-patch kernels (3x3 / 5x5 on 1 or 3 channels)
+    "first5x5_rgb": ({"middle_layer": [{"layer": "conv", "filter": [5, 5, 40], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
+                                       {"layer": "connect", "hidden": 16}]}, 12, 10, 3, 7),
+    "first5x5_gray_sigmoid": ({"middle_layer": [{"layer": "conv", "filter": [5, 5, 8]}, {"layer": "active"},
+                                                {"layer": "connect", "hidden": 16}]}, 9, 14, 1, 5),
     # even filter sizes: SAME padding is asymmetric (extra row / column at the bottom / right), which the TMA im2col walk
     # has to mirror in its window origin, forward and (mirrored) in dgrad; odd picture size -> partial last tiles
     "even_filters": ({"middle_layer": [
