@@ -527,6 +527,8 @@ predict_chain_mma_kernel(const uint8_t* __restrict__ src, long long img_stride, 
     const unsigned d_dst = 4u * (unsigned)kThreads + dr * padw;          // words per step without wrap
     const unsigned dst0 = it_r0 * (unsigned)pitch + 4u * it_g0;
     const unsigned full_items = (unsigned)sr * ipr, last_items = (unsigned)(h - (nstages - 1) * sr) * ipr;
+    const bool two_items = full_items == 2u * (unsigned)kThreads;
+    const unsigned dst1 = dst0 + d_dst + ((it_g0 + dg >= ipr) ? padw : 0u);       // gray offset of this thread's second item
     // per-buffer bases (buffer = s & 1), selected per stage instead of recomputed
     const uint4* p_b0 = reinterpret_cast<const uint4*>(raw) + 3u * (unsigned)tid;
     const uint4* p_b1 = reinterpret_cast<const uint4*>(raw + stage_bytes) + 3u * (unsigned)tid;
@@ -545,7 +547,23 @@ predict_chain_mma_kernel(const uint8_t* __restrict__ src, long long img_stride, 
         if (worker) mbar_wait(bar0 + 8u * odd, (unsigned)((s >> 1) & 1));
         // ---------------- phase 1: staged bytes -> rgb2l -> gray block (s & 1)
         unsigned* gblk = odd ? g_b1 : g_b0;
-        if (worker) {
+        if (worker && !last && two_items) {
+            // the common shape (1024 wide, 10-row stages): exactly two items per thread, straight-line, all six loads first
+            const uint4* p = odd ? p_b1 : p_b0;
+            const uint4 q0 = p[0], q1 = p[1], q2 = p[2];
+            const uint4 r0 = p[3 * kThreads], r1 = p[3 * kThreads + 1], r2 = p[3 * kThreads + 2];
+            uint4 o;
+            o.x = gray4(q0.x, q0.y, q0.z, A01, A2_, A_0, A12);
+            o.y = gray4(q0.w, q1.x, q1.y, A01, A2_, A_0, A12);
+            o.z = gray4(q1.z, q1.w, q2.x, A01, A2_, A_0, A12);
+            o.w = gray4(q2.y, q2.z, q2.w, A01, A2_, A_0, A12);
+            *reinterpret_cast<uint4*>(gblk + dst0) = o;
+            o.x = gray4(r0.x, r0.y, r0.z, A01, A2_, A_0, A12);
+            o.y = gray4(r0.w, r1.x, r1.y, A01, A2_, A_0, A12);
+            o.z = gray4(r1.z, r1.w, r2.x, A01, A2_, A_0, A12);
+            o.w = gray4(r2.y, r2.z, r2.w, A01, A2_, A_0, A12);
+            *reinterpret_cast<uint4*>(gblk + dst1) = o;
+        } else if (worker) {
             const unsigned items = last ? last_items : full_items;
             unsigned g = it_g0;
             unsigned dst = dst0;
