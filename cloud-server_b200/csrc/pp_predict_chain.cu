@@ -383,14 +383,14 @@ predict_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int 
 // u8 x s8 -> s32 warp MMA (m16n8k32).  Warp v owns output columns 2v and 2v+1: the 8 MMA
 // columns are {o0d0, o0d1, o1d0, o1d1, o0d2, 0, o1d2, 0}, its K range is the union of the two tap
 // windows (nch 32-pixel chunks from kw[v]), and its B fragments are constant for the whole
-// picture, so they live in registers.  The MMA's K slots are permuted (slots 4t..4t+3 and
-// 16+4t..16+4t+3 of thread-in-group t = pixels 8t..8t+7 of the chunk) so a thread's A registers are
-// one 8-byte shared load per row.  One raw stage = one gray block of `sr` <= 16 rows, gray
+// picture, so they live in registers.  A fragments come from the gray block with one ldmatrix.x4
+// per chunk (the 16 x 32-byte u8 tile is four 8 x 16-byte matrices; K ranges start on 16-pixel
+// boundaries).  One raw stage = one gray block of `sr` <= 16 rows, gray
 // blocks double buffered: a single __syncthreads per stage.
-// Costs 9 MMA + 36 LDS per warp and block where the dp4a pass needs ~270 instructions.
+// Costs 9 MMA + 9 LDSM per warp and block where the dp4a pass needs ~270 instructions.
 // ---------------------------------------------------------------------------------------------
 struct MmaPlan {
-    int kw[kOut / 2];        // first gray word (4 pixels) of the warp's K range, even
+    int kw[kOut / 2];        // first gray word (4 pixels) of the warp's K range, a multiple of 4 (16-byte aligned rows for ldmatrix)
     int nch;                 // 32-pixel chunks in every warp's range
 };
 
@@ -517,7 +517,10 @@ predict_chain_mma_kernel(const uint8_t* __restrict__ src, long long img_stride, 
         const uint2 b = __ldg(g_bfrag + ((size_t)wv * NCH + c) * 32 + lane);
         bx[c] = b.x; by[c] = b.y;
     }
-    const unsigned a_off = (unsigned)gid * (unsigned)pitch + (unsigned)g_plan->kw[wv] + 2u * (unsigned)tig;
+    // ldmatrix address of this lane: the A fragment of one chunk is four 8-row x 16-byte matrices (rows 0-7 / 8-15, pixel
+    // bytes 0-15 / 16-31 of the chunk); lanes 8m .. 8m+7 supply the row addresses of matrix m.  Byte offset in a gray block.
+    const unsigned a_off = ((unsigned)((lane & 7) + ((lane >> 3) & 1) * 8) * (unsigned)pitch + (unsigned)g_plan->kw[wv]) * 4u +
+                           (unsigned)(lane >> 4) * 16u;
 
     // phase-1 item walk: item = 16 pixels = 48 contiguous staged bytes -> 4 gray words; items of a stage are
     // contiguous in the raw buffer (row_bytes = 48 ipr), the gray rows have `pitch - 4 ipr` words of padding
@@ -622,13 +625,14 @@ predict_chain_mma_kernel(const uint8_t* __restrict__ src, long long img_stride, 
         }
         // ---------------- phase 2: horizontal pass, one m16n8k32 MMA per 32-pixel chunk
         if (worker) {
-            const uint2* a_lo = reinterpret_cast<const uint2*>(gblk + a_off);
-            const uint2* a_hi = a_lo + 4u * (unsigned)pitch;
+            const unsigned a_addr = (unsigned)__cvta_generic_to_shared(gblk) + a_off;
             int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
 #pragma unroll
             for (int c = 0; c < NCH; ++c) {
-                const uint2 lo = a_lo[4 * c], hi = a_hi[4 * c];           // 8 consecutive pixels of rows gid, gid + 8
-                mma_u8s8(c0, c1, c2, c3, lo.x, hi.x, lo.y, hi.y, bx[c], by[c]);
+                unsigned a0, a1, a2, a3;                                   // one ldmatrix = the whole 16 x 32-byte A fragment
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3) : "r"(a_addr + 32u * (unsigned)c));
+                mma_u8s8(c0, c1, c2, c3, a0, a1, a2, a3, bx[c], by[c]);
             }
             // columns held: (2 tig, 2 tig + 1) = tig 0: o0 d0,d1 | tig 1: o1 d0,d1 | tig 2: o0 d2,0 | tig 3: o1 d2,0
             int p_lo = tig < 2 ? c0 + c1 * 256 : c0 * 65536;
@@ -667,14 +671,14 @@ void build_mma_plan(const PilAxisHost& ax, int w, MmaPlan* plan, std::vector<uin
     for (int v = 0; v < kOut / 2; ++v) {
         const int lo = std::min(ax.xmin[2 * v], ax.xmin[2 * v + 1]);
         const int hi = std::max(ax.xmin[2 * v] + ax.cnt[2 * v], ax.xmin[2 * v + 1] + ax.cnt[2 * v + 1]);
-        k0s[v] = lo & ~7;
+        k0s[v] = lo & ~15;
         maxch = std::max(maxch, (hi - k0s[v] + 31) / 32);
     }
     plan->nch = maxch;
     // every warp runs maxch chunks; slide a range down where it would pass the 32 pixels of slack behind the row
     for (int v = 0; v < kOut / 2; ++v) {
         int k0 = k0s[v];
-        const int limit = (w + 32 - 32 * maxch) & ~7;
+        const int limit = (w + 32 - 32 * maxch) & ~15;
         if (k0 > limit) k0 = limit;
         if (k0 < 0) k0 = 0;
         plan->kw[v] = k0 / 4;
@@ -700,10 +704,10 @@ void build_mma_plan(const PilAxisHost& ax, int w, MmaPlan* plan, std::vector<uin
                 if (col_o[n] >= 0) {
                     const int o = 2 * v + col_o[n];
                     for (int i = 0; i < 4; ++i) {
-                        // K slots 4 tig + i (b0) and 16 + 4 tig + i (b1) are pixels 8 tig + i and 8 tig + 4 + i of the chunk
-                        const int x0 = plan->kw[v] * 4 + 32 * c + 8 * tig + i;
+                        // K slots 4 tig + i (b0) and 16 + 4 tig + i (b1) are those pixels of the chunk
+                        const int x0 = plan->kw[v] * 4 + 32 * c + 4 * tig + i;
                         q.x |= ((unsigned)digit(o, x0, col_d[n]) & 255u) << (8 * i);
-                        q.y |= ((unsigned)digit(o, x0 + 4, col_d[n]) & 255u) << (8 * i);
+                        q.y |= ((unsigned)digit(o, x0 + 16, col_d[n]) & 255u) << (8 * i);
                     }
                 }
                 (*frag)[((size_t)v * maxch + c) * 32 + lane] = q;
@@ -845,8 +849,8 @@ static int predict_impl(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, in
         if (!getenv("NC_PREDICT_NO_MMA") && tabs.bstride <= 16) {
             const unsigned ipr = (unsigned)w / 16;
             int pitch = w / 4 + 8;                       // >= 8 words of slack: the last chunk may overrun the row by < 32 pixels
-            while ((pitch & 15) != 8) pitch += 4;        // = 8 mod 16 words: 16-byte item stores, and the 4 rows x 8 words of a
-                                                         // half-warp's 8-byte A loads cover 32 distinct banks
+            while ((pitch & 7) != 4) pitch += 4;         // = 4 mod 8 words: 16-byte item stores, and the 8 rows x 16 bytes of an
+                                                         // ldmatrix 8x8 matrix fall on 8 distinct 16-byte bank groups
             // rows per stage: a multiple of the 320-thread item walk when possible (w = 1024: 10 rows = 2 items per thread)
             int sr = 16;
             while (sr > 1 && (size_t)sr * w * 3 > 32 * 1024) --sr;
