@@ -435,7 +435,7 @@ def run_ours(args, rank, local_rank, world):
                      % (100 * ms_p / (ms_p + ms_t)), "peak_source": peak_src + " (burst copy bandwidth)",
                      "algorithmic_bytes_per_launch": ALG_BYTES_PREDICT_CHAIN * n, "launch_ms": ms_p,
                      "note": "peak = copy bandwidth (half reads, half writes); this kernel only reads (99.7 %), and a "
-                             "read-only stream can pass the copy figure: frac > 1 is possible.  ncu: 77-82 % of the 8.18 TB/s "
+                             "read-only stream can pass the copy figure: frac > 1 is possible.  CUDA events: 82-85 % of the 8.18 TB/s "
                              "pin rate (profiles/r01n_ncu_preprocess.md)"},
         "train_side_chain": {"value": world * n / (ms_t * 1e-3), "unit": "images/s", "launch_ms": ms_t,
                              "roofline": {"bound": "hbm", "achieved": ach_t, "peak": peak, "unit": "GB/s", "frac": ach_t / peak,
