@@ -36,8 +36,10 @@ _SIGS = {
     "nc_pp_cubic_table": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p]),
     "nc_pp_pil_table": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "nc_pp_gaussian_q8": (C.c_int, [C.c_int, C.c_void_p]),
+    "nc_crc32c": (C.c_uint32, [C.c_void_p, C.c_size_t, C.c_uint32]),
     "nc_pp_normalise": (C.c_int, [C.c_void_p, c_u8p, C.c_int64, c_f32p, C.c_void_p]),
     "nc_gather_rows": (C.c_int, [C.c_void_p, c_f32p, C.c_int64, C.c_int, C.c_void_p, C.c_int, c_f32p, C.c_void_p]),
+    "nc_gather_rows_status": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nc_matmul": (C.c_int, [C.c_void_p, c_f32p, c_f32p, c_f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_f32p, C.c_void_p]),
     "nc_dense_forward_noalloc": (C.c_int, [C.c_void_p, c_f32p, c_f32p, c_f32p, C.c_int, C.c_int, C.c_int, c_f32p, C.c_void_p]),
     "nc_net_create": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64,
@@ -60,6 +62,8 @@ _SIGS = {
                                     C.c_void_p]),
     "nc_net_global_step": (C.c_int64, [C.c_void_p]),
     "nc_net_advance_step": (C.c_int, [C.c_void_p, C.c_int64]),
+    "nc_net_arena_generation": (C.c_int64, [C.c_void_p]),
+    "nc_net_reserve": (C.c_int, [C.c_void_p, C.c_int]),
     "nc_nccl_unique_id": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p]),
     "nc_net_attach_nccl": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int]),
     "nc_net_allreduce_grads": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -103,6 +107,8 @@ def check(ctx_handle, rc):
     if rc != NC_OK:
         msg = lib().nc_last_error(ctx_handle)
         msg = msg.decode("utf-8", "replace") if msg else ""
+        if msg.startswith("IndexError"):
+            raise IndexError(msg)
         if rc in (NC_EINVAL, NC_ECONFIG):
             raise ValueError(msg)
         raise NcError(rc, msg)

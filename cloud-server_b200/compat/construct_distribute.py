@@ -9,7 +9,9 @@ Differences that follow from the design, not from the interface:
   * --job_name=ps returns at once: there is no parameter server, the weights live on the GPU.
   * under torchrun (WORLD_SIZE > 1) every rank trains on its slice of each batch and the flat
     gradient buffer is all-reduced over NCCL (net.DataParallel).
-  * checkpoints are .npz (+ an empty .meta marker so get_model() finds the newest step).
+  * checkpoints are TensorFlow V2 bundles (<model>.ckpt-<step>.index / .data-00000-of-00001, written without TensorFlow by
+    cloud_server_b200.tf_bundle with the variable names the reference's Saver would use) + an empty .meta marker so
+    get_model() finds the newest step; the .npz files of earlier versions of this script are still read.
 As in the reference the optimizer that runs is Adagrad(1e-4) and the batch is 50 whatever the
 config says (:372-373, :403); pass --honor_config to use config["optimizer_name"/"learning_rate"].
 """
@@ -124,14 +126,15 @@ class Datasets(object):
         self.train, self.validation, self.test = train, validation, test
 
 
-def read_user_data(path, ratio):
+def read_user_data(path, ratio, base_dir=None):
     """:424-463: tag.json from `path`, pictures from ./data (hard-coded there, :441), *.jpg only,
-    labels by file name, split at int(N*ratio) without pre-shuffle."""
+    labels by file name, split at int(N*ratio) without pre-shuffle.  base_dir (extension): what the
+    reference's working directory would be (the model directory the job is started in)."""
     from PIL import Image
     images, labels = [], []
-    with open(os.path.join(path, 'tag.json')) as file:
+    with open(os.path.join(base_dir or '', path, 'tag.json')) as file:
         lablejson = json.load(file)
-    path = 'data'
+    path = os.path.join(base_dir, 'data') if base_dir else 'data'
     for (root, dirs, files) in os.walk(path):
         for filename in files:
             if filename.endswith('.jpg'):
@@ -147,27 +150,36 @@ def read_user_data(path, ratio):
 
 
 def save_checkpoint(net, prefix, step, config, opt_id):
+    """what the Supervisor's Saver leaves in logdir (:385-392): <prefix>-<step>.index / .data-00000-of-00001 / .meta"""
+    from cloud_server_b200 import tf_bundle
     os.makedirs(os.path.dirname(prefix) or ".", exist_ok=True)
     base = "%s-%d" % (prefix, step)
-    np.savez(base + ".npz", params=net.get_params(), state=net.get_state(opt_id), opt=opt_id, global_step=step,
-             config=json.dumps(config))
-    open(base + ".meta", "w").close()
-    open(base + ".index", "w").close()
+    tf_bundle.save_net(base, net, opt_id)
 
 
 def load_checkpoint(net, base):
-    z = np.load(base + ".npz")
+    """saver.restore(sess, base) (construct_inference.py:336-339)"""
+    if os.path.exists(base + ".index") and os.path.getsize(base + ".index") > 0:
+        from cloud_server_b200 import tf_bundle
+        return tf_bundle.load_net(base, net)
+    z = np.load(base + ".npz")                     # written by earlier versions of this script
     net.set_params(z["params"])
     net.set_state(int(z["opt"]), z["state"], int(z["global_step"]))
     return int(z["global_step"])
 
 
-def main(argv=None):
+def main(argv=None, base_dir=None, should_stop=None, keep=None):
+    """base_dir / should_stop / keep (extensions, for in-process callers -- compat/construct_view.py): the directory the
+    reference would `cd` into before starting the script; a callable polled where the reference polls sv.should_stop()
+    (:402); a dict that receives the live net ("net") and its step ("step") when training ends."""
     FLAGS = build_flags(argv)
     model_name = FLAGS.model_name
-    pre = FLAGS.save_path
-    save_path = FLAGS.save_path + model_name + ".ckpt"
-    result_path = FLAGS.result
+
+    def _p(path):
+        return path if (not base_dir or os.path.isabs(path)) else os.path.join(base_dir, path)
+    pre = _p(FLAGS.save_path)
+    save_path = pre + model_name + ".ckpt"
+    result_path = _p(FLAGS.result)
     ratio = float(FLAGS.ratio)
     config = json.loads(FLAGS.config)
     iters = int(config["iter"])
@@ -192,10 +204,17 @@ def main(argv=None):
     torch.cuda.set_device(local_rank)
     if world > 1 and not torch.distributed.is_initialized():
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    if FLAGS.seed is not None:
+    if world > 1:
+        # every rank must cut its rows out of the SAME shuffled batch: one shuffle seed for all (rank 0's draw unless --seed)
+        box = [FLAGS.seed if FLAGS.seed is not None else int(np.random.SeedSequence().entropy % (2 ** 32))]
+        torch.distributed.broadcast_object_list(box, src=0)
+        np.random.seed(box[0])
+        if FLAGS.batch % world:
+            raise ValueError("batch %d is not a multiple of the %d ranks: the global-batch gradient would be mis-scaled" % (FLAGS.batch, world))
+    elif FLAGS.seed is not None:
         np.random.seed(FLAGS.seed)
     ctx = Context(local_rank)
-    mnist = read_user_data(FLAGS.data_dir, ratio)
+    mnist = read_user_data(FLAGS.data_dir, ratio, base_dir)
     x = placeholder(28, 28, 1)
     y_conv = get_net(net_type, net_config, x, None)
     loss = loss_function(loss_name, y_conv, None)
@@ -224,7 +243,7 @@ def main(argv=None):
         pred = net.predict(xs).cpu().numpy()
         return float(np.mean(pred == np.asarray(labels).argmax(1))) if len(pred) else float("nan")
 
-    while step < iters:
+    while not (should_stop and should_stop()) and step < iters:
         bx, by = mnist.train.next_batch(batch)
         step = net.global_step
         if step % 100 == 0:
@@ -258,6 +277,8 @@ def main(argv=None):
         save_checkpoint(net, save_path, net.global_step, config, opt_id)
     if world > 1:
         torch.distributed.barrier()
+    if keep is not None:
+        keep["net"], keep["step"] = net, net.global_step
     return 0
 
 

@@ -24,6 +24,7 @@
 // cudaGetSymbolAddress, no allocation) and remembers it.  Make that first call before starting
 // any stream capture on that device.
 #include "nc_internal.h"
+#include <atomic>
 
 #define NC_NOALLOC_SCRATCH_FLOATS (1u << 20)                       // 4 MiB
 #define NC_NOALLOC_SCRATCH_BYTES (NC_NOALLOC_SCRATCH_FLOATS * 4u)
@@ -39,8 +40,8 @@ constexpr int TM = 64, TN = 64, TK = 16;
 __global__ void __launch_bounds__(256)
 dense_partial_kernel(const float* __restrict__ x, const float* __restrict__ w, int M, int N, int K, int kslice,
                      float* __restrict__ partial) {
-    __shared__ float As[TK][TM + 4];
-    __shared__ float Bs[TK][TN + 4];
+    __shared__ __align__(16) float As[TK][TM + 4];     // read back through float4: rows are (TM + 4) * 4 bytes, a multiple of 16
+    __shared__ __align__(16) float Bs[TK][TN + 4];
     const int tid = threadIdx.x;
     const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
     const int kbeg = blockIdx.z * kslice, kend = min(K, kbeg + kslice);
@@ -101,7 +102,9 @@ __global__ void dense_reduce_kernel(float* __restrict__ y, const float* __restri
 }
 
 constexpr int kMaxDevices = 64;
-float* g_scratch_addr[kMaxDevices];   // device address of g_noalloc_scratch, per device ordinal
+// device address of g_noalloc_scratch, per device ordinal.  Host threads of different ctxs may look the same device up at
+// the same time: both get the same address from the runtime, so the only requirement is an untorn pointer (atomic).
+std::atomic<float*> g_scratch_addr[kMaxDevices];
 
 }  // namespace
 
@@ -114,10 +117,10 @@ extern "C" int nc_dense_forward_noalloc(nc_ctx* ctx, const float* x, const float
     NC_CUDA(ctx, cudaSetDevice(ctx->device));
 
     // one-time set-up per device (no allocation): where does the scratch array live on THIS device?
-    float* scratch = g_scratch_addr[ctx->device];
+    float* scratch = g_scratch_addr[ctx->device].load(std::memory_order_acquire);
     if (!scratch) {
         NC_CUDA(ctx, cudaGetSymbolAddress((void**)&scratch, g_noalloc_scratch));
-        g_scratch_addr[ctx->device] = scratch;
+        g_scratch_addr[ctx->device].store(scratch, std::memory_order_release);
     }
 
     // same slicing rule as the library's workspace path, then shrink until the partials fit

@@ -75,6 +75,7 @@ extern "C" int nc_destroy(nc_ctx* ctx) {
     cudaSetDevice(ctx->device);
     for (auto& kv : ctx->pil_tables) cudaFree(kv.second.dptr);
     if (ctx->ws) cudaFree(ctx->ws);
+    if (ctx->gather_bad) cudaFree(ctx->gather_bad);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     delete ctx;
     return NC_OK;

@@ -31,6 +31,7 @@ struct nc_ctx {
     // small pinned host staging buffer for host_draws etc.
     void* pinned = nullptr;
     size_t pinned_bytes = 0;
+    int* gather_bad = nullptr;      // device flag: nc_gather_rows saw an out-of-range index (nc_gather_rows_status)
 };
 
 int nc_set_error(nc_ctx* ctx, int code, const char* fmt, ...);

@@ -143,6 +143,7 @@ struct nc_net {
     float *dbuf0 = nullptr, *dbuf1 = nullptr;
     float* ws = nullptr; size_t ws_bytes = 0;              // split-K partial sums (scratch)
     float* col = nullptr; size_t col_bytes = 0;            // im2col of the first (few-channel) conv layer, tensor path
+    int64_t arena_gen = 0;      // bumped whenever act / aux / dbuf / ws / col move: device pointers a CUDA graph captured are stale then
     // data parallel (nc_net_attach_nccl): communicator + 2*max(norm channels) floats for the cross-rank moments
     bool fuse_first = false;    // layers 0..2 are conv (few channels, stride 1) -> relu -> pool 2x2/2: one kernel each way
     void* comm = nullptr; int rank = 0, world = 1;
@@ -424,6 +425,7 @@ extern "C" int nc_net_set_math(nc_net* net, int math) {
     return NC_OK;
 }
 extern "C" int64_t nc_net_global_step(nc_net* net) { return net ? net->global_step : 0; }
+extern "C" int64_t nc_net_arena_generation(nc_net* net) { return net ? net->arena_gen : -1; }
 
 // ------------------------------------------------------------------------------------------------
 // buffers
@@ -431,6 +433,7 @@ extern "C" int64_t nc_net_global_step(nc_net* net) { return net ? net->global_st
 static int reserve_batch(nc_net* net, int n) {
     if (n <= net->cap) return NC_OK;
     cudaFree(net->act); cudaFree(net->aux); cudaFree(net->dbuf0); cudaFree(net->dbuf1);
+    net->arena_gen++;
     net->act = nullptr; net->aux = nullptr; net->dbuf0 = net->dbuf1 = nullptr; net->cap = 0;
     const size_t a = (size_t)net->act_floats * n * sizeof(float);
     const size_t d = (size_t)net->max_out * n * sizeof(float);
@@ -445,10 +448,17 @@ static int reserve_batch(nc_net* net, int n) {
 static int reserve_ws(nc_net* net, size_t bytes) {
     if (bytes <= net->ws_bytes) return NC_OK;
     cudaFree(net->ws); net->ws = nullptr; net->ws_bytes = 0;
+    net->arena_gen++;
     bytes = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
     if (cudaMalloc(&net->ws, bytes) != cudaSuccess) { cudaGetLastError(); return net_err(net, NC_ENOMEM, "split-K workspace of %zu bytes", bytes); }
     net->ws_bytes = bytes;
     return NC_OK;
+}
+extern "C" int nc_net_reserve(nc_net* net, int max_batch) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (max_batch <= 0) return net_err(net, NC_EINVAL, "max_batch must be positive, got %d", max_batch);
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    return reserve_batch(net, max_batch);
 }
 static inline float* act_ptr(nc_net* net, const Layer& L) { return net->act + L.out_off * net->cap; }
 
@@ -541,6 +551,7 @@ static int smallc_im2col(nc_net* net, const Layer& L, int n, const float* x, cud
     const size_t need = (size_t)M * Kp * sizeof(float);
     if (need > net->col_bytes) {
         cudaFree(net->col); net->col = nullptr; net->col_bytes = 0;
+        net->arena_gen++;
         if (cudaMalloc(&net->col, need) != cudaSuccess) { cudaGetLastError(); return net_err(net, NC_ENOMEM, "im2col buffer of %zu bytes", need); }
         net->col_bytes = need;
     }

@@ -69,8 +69,11 @@ __device__ __forceinline__ void finish_picture(const PredHdr& hdr, const unsigne
     if (tid == 0) *s_err = 0;
     __syncthreads();
 
-    if (out_small20)
+    // out_small20 = the picture as im.resize((20,20)) returns it (:315), before the compat scan below patches 220s into it
+    if (out_small20) {
         for (int o = tid; o < kOut * kOut; o += nthreads) out_small20[(long long)blockIdx.x * 400 + o] = s_small[o];
+        if (compat) __syncthreads();      // (block-uniform) the scan of thread 0 writes s_small
+    }
 
     // ---------------- phase 4: construct_inference.py:317-330
     if (!compat) {

@@ -312,8 +312,9 @@ extern "C" int nc_pp_resize_gray_norm_host(nc_ctx* ctx, const uint8_t* host_src,
         return launch_train_chain(ctx, (const uint8_t*)attr.devicePointer, n, h, w, c, img_stride, out_u8, out_f32, st);
     }
     // pageable: stage the whole batch through the workspace
-    const size_t bytes = (size_t)n * (size_t)img_stride;
-    rc = nc_ws_reserve(ctx, bytes);
+    // (the caller's buffer may end right behind the last picture: copy (n-1) strides + one picture, not n strides)
+    const size_t bytes = (size_t)(n - 1) * (size_t)img_stride + (size_t)h * w * c;
+    rc = nc_ws_reserve(ctx, (size_t)n * (size_t)img_stride);
     if (rc != NC_OK) return rc;
     NC_CUDA(ctx, cudaMemcpyAsync(ctx->ws, host_src, bytes, cudaMemcpyHostToDevice, st));
     if (staged) *staged = 1;

@@ -30,6 +30,7 @@ class DeviceDataSet:
         self._order = np.arange(self._num_examples)                    # current arrangement (the reference permutes in place)
         self._epochs_completed = 0
         self._index_in_epoch = 0
+        self._check_next = True
 
     num_examples = property(lambda self: self._num_examples)
     epochs_completed = property(lambda self: self._epochs_completed)
@@ -46,6 +47,10 @@ class DeviceDataSet:
                                                          C.c_void_p(d_idx.data_ptr()), n, C.c_void_p(out.data_ptr()),
                                                          self.ctx._stream()))
             outs.append(out)
+        if self._check_next:
+            # first batch and every epoch wrap (a new permutation): read the kernel's out-of-range flag back (synchronises)
+            self._check_next = False
+            _lib.check(self.ctx.handle, L.nc_gather_rows_status(self.ctx.handle, self.ctx._stream()))
         return outs[0], outs[1]
 
     def next_batch(self, batch_size, fake_data=False, shuffle=True):
@@ -56,6 +61,7 @@ class DeviceDataSet:
             self._order = self._order[perm0]
         if start + batch_size > self._num_examples:
             self._epochs_completed += 1
+            self._check_next = True
             rest = self._order[start:self._num_examples]
             if shuffle:
                 perm = np.arange(self._num_examples)

@@ -83,6 +83,14 @@ class Net:
     def global_step(self):
         return int(_lib.lib().nc_net_global_step(self.handle))
 
+    @property
+    def arena_generation(self):
+        """changes whenever the library moved its activation arena / workspaces (a larger batch came along)"""
+        return int(_lib.lib().nc_net_arena_generation(self.handle))
+
+    def reserve(self, max_batch):
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_reserve(self.handle, int(max_batch)))
+
     def get_state(self, opt):
         slots = _lib.lib().nc_net_state_slots(self.handle, opt)
         out = np.empty(slots * self.param_count, np.float32)
@@ -212,13 +220,22 @@ class GraphedTrainStep:
         torch.cuda.synchronize(dev)
         net.params.copy_(w0)
         net.set_state(oid, st0, gs0)
+        self._oid, self._args = oid, (loss_name, opt, lr)
+        self._capture()
+
+    def _capture(self):
+        """(Re)capture: the graph holds raw device addresses of the net's activation arena and workspaces, which move
+        when a later forward / predict / backward brings a larger batch (nc_net_arena_generation)."""
+        net, gs0 = self.net, self.net.global_step
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
-            self.loss, self.correct = net.train_step(self.x, self.y, loss_name, opt, lr)
-        net.set_state(oid, None, gs0)      # the captured call bumped the host-side counter without running anything
-        self._oid = oid
+            self.loss, self.correct = net.train_step(self.x, self.y, *self._args)
+        net.set_state(self._oid, None, gs0)      # the captured call bumped the host-side counter without running anything
+        self._gen = net.arena_generation
 
     def __call__(self, x, y):
+        if self.net.arena_generation != self._gen:
+            self._capture()                # the buffers only ever grow: they are large enough for this batch, just elsewhere
         self.x.copy_(x.reshape(self.batch, -1), non_blocking=True)
         self.y.copy_(y.reshape(self.batch, -1), non_blocking=True)
         self.graph.replay()
@@ -277,16 +294,16 @@ class DataParallel:
         if in_library is None:
             in_library = has_norm and not allow_local_norm
         self.in_library = bool(in_library) and self.world > 1
+        src0 = dist.get_global_rank(group, 0) if (group is not None and self.world > 1) else 0
         if self.world > 1:
-            dist.broadcast(net.params, src=0, group=group)     # identical initial weights
+            dist.broadcast(net.params, src=src0, group=group)  # identical initial weights
         if self.in_library:
             if not hasattr(net, "attach_nccl"):
                 raise NotImplementedError("data parallel training of a net with 'norm' layers needs the library's "
                                           "communicator (Net.attach_nccl); pass allow_local_norm=True for per-rank moments")
             rank = dist.get_rank(group)
             box = [new_nccl_unique_id(net.ctx) if rank == 0 else None]
-            src = dist.get_global_rank(group, 0) if group is not None else 0
-            dist.broadcast_object_list(box, src=src, group=group)
+            dist.broadcast_object_list(box, src=src0, group=group)
             net.attach_nccl(box[0], rank, self.world)
 
     def train_step(self, x_local, y_local, loss_name="entropy", opt="compat", lr=1e-4):

@@ -87,7 +87,8 @@ int nc_pp_resize_gray_norm_host(nc_ctx* ctx, const uint8_t* host_src, int n, int
  * channel_order: 0 = RGB (PIL), 1 = BGR (cv2 buffers).  compat != 0 reproduces the reference's
  * `arr[bizar+i][bizar+j] = 220` statement (:325-326) including its IndexError: status[i] is set
  * to 1 where the reference raises (out_f32 row i is then all zero), else 0.  status may be NULL
- * when compat == 0.  out_small20 (nullable) receives the 20x20 'L' picture after the resize. */
+ * when compat == 0.  out_small20 (nullable) receives the 20x20 'L' picture as the resize returns it
+ * (before the compat statement patches 220s into its working copy). */
 int nc_pp_predict_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
                         int64_t img_stride, int channel_order, int compat, float* out_f32,
                         uint8_t* out_small20, int* status, void* stream);
@@ -149,6 +150,11 @@ int nc_pp_cubic_table(int src, int32_t* ofs, int16_t* coef);
 int nc_pp_pil_table(int in_size, int out_size, int32_t* xmin, int32_t* cnt, int32_t* kk, int kk_capacity);
 int nc_pp_gaussian_q8(int k, int32_t* q);
 
+/* CRC-32C (Castagnoli) of n host bytes, continuing from `crc` (0 to start): the checksum TensorFlow's
+ * checkpoint bundles keep per tensor and per index block -- tf.train.Saver() / saver.restore
+ * (construct_distribute.py:375, :385-392; construct_inference.py:336-339).  Host-only. */
+uint32_t nc_crc32c(const void* host_data, size_t n, uint32_t crc);
+
 /* [n][28][28] uint8 -> [n][784] float32, x * float32(1/255)
  * (DataSet.__init__, construct_distribute.py:503-504). */
 int nc_pp_normalise(nc_ctx* ctx, const uint8_t* in, int64_t count, float* out, void* stream);
@@ -158,6 +164,10 @@ int nc_pp_normalise(nc_ctx* ctx, const uint8_t* in, int64_t count, float* out, v
  * dataset resident in HBM.  idx is a DEVICE array of int64 row numbers in [0, n_src). */
 int nc_gather_rows(nc_ctx* ctx, const float* src, int64_t n_src, int width, const int64_t* idx, int n,
                    float* out, void* stream);
+/* numpy raises IndexError for an index outside [0, n_src) (construct_distribute.py:541, :556); the kernel
+ * zero-fills such a row and sets a sticky flag.  This call synchronises `stream`, returns NC_EINVAL if any
+ * nc_gather_rows on ctx since the previous status call saw such an index, and clears the flag. */
+int nc_gather_rows_status(nc_ctx* ctx, void* stream);
 
 /* ---- CNN graph: construct / forward / backward / update --------------------------------
  * nc_net_create replaces cnn() + get_net() (construct_distribute.py:208-281, identical copy in
@@ -214,6 +224,16 @@ int64_t nc_net_global_step(nc_net* net);
  * keeps in tf.train.get_or_create_global_step() (:371).  Adam must not be captured: its step size
  * depends on global_step and is computed on the host. */
 int nc_net_advance_step(nc_net* net, int64_t k);
+/* The library-owned activation arena, split-K workspace and im2col buffer grow on demand (a forward,
+ * predict or backward with a larger batch than any before frees and re-allocates them).  A CUDA graph
+ * captured earlier holds the OLD device addresses: replaying it would read and write freed memory.
+ * nc_net_arena_generation returns a counter that changes whenever any of those buffers moved; a host
+ * that replays captured steps records it at capture time and re-captures when it differs.
+ * nc_net_reserve sizes every batch-proportional buffer for max_batch rows up front (the split-K and
+ * im2col workspaces are sized by the first call that needs them), so later calls up to that
+ * batch move nothing. */
+int64_t nc_net_arena_generation(nc_net* net);
+int nc_net_reserve(nc_net* net, int max_batch);
 
 /* ---- data parallel inside the library (NCCL bound with dlopen, one process per GPU) ----------
  * Replaces the 1 ps + 1 worker gRPC exchange of construct_distribute.py:344-357 (cmd.py:63-69) by

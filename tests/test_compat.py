@@ -193,6 +193,25 @@ def test_device_dataset_matches_reference_dataset(ctx):
 
 
 @pytest.mark.gpu
+def test_gather_rows_out_of_range_index_is_reported(ctx):
+    """`self._images[perm]` (construct_distribute.py:541) raises IndexError for an index outside the set; the gather
+    kernel zero-fills that row and nc_gather_rows_status reports (and clears) the sticky flag."""
+    import ctypes as C
+    import torch
+    from cloud_server_b200 import _lib
+    L = _lib.lib()
+    src = torch.arange(5 * 8, dtype=torch.float32, device="cuda").reshape(5, 8)
+    idx = torch.tensor([4, 0, 5, -1, 2], dtype=torch.int64, device="cuda")
+    out = torch.full((5, 8), -7.0, device="cuda")
+    _lib.check(ctx.handle, L.nc_gather_rows(ctx.handle, C.c_void_p(src.data_ptr()), 5, 8, C.c_void_p(idx.data_ptr()), 5,
+                                            C.c_void_p(out.data_ptr()), ctx._stream()))
+    with pytest.raises(IndexError):
+        _lib.check(ctx.handle, L.nc_gather_rows_status(ctx.handle, ctx._stream()))
+    assert torch.equal(out[[0, 1, 4]], src[[4, 0, 2]]) and float(out[[2, 3]].abs().max()) == 0.0
+    _lib.check(ctx.handle, L.nc_gather_rows_status(ctx.handle, ctx._stream()))       # cleared by the read
+
+
+@pytest.mark.gpu
 def test_batched_view_adapter_equals_per_file_loop(ctx, tmp_path):
     """compat.preprocess_view.execute (one batch per step) leaves the same files and tag.json as the reference's
     per-file loop (resize(path); op(path, overlap, v1, v2) for every tag entry, views.py:118-132)."""
@@ -232,3 +251,76 @@ def test_batched_view_adapter_equals_per_file_loop(ctx, tmp_path):
     assert files == sorted(os.listdir(tmp_path / "b")) and len(files) > 6
     for f in files:
         assert open(tmp_path / "a" / f, "rb").read() == open(tmp_path / "b" / f, "rb").read(), f
+
+
+def test_read_train_results_matches_reference_golden():
+    """compat.construct_view.read_train_results == TensorResultView.read_train_results (apps/runtime/views.py:44-72) on the
+    vectors tests/golden/make_train_results.py produced by executing the reference's method."""
+    from cloud_server_b200.compat import construct_view as cv
+    cases = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "train_results.json")))
+    assert len(cases) >= 16
+    import tempfile
+    for c in cases:
+        with tempfile.NamedTemporaryFile("w", delete=False) as f:
+            f.write(c["text"])
+        try:
+            assert cv.read_train_results(f.name, c["iter"]) == c["json"], c
+        finally:
+            os.unlink(f.name)
+
+
+@pytest.mark.gpu
+def test_in_process_views_train_infer_monitor(ctx, tmp_path):
+    """compat.construct_view: ConstructView.create_file -> training thread in this process; TensorResultView's parser on
+    the result.txt it leaves; InferenceView.create_file -> result.json from ONE resident net (no reload on the second
+    request); the checkpoint on disk is a TensorFlow V2 bundle that restores into a fresh net bit for bit."""
+    import cv2
+    import torch
+    from cloud_server_b200 import tf_bundle
+    from cloud_server_b200.compat import construct_view as cv, construct_distribute as cd
+    from cloud_server_b200.compat.graph import get_net, placeholder, compile_net
+    pics = golden("pics.npz")
+    mdir = tmp_path / "NJUCloud" / "7" / "model" / "digits"
+    os.makedirs(mdir / "data")
+    os.makedirs(mdir / "infer")
+    tags = {}
+    for i, (name, lab) in enumerate(zip(pics["names"], pics["labels"])):
+        cv2.imwrite(str(mdir / "data" / str(name)), pics["gray_cv"][i])
+        tags[str(name)] = str(int(lab))
+    json.dump(tags, open(mdir / "tag.json", "w"))
+    body = {"ratio": 0.8, "iter": "120", "learning_rate": "0.01", "loss_name": "entropy", "optimizer_name": "GradientDescentOptimizer",
+            "net_type": "CNN", "net_config": {"middle_layer": [{"layer": "conv", "filter": [3, 3, 8], "isBias": "True"},
+                                                               {"layer": "active", "active_func": "relu"}, {"layer": "pool"},
+                                                               {"layer": "connect", "hidden": 64}, {"layer": "active", "active_func": "relu"}],
+                                              "output_layer": {}}}
+    json.dump(body, open(mdir / "model.json", "w"))                 # ConstructView.save_model_file (views.py:148-162)
+    try:
+        job = cv.create_file(body, str(mdir), "file", "digits", wait=True, extra_argv=["--seed=3"])
+        assert not job["error"] and "--job_name=worker" in job["argv"] and "--ratio=0.800000" in job["argv"]
+        mon = json.loads(cv.read_train_results(str(mdir / "result.txt"), "120"))
+        assert [r["step"] for r in mon["every_result"]] == ["0", "100"] and 0.0 <= float(mon["final_accuracy"]) <= 1.0
+        files = sorted(os.listdir(mdir / "train_model"))
+        assert files == ["model.ckpt-120.data-00000-of-00001", "model.ckpt-120.index", "model.ckpt-120.meta"]
+        # inference: a 28x28 bundled picture whose scan stays in range, twice; the second request reuses the resident net
+        ok = [0]
+        name = str(pics["names"][ok[0]])
+        cv2.imwrite(str(mdir / "infer" / name), pics["gray_cv"][ok[0]])
+        r1 = json.loads(cv.infer(str(mdir), name, intended=True))
+        net1 = cv._LIVE[str(mdir)]["net"]
+        before = ctx.launches
+        r2 = json.loads(cv.infer(str(mdir), name, intended=True))
+        assert r1 == r2 == json.load(open(mdir / "result.json")) and r1["result"] == "success" and r1["message"] in list("0123456789")
+        assert cv._LIVE[str(mdir)]["net"] is net1                    # no rebuild, no checkpoint read
+        assert ctx.launches - before <= 12                           # one preprocess kernel + one forward pass
+        with pytest.raises(ValueError):
+            cv.create_file(body, str(mdir), "url", "digits")
+        # the bundle restores into a fresh net exactly (variables, Adagrad slots, step), by the reference's names
+        t = tf_bundle.read_bundle(str(mdir / "train_model" / "model.ckpt-120"))
+        assert {"Variable", "Variable_1", "Variable_2", "Variable_3", "Variable_4", "Variable_5", "Variable_6"} <= set(t)
+        assert t["Variable"].shape == (3, 3, 1, 8) and t["Variable_6"].dtype == np.int32 and int(t["Variable_6"]) == 120
+        fresh = compile_net(get_net("CNN", body["net_config"], placeholder(28, 28, 1), None), ctx, seed=99)
+        assert cd.load_checkpoint(fresh, str(mdir / "train_model" / "model.ckpt-120")) == 120
+        assert np.array_equal(fresh.get_params(), net1.get_params()) and fresh.global_step == 120
+        fresh.close()
+    finally:
+        cv.close_all()

@@ -8,39 +8,7 @@ import torch
 import torch.nn.functional as F
 
 from oracle import tfref
-
-
-def torch_forward(net, x, params):
-    """Independent derivation: same graph in torch float64, NCHW internally."""
-    n = x.shape[0]
-    a = x.reshape((n,) + net.in_shape).permute(0, 3, 1, 2)
-    for L in net.layers:
-        k = L["kind"]
-        if k == "conv":
-            w = params[L["w"]].permute(3, 2, 0, 1)     # HWIO -> OIHW
-            pb = max((L["oh"] - 1) * L["sh"] + L["fh"] - L["ih"] - L["pt"], 0)
-            pr = max((L["ow"] - 1) * L["sw"] + L["fw"] - L["iw"] - L["pl"], 0)
-            a = F.pad(a, (L["pl"], pr, L["pt"], pb))
-            a = F.conv2d(a, w, params[L["b"]] if L["b"] is not None else None, stride=(L["sh"], L["sw"]))
-            a = a[:, :, :L["oh"], :L["ow"]]
-        elif k == "pool":
-            pb = max((L["oh"] - 1) * L["sh"] + L["kh"] - L["ih"] - L["pt"], 0)
-            pr = max((L["ow"] - 1) * L["sw"] + L["kw"] - L["iw"] - L["pl"], 0)
-            a = F.pad(a, (L["pl"], pr, L["pt"], pb), value=float("-inf"))
-            a = F.max_pool2d(a, (L["kh"], L["kw"]), (L["sh"], L["sw"]))[:, :, :L["oh"], :L["ow"]]
-        elif k == "active":
-            a = torch.relu(a) if L["fn"] == "relu" else torch.sigmoid(a) if L["fn"] == "sigmoid" else torch.maximum(a, L["slope"] * a)
-        elif k == "norm":
-            axes = [0, 2, 3] if a.dim() == 4 else [0]
-            mean = a.mean(dim=axes, keepdim=True)
-            var = ((a - mean) ** 2).mean(dim=axes, keepdim=True)
-            shp = (1, -1, 1, 1) if a.dim() == 4 else (1, -1)
-            a = (a - mean) / torch.sqrt(var + L["eps"]) * params[L["scale"]].reshape(shp) + params[L["offset"]].reshape(shp)
-        elif k == "connect":
-            if a.dim() == 4:
-                a = a.permute(0, 2, 3, 1).reshape(n, -1)
-            a = a @ params[L["w"]] + params[L["b"]]
-    return a
+from oracle.torchref import torch_forward, TorchStep
 
 
 CONFIGS = {
@@ -161,3 +129,22 @@ def test_dataset_next_batch_semantics():
     first_epoch = np.concatenate(seen[:2] + [seen[2][:1]])
     assert sorted(first_epoch.tolist()) == list(range(7))      # wrap batch = tail + head of reshuffle
     assert np.allclose(ds._images.max(), np.float32(27) * np.float32(1 / 255.0))
+
+
+@pytest.mark.parametrize("opt,lr", [("adagrad", 0.05), ("sgd", 0.05)])
+def test_torch_cpu_step_equals_tfref_step(opt, lr):
+    """oracle.torchref.TorchStep (bench.py's CPU arm for the train step) walks the same trajectory as tfref.train_step."""
+    rng = np.random.default_rng(3)
+    ref = tfref.Net(tfref.LENET)
+    w = ref.flatten(tfref.init_params(ref.param_specs, rng))
+    x = rng.random((16, 784), dtype=np.float32)
+    y = np.eye(10, dtype=np.float32)[rng.integers(0, 10, 16)]
+    ts = TorchStep(tfref.LENET, flat_params=w.copy(), opt=opt, lr=lr, threads=2)
+    o = tfref.Adagrad(w.size, lr) if opt == "adagrad" else tfref.SGD(w.size, lr)
+    w0 = w.copy()
+    for _ in range(3):
+        l0, _, _ = tfref.train_step(ref, w, x, y, o)
+        l1 = ts.step(torch.from_numpy(x), torch.from_numpy(y))
+        assert abs(l0 - l1) < 1e-4 * max(1.0, abs(l0))
+    d0, d1 = w - w0, ts.flat() - w0
+    assert np.abs(d0 - d1).max() < 1e-3 * np.abs(d0).max()
