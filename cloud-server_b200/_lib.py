@@ -62,6 +62,9 @@ _SIGS = {
                                     C.c_void_p]),
     "nc_net_global_step": (C.c_int64, [C.c_void_p]),
     "nc_net_advance_step": (C.c_int, [C.c_void_p, C.c_int64]),
+    "nc_net_profile": (C.c_int, [C.c_void_p, C.c_int]),
+    "nc_net_profile_read": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_int)]),
+    "nc_net_attach_comm": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int]),
     "nc_net_arena_generation": (C.c_int64, [C.c_void_p]),
     "nc_net_reserve": (C.c_int, [C.c_void_p, C.c_int]),
     "nc_nccl_unique_id": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p]),

@@ -43,6 +43,7 @@ int nc_nccl_load(nc_ctx* ctx, const char* path);    // idempotent; NULL / "" = "
 int nc_nccl_version();
 int nc_nccl_unique_id_impl(nc_ctx* ctx, unsigned char out[128]);
 int nc_nccl_comm_init(nc_ctx* ctx, void** comm, const unsigned char id[128], int rank, int world);
+int nc_nccl_comm_dup(nc_ctx* ctx, void* comm, int rank, void** out);
 void nc_nccl_comm_destroy(void* comm);
 int nc_nccl_allreduce_sum_f32(nc_ctx* ctx, void* comm, float* buf, size_t count, cudaStream_t st);
 

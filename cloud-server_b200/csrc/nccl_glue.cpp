@@ -18,6 +18,7 @@ using fn_comm_destroy = int (*)(void*);
 using fn_all_reduce = int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t);
 using fn_error_string = const char* (*)(int);
 using fn_get_version = int (*)(int*);
+using fn_comm_split = int (*)(void*, int, int, void**, void*);
 
 struct Api {
     void* handle = nullptr;
@@ -27,6 +28,7 @@ struct Api {
     fn_all_reduce all_reduce = nullptr;
     fn_error_string error_string = nullptr;
     fn_get_version get_version = nullptr;
+    fn_comm_split comm_split = nullptr;
     std::string path;
 };
 Api g_api;
@@ -52,6 +54,7 @@ int nc_nccl_load(nc_ctx* ctx, const char* path) {
     a.all_reduce = (fn_all_reduce)dlsym(h, "ncclAllReduce");
     a.error_string = (fn_error_string)dlsym(h, "ncclGetErrorString");
     a.get_version = (fn_get_version)dlsym(h, "ncclGetVersion");
+    a.comm_split = (fn_comm_split)dlsym(h, "ncclCommSplit");      // NCCL >= 2.18; optional
     if (!a.get_unique_id || !a.comm_init_rank || !a.comm_destroy || !a.all_reduce)
         return nc_set_error(ctx, NC_EUNSUPPORTED, "'%s' does not export the NCCL entry points", p);
     g_api = a;
@@ -77,6 +80,16 @@ int nc_nccl_comm_init(nc_ctx* ctx, void** comm, const unsigned char id_bytes[128
     memcpy(id.internal, id_bytes, 128);
     const int rc = g_api.comm_init_rank(comm, world, id, rank);
     if (rc != 0) { *comm = nullptr; return nc_set_error(ctx, NC_ECUDA, "ncclCommInitRank(rank %d of %d) failed: %s", rank, world, err_text(rc)); }
+    return NC_OK;
+}
+
+// A second communicator over the same ranks (ncclCommSplit with one colour), so that collectives issued from two streams
+// never share a communicator.  Collective over all ranks of `comm`.  *out stays NULL when this NCCL has no ncclCommSplit.
+int nc_nccl_comm_dup(nc_ctx* ctx, void* comm, int rank, void** out) {
+    *out = nullptr;
+    if (!g_api.comm_split) return NC_OK;
+    const int rc = g_api.comm_split(comm, 0, rank, out, nullptr);
+    if (rc != 0) { *out = nullptr; return nc_set_error(ctx, NC_ECUDA, "ncclCommSplit failed: %s", err_text(rc)); }
     return NC_OK;
 }
 

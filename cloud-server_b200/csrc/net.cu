@@ -9,6 +9,7 @@
 // flat fp32 buffer, gradients and optimizer state in matching flat buffers.
 #include "nc_internal.h"
 #include "net_kernels.cuh"
+#include "fused_kernels.cuh"
 #include "tc_gemm.h"
 #include <cmath>
 #include <cstring>
@@ -135,7 +136,7 @@ struct nc_net {
     float *params = nullptr, *grads = nullptr;
     float *st_adagrad = nullptr, *st_adam = nullptr;
     int64_t global_step = 0;
-    int math = 0;
+    int math = 3;
     // activation arena, sized for `cap` samples
     int cap = 0;
     int64_t act_floats = 0, aux_bytes = 0, stat_floats = 0, max_out = 0;
@@ -143,15 +144,27 @@ struct nc_net {
     float *dbuf0 = nullptr, *dbuf1 = nullptr;
     float* ws = nullptr; size_t ws_bytes = 0;              // split-K partial sums (scratch)
     float* col = nullptr; size_t col_bytes = 0;            // im2col of the first (few-channel) conv layer, tensor path
+    // tensor-core operand copies of the parameters (math 3): hi = rn_tf32(w) (what the single-product gradient GEMMs read),
+    // refreshed from `params` at the start of every training step
+    float* params_hi = nullptr;
+    // fused glue: ticket counters of the "last CTA sums" kernels (zero between launches), per-CTA loss / hit partials
+    unsigned* counters = nullptr; float* red_f = nullptr; int* red_i = nullptr;
+    bool head_fused = false;    // output layer + loss + its gradients run as head_fwd_bwd_kernel / head_wgrad_kernel
+    // per-stage CUDA-event timing of one step (nc_net_profile): names[i] covers events[i] .. events[i + 1]
+    bool prof_on = false; std::vector<std::string> prof_names; std::vector<cudaEvent_t> prof_events; size_t prof_used = 0;
     int64_t arena_gen = 0;      // bumped whenever act / aux / dbuf / ws / col move: device pointers a CUDA graph captured are stale then
     // data parallel (nc_net_attach_nccl): communicator + 2*max(norm channels) floats for the cross-rank moments
     bool fuse_first = false;    // layers 0..2 are conv (few channels, stride 1) -> relu -> pool 2x2/2: one kernel each way
     void* comm = nullptr; int rank = 0, world = 1;
+    bool comm_owned = true;     // false: the host passed its own ncclComm_t (nc_net_attach_comm)
+    // second communicator over the same ranks for the small batch-norm moment exchanges on the compute stream: the
+    // gradient exchange owns `comm` on comm_stream, and two streams must not share one communicator
+    void* comm_norm = nullptr;
     float* dp_buf = nullptr;
     // overlap of the gradient exchange with the rest of backward: the tail of the flat gradient buffer (the dense layers
     // at the end of the net: 98 % of LeNet's parameters) is final as soon as backward has passed layer `split_layer`;
     // it is all-reduced on comm_stream while the convolution gradients are still being computed
-    cudaStream_t comm_stream = nullptr; cudaEvent_t ev_tail_ready = nullptr, ev_tail_done = nullptr;
+    cudaStream_t comm_stream = nullptr; cudaEvent_t ev_tail_ready = nullptr, ev_tail_done = nullptr, ev_head_ready = nullptr;
     int split_layer = -1; int64_t split_off = 0; bool tail_in_flight = false;
     bool dp_step = false;       // set by nc_net_train_step around its backward pass: the exchange may start early
     std::string err;
@@ -168,6 +181,19 @@ static int net_err(nc_net* net, int code, const char* fmt, ...) {
     return net_err((net), NC_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
 #define NET_LAUNCH(net) do { (net)->ctx->launches++; cudaError_t e__ = cudaGetLastError(); if (e__ != cudaSuccess) \
     return net_err((net), NC_ECUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(e__), __FILE__, __LINE__); } while (0)
+
+// nc_net_profile: a mark closes the previous stage and opens the next one (CUDA events on the step's stream)
+static void prof_mark(nc_net* net, cudaStream_t st, const char* name) {
+    if (!net->prof_on) return;
+    if (net->prof_used == net->prof_events.size()) {
+        cudaEvent_t e = nullptr;
+        if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); return; }
+        net->prof_events.push_back(e);
+    }
+    cudaEventRecord(net->prof_events[net->prof_used++], st);
+    net->prof_names.push_back(name);
+}
+#define PROF(net, st, name) prof_mark((net), (st), (name))
 
 static void same_pad(int n, int k, int s, bool same, int* out, int* before) {
     // tf.nn.conv2d / max_pool: SAME out = ceil(n/s), pad = max((out-1)*s+k-n, 0), before = pad/2
@@ -341,11 +367,16 @@ static double trunc_normal(uint64_t& s) {
 
 static void free_net(nc_net* net) {
     if (!net) return;
-    if (net->comm) { nc_nccl_comm_destroy(net->comm); net->comm = nullptr; }
+    if (net->comm_norm) { nc_nccl_comm_destroy(net->comm_norm); net->comm_norm = nullptr; }
+    if (net->comm && net->comm_owned) nc_nccl_comm_destroy(net->comm);
+    net->comm = nullptr;
     if (net->comm_stream) cudaStreamDestroy(net->comm_stream);
     if (net->ev_tail_ready) cudaEventDestroy(net->ev_tail_ready);
     if (net->ev_tail_done) cudaEventDestroy(net->ev_tail_done);
+    if (net->ev_head_ready) cudaEventDestroy(net->ev_head_ready);
     cudaFree(net->dp_buf);
+    cudaFree(net->params_hi); cudaFree(net->counters); cudaFree(net->red_f); cudaFree(net->red_i);
+    for (cudaEvent_t e : net->prof_events) cudaEventDestroy(e);
     cudaFree(net->params); cudaFree(net->grads); cudaFree(net->st_adagrad); cudaFree(net->st_adam);
     cudaFree(net->act); cudaFree(net->aux); cudaFree(net->stat); cudaFree(net->dbuf0); cudaFree(net->dbuf1); cudaFree(net->ws); cudaFree(net->col);
     delete net;
@@ -372,6 +403,21 @@ extern "C" int nc_net_create(nc_ctx* ctx, const char* net_config_json, int in_h,
         cudaGetLastError(); free_net(net); return nc_set_error(ctx, NC_ENOMEM, "cudaMalloc of %zu parameter bytes failed", pb);
     }
     cudaMemset(net->grads, 0, pb);
+    if (cudaMalloc(&net->counters, 1024 * sizeof(unsigned)) != cudaSuccess || cudaMalloc(&net->red_f, 4096 * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&net->red_i, 4096 * sizeof(int)) != cudaSuccess) {
+        cudaGetLastError(); free_net(net); return nc_set_error(ctx, NC_ENOMEM, "cudaMalloc of the reduction scratch failed");
+    }
+    cudaMemset(net->counters, 0, 1024 * sizeof(unsigned));
+    {
+        // the output layer runs as the fused head when its weights fit shared memory (always, for 10 classes)
+        const Layer& O = net->layers.back();
+        const size_t head_smem = (size_t)O.in_size * (O.oc > 8 ? O.oc : 8) * sizeof(float);
+        net->head_fused = O.oc <= 32 && head_smem <= 200 * 1024 && !getenv("NC_NO_HEAD_FUSION");
+        // default arithmetic: tensor cores, 3xTF32 forward + single rounded-TF32 products for the gradients (what bench.py
+        // times and the BASELINE-size parity tests hold); NC_NET_MATH overrides, nc_net_set_math changes it per net
+        net->math = 3;
+        if (const char* e = getenv("NC_NET_MATH")) { const int m = atoi(e); if (m >= 0 && m <= 3) net->math = m; }
+    }
     if (net->stat_floats) cudaMalloc(&net->stat, net->stat_floats * sizeof(float));
     // initial values (weight_variable / bias_variable :57-87)
     std::vector<float> host((size_t)net->nparams);
@@ -607,6 +653,15 @@ static bool patch_geom(const Layer& c, PatchGeom* g, size_t* smem) {
         else KERNEL<5, 5, 1> __VA_ARGS__;                                                          \
     } while (0)
 
+static std::string stage_name(const char* phase, int li, const Layer& L) {
+    static const char* kinds[] = {"conv", "pool", "active", "connect", "norm"};
+    char buf[96];
+    if (L.kind == L_CONV) snprintf(buf, sizeof(buf), "%s L%d conv %dx%dx%d->%d", phase, li, L.fh, L.fw, L.ic, L.oc);
+    else if (L.kind == L_CONNECT) snprintf(buf, sizeof(buf), "%s L%d connect %lld->%d", phase, li, (long long)L.in_size, L.oc);
+    else snprintf(buf, sizeof(buf), "%s L%d %s", phase, li, kinds[L.kind]);
+    return buf;
+}
+
 // ------------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------------
@@ -619,10 +674,12 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
     int li = -1;
     for (auto& L : net->layers) {
         ++li;
+        if (training && net->head_fused && li == (int)net->layers.size() - 1) break;  // the fused head of backward computes the logits
         if (L.kind == L_ACT && L.relu_into_pool) { pending_relu = true; continue; }   // `in` stays the pre-activation
         if (net->fuse_first && li == 0) continue;                                     // computed inside the pool launch below
         if (L.kind == L_ACT && li > 0 && net->layers[li - 1].act_fused) continue;   // done in the producer's epilogue
         float* out = act_ptr(net, L);
+        if (net->prof_on) PROF(net, st, stage_name("fwd", li, L).c_str());
         if (net->fuse_first && li == 2) {
             const Layer& c = net->layers[0];
             const FirstGeom fg = first_geom(c, L);
@@ -755,11 +812,11 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
                 const float inv_total = 1.0f / (float)(rows * net->world);
                 norm_sum_kernel<<<L.oc, 256, 0, st>>>(in, rows, L.oc, sum);
                 NET_LAUNCH(net);
-                int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, sum, (size_t)L.oc, st);
+                int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm_norm ? net->comm_norm : net->comm, sum, (size_t)L.oc, st);
                 if (rc != NC_OK) return rc;
                 norm_sqdev_kernel<<<L.oc, 256, 0, st>>>(in, rows, L.oc, sum, inv_total, sq);
                 NET_LAUNCH(net);
-                rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, sq, (size_t)L.oc, st);
+                rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm_norm ? net->comm_norm : net->comm, sq, (size_t)L.oc, st);
                 if (rc != NC_OK) return rc;
                 norm_apply_kernel<<<L.oc, 256, 0, st>>>(in, out, net->act + L.aux_off * net->cap, net->stat + L.stat_off, W, Bp, rows, L.oc,
                                                          L.eps, sum, sq, inv_total);
@@ -820,17 +877,87 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         return net_err(net, NC_ECONFIG, "loss_function returns None for this loss_name (reference: ValueError in minimize); use entropy or mse");
     NET_CUDA(net, cudaSetDevice(net->ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
+    const int sms = net->ctx->sm_count;
+    // math 3: the two gradient contractions are single TF32 products.  The tensor core TRUNCATES fp32 operands (a one-sided
+    // ~3e-4 shrink per operand that compounds layer by layer); instead every operand is put on the TF32 grid by
+    // round-to-nearest where it is produced -- the weights here (hi = rn(w)), the activation gradients in the kernels that
+    // write them -- so the products themselves are exact and what is left is unbiased rounding noise.
+    const bool round_bwd = net->math == 3;
+    if (round_bwd) {
+        if (!net->params_hi) NET_CUDA(net, cudaMalloc(&net->params_hi, (size_t)net->nparams * sizeof(float)));
+        PROF(net, st, "split weights (hi = rn_tf32)");
+        split_params_kernel<<<grid_for(net->nparams / 4 + 1, sms), 256, 0, st>>>(net->params, net->params_hi, nullptr, net->nparams);
+        NET_LAUNCH(net);
+    }
     rc = forward_impl(net, x, n, st, true);
     if (rc != NC_OK) return rc;
-    const int sms = net->ctx->sm_count;
     float* d = net->dbuf0;
     float* dn = net->dbuf1;
-    loss_kernel<<<1, 1024, 0, st>>>(act_ptr(net, net->layers.back()), y_onehot, d, n, net->classes, loss_name, grad_scale, loss_out, (int*)correct_out);
-    NET_LAUNCH(net);
+    const int nl = (int)net->layers.size();
+    int start = nl - 1;          // first layer the generic loop below handles
+    int bias_done = -1;          // layer whose bias gradient a fused kernel has already written
+    if (net->head_fused) {
+        // output layer + loss + both of its gradients (+ the relu in front, + the bias gradient of the dense layer below)
+        Layer& O = net->layers[nl - 1];
+        const float* in = nl == 1 ? x : act_ptr(net, net->layers[nl - 2]);
+        const int M = n, N = O.oc, K = (int)O.in_size;
+        int below = nl - 2, relu_mask = 0;
+        if (below >= 0 && net->layers[below].kind == L_ACT && net->layers[below].act == ACT_RELU && !net->layers[below].relu_into_pool) {
+            relu_mask = 1;       // y = relu(.) is the head's input: y > 0 <=> pre-activation > 0
+            --below;
+        }
+        float* dx = below >= 0 ? d : nullptr;
+        float* dz = dn;          // [M][N], consumed by head_wgrad_kernel right behind
+        bool cs = false;
+        if (below >= 0 && net->layers[below].kind == L_CONNECT && net->layers[below].b_off >= 0 && K <= 1024 && net->layers[below].oc == K) cs = true;
+        const int G = (M + 7) / 8 < 2 * sms ? (M + 7) / 8 : 2 * sms;
+        int slices = (sms * 2 + (K + 255) / 256 - 1) / ((K + 255) / 256);          // K blocks x batch slices of the weight gradient
+        if (slices > (M + 15) / 16) slices = (M + 15) / 16;
+        if (slices < 1) slices = 1;
+        int rps = (M + slices - 1) / slices;
+        while ((size_t)rps * N * sizeof(float) > 48 * 1024) { slices *= 2; rps = (M + slices - 1) / slices; }
+        slices = (M + rps - 1) / rps;
+        if ((K + 255) / 256 > 512) return net_err(net, NC_EUNSUPPORTED, "output layer with %d inputs", K);
+        {
+            // one workspace, used by the two launches one after the other: the head's column sums, then the slice partials
+            const size_t a = cs ? (size_t)G * K * sizeof(float) : 0, b = (size_t)slices * K * N * sizeof(float);
+            rc = reserve_ws(net, a > b ? a : b);
+            if (rc != NC_OK) return rc;
+        }
+        const size_t smem = (size_t)K * (size_t)(cs && N < 8 ? 8 : N) * sizeof(float);
+        float* dbp = cs ? net->grads + net->layers[below].b_off : nullptr;
+        PROF(net, st, "head: output layer + loss + dlogits + dgrad");
+#define NC_HEAD(NM, CSF)                                                                                                   \
+        do {                                                                                                                \
+            auto kfn = head_fwd_bwd_kernel<NM, CSF>;                                                                        \
+            if (smem > 48 * 1024) NET_CUDA(net, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+            kfn<<<G, 256, smem, st>>>(in, net->params + O.w_off, net->params + O.b_off, y_onehot, act_ptr(net, O), dz, dx, M, N, K, \
+                                      loss_name, grad_scale, relu_mask, round_bwd ? 1 : 0, net->ws, dbp, net->red_f, net->red_i,   \
+                                      net->counters, loss_out, (int*)correct_out);                                          \
+        } while (0)
+        if (N <= 16) { if (cs) NC_HEAD(16, true); else NC_HEAD(16, false); }
+        else { if (cs) NC_HEAD(32, true); else NC_HEAD(32, false); }
+#undef NC_HEAD
+        NET_LAUNCH(net);
+        if (cs) bias_done = below;
+        {
+            dim3 grid((K + 255) / 256, slices);
+            PROF(net, st, "head: output layer wgrad + bias grad");
+            if (N <= 16) head_wgrad_kernel<16><<<grid, 256, (size_t)rps * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off, M, N, K, rps, net->counters + 16);
+            else head_wgrad_kernel<32><<<grid, 256, (size_t)rps * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off, M, N, K, rps, net->counters + 16);
+            NET_LAUNCH(net);
+        }
+        start = below;
+    } else {
+        PROF(net, st, "loss");
+        loss_kernel<<<1, 1024, 0, st>>>(act_ptr(net, net->layers.back()), y_onehot, d, n, net->classes, loss_name, grad_scale, loss_out, (int*)correct_out);
+        NET_LAUNCH(net);
+    }
     bool skip_fused_relu = false;
     const float* first_relu_y = nullptr;
-    for (int li = (int)net->layers.size() - 1; li >= 0; --li) {
+    for (int li = start; li >= 0; --li) {
         Layer& L = net->layers[li];
+        if (net->prof_on) PROF(net, st, stage_name("bwd", li, L).c_str());
         if (L.kind == L_ACT && L.relu_into_pool && skip_fused_relu) { skip_fused_relu = false; continue; }   // done inside the pool backward
         // the input of a layer that follows a fused relu is that relu's (never materialised) output: pool kernels take the pre-activation
         const float* in = li == 0 ? x : act_ptr(net, net->layers[li - 1]);
@@ -870,12 +997,8 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                 else first_conv_wgrad_from_pool_kernel<<<blocks, 256, smem, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
                 NET_LAUNCH(net);
             }
-            reduce_partials_warp_kernel<<<(K * N + 7) / 8, 256, 0, st>>>(dW, pw, blocks, (long long)K * N);
+            reduce_partials_warp2_kernel<<<(K * N + N + 7) / 8, 256, 0, st>>>(dW, pw, (long long)K * N, dB, pb, dB ? N : 0, blocks);
             NET_LAUNCH(net);
-            if (dB) {
-                reduce_partials_warp_kernel<<<(N + 7) / 8, 256, 0, st>>>(dB, pb, blocks, N);
-                NET_LAUNCH(net);
-            }
             continue;
         }
         switch (L.kind) {
@@ -905,10 +1028,9 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             }
             if (!done) rc = run_gemm<false, true>(net, K, N, M, ColMajor{in, K}, RowMajor{d, N}, dW, nullptr, st);
             if (rc != NC_OK) return rc;
-            rc = run_colsum(net, d, M, N, dB, st);
-            if (rc != NC_OK) return rc;
+            if (li != bias_done) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
             if (need_dx) {   // dX[M][K] = dY[M][N] * W^T[N][K]   (W[in][out] is already the K-major B operand)
-                rc = tc_try(net, d, W, dn, nullptr, M, K, N, false, false, st, &done, true);
+                rc = tc_try(net, d, round_bwd ? net->params_hi + L.w_off : W, dn, nullptr, M, K, N, false, false, st, &done, true);
                 if (rc != NC_OK) return rc;
                 if (!done) rc = run_gemm<true, false>(net, M, K, N, RowMajor{d, N}, ColMajor{W, N}, dn, nullptr, st);
                 if (rc != NC_OK) return rc;
@@ -920,7 +1042,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             bool done;
             rc = tc_conv_try(net, 2, L, n, in, d, dW, nullptr, st, &done);
             if (rc != NC_OK) return rc;
-            bool bias_done = false;
+            bool bias_done_here = false;
             if (!done && L.ic <= 4 && K <= 32) {
                 // first layer: weight AND bias gradient in one pass over dY (tile kernel), CTA partials summed in fixed order
                 const long long ntiles = ((long long)M + 63) / 64;
@@ -933,14 +1055,10 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                     conv_smallc_wgrad_tile_kernel<<<blocks, 256, 0, st>>>(in, d, pw, pb, geom(L), M, ob, first_relu_y);
                     NET_LAUNCH(net);
                 }
-                reduce_partials_warp_kernel<<<(K * N + 7) / 8, 256, 0, st>>>(dW, pw, blocks, (long long)K * N);
+                reduce_partials_warp2_kernel<<<(K * N + N + 7) / 8, 256, 0, st>>>(dW, pw, (long long)K * N, dB, pb, dB ? N : 0, blocks);
                 NET_LAUNCH(net);
-                if (dB) {
-                    reduce_partials_warp_kernel<<<(N + 7) / 8, 256, 0, st>>>(dB, pb, blocks, N);
-                    NET_LAUNCH(net);
-                }
                 done = true;
-                bias_done = true;
+                bias_done_here = true;
             }
             if (!done && smallc_tc_ok(net, L, W, d)) {
                 // first layer: dW[K][N] = col^T[K][M] . dY[M][N] on the tensor cores over an explicit im2col
@@ -969,14 +1087,14 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                     NET_LAUNCH(net);
                 }
                 done = true;
-                bias_done = true;
+                bias_done_here = true;
             }
             if (!done) rc = run_gemm<false, true>(net, K, N, M, Im2colT{Im2col{in, geom(L)}}, RowMajor{d, N}, dW, nullptr, st);
             if (rc != NC_OK) return rc;
-            if (dB && !bias_done) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
+            if (dB && !bias_done_here && li != bias_done) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
             if (need_dx) {
                 const int Mi = n * L.ih * L.iw, Ki = L.fh * L.fw * L.oc;
-                rc = tc_conv_try(net, 1, L, n, d, W, dn, nullptr, st, &done);
+                rc = tc_conv_try(net, 1, L, n, d, round_bwd ? net->params_hi + L.w_off : W, dn, nullptr, st, &done);
                 if (rc != NC_OK) return rc;
                 if (!done) rc = run_gemm<true, false>(net, Mi, L.ic, Ki, DgradA{d, geom(L)}, DgradB{W, geom(L)}, dn, nullptr, st);
                 if (rc != NC_OK) return rc;
@@ -992,7 +1110,22 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                 uint8_t* argp = net->aux + L.aux_off * net->cap;
                 const bool v4 = tiled && (L.ic % 4) == 0 && (reinterpret_cast<uintptr_t>(argp) & 3) == 0 &&
                                 ((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(dn) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
-                if (v4) maxpool_bwd_tiled_vec4_kernel<<<grid_for(total_out / 4, sms), 256, 0, st>>>(d, argp, dn, pgeom(L), total_out / 4, fused ? out : nullptr);
+                // the gradient this launch scatters is the dY of the convolution below the pool (below the folded relu): summed
+                // per channel on the way, it is that layer's bias gradient
+                const int tgt = fused ? li - 2 : li - 1;
+                const int c4n = L.ic / 4;
+                if (v4 && c4n > 0 && 256 % c4n == 0) {
+                    const bool want_cs = tgt >= 0 && net->layers[tgt].kind == L_CONV && net->layers[tgt].b_off >= 0 && net->layers[tgt].oc == L.ic &&
+                                         !(net->fuse_first && tgt == 0) && ((net->layers[tgt].b_off & 3) == 0);
+                    int blocks = grid_for(total_out / 4, sms);
+                    if (want_cs && blocks > 4 * sms) blocks = 4 * sms;            // the last CTA sums one partial row per CTA
+                    if (want_cs) { rc = reserve_ws(net, (size_t)blocks * L.ic * sizeof(float)); if (rc != NC_OK) return rc; }
+                    maxpool_bwd_tiled_vec4_cs_kernel<<<blocks, 256, 0, st>>>(d, argp, dn, pgeom(L), total_out / 4, fused ? out : nullptr,
+                                                                              round_bwd ? 1 : 0, want_cs ? net->ws : nullptr,
+                                                                              want_cs ? net->grads + net->layers[tgt].b_off : nullptr, net->counters + 8);
+                    if (want_cs) bias_done = tgt;
+                }
+                else if (v4) maxpool_bwd_tiled_vec4_kernel<<<grid_for(total_out / 4, sms), 256, 0, st>>>(d, argp, dn, pgeom(L), total_out / 4, fused ? out : nullptr);
                 else if (tiled) maxpool_bwd_tiled_kernel<<<grid_for(total_out, sms), 256, 0, st>>>(d, argp, dn, pgeom(L), total_out, fused ? out : nullptr);
                 else maxpool_bwd_kernel<<<grid_for(total_in, sms), 256, 0, st>>>(d, net->aux + L.aux_off * net->cap, dn, pgeom(L), total_in);
                 NET_LAUNCH(net);
@@ -1002,7 +1135,24 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             if (need_dx) {
                 const long long total = (long long)n * L.out_size;
                 const bool fused = li > 0 && net->layers[li - 1].act_fused;
-                act_bwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(fused ? out : in, out, d, dn, total, L.act, L.slope);   // relu: y > 0 <=> x > 0
+                const float* xin = fused ? out : in;                          // relu: y > 0 <=> x > 0
+                const int C = L.oc, c4n = C / 4;
+                const bool v4 = (C % 4) == 0 && c4n > 0 && 256 % c4n == 0 &&
+                                ((reinterpret_cast<uintptr_t>(xin) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(dn)) & 15) == 0;
+                if (v4) {
+                    // dn is the dY of the layer below: its per-channel sums are that layer's bias gradient
+                    const Layer& B = net->layers[li - 1];
+                    const bool want_cs = (B.kind == L_CONV || B.kind == L_CONNECT) && B.b_off >= 0 && B.oc == C && (B.b_off & 3) == 0 &&
+                                         !(net->fuse_first && li - 1 == 0) && !(li - 1 == 0 && B.kind == L_CONV && B.ic <= 4 && B.fh * B.fw * B.ic <= 32);
+                    int blocks = grid_for(total / 4, sms);
+                    if (want_cs && blocks > 4 * sms) blocks = 4 * sms;
+                    if (want_cs) { rc = reserve_ws(net, (size_t)blocks * C * sizeof(float)); if (rc != NC_OK) return rc; }
+                    act_bwd_vec4_cs_kernel<<<blocks, 256, 0, st>>>(xin, out, d, dn, total / 4, c4n, L.act, L.slope, round_bwd ? 1 : 0,
+                                                                    want_cs ? net->ws : nullptr, want_cs ? net->grads + B.b_off : nullptr, net->counters + 8);
+                    if (want_cs) bias_done = li - 1;
+                } else {
+                    act_bwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(xin, out, d, dn, total, L.act, L.slope);
+                }
                 NET_LAUNCH(net);
             }
             break;
@@ -1012,7 +1162,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                 float* sums = net->dp_buf;
                 norm_bwd_sums_kernel<<<L.oc, 256, 0, st>>>(d, net->act + L.aux_off * net->cap, rows, L.oc, sums, dW, dB);
                 NET_LAUNCH(net);
-                const int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, sums, (size_t)2 * L.oc, st);
+                const int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm_norm ? net->comm_norm : net->comm, sums, (size_t)2 * L.oc, st);
                 if (rc != NC_OK) return rc;
                 norm_bwd_apply_kernel<<<L.oc, 256, 0, st>>>(d, net->act + L.aux_off * net->cap, net->stat + L.stat_off, W, dn, rows, L.oc, sums,
                                                              (float)(rows * net->world));
@@ -1063,6 +1213,7 @@ extern "C" int nc_net_apply(nc_net* net, int opt, float lr, void* stream) {
     int rc = ensure_state(net, opt, st);
     if (rc != NC_OK) return rc;
     const int grid = grid_for(net->nparams, net->ctx->sm_count);
+    PROF(net, st, "optimizer");
     if (opt == 0) adagrad_kernel<<<grid, 256, 0, st>>>(net->params, net->grads, net->st_adagrad, net->nparams, lr);
     else if (opt == 1) sgd_kernel<<<grid, 256, 0, st>>>(net->params, net->grads, net->nparams, lr);
     else {
@@ -1073,6 +1224,40 @@ extern "C" int nc_net_apply(nc_net* net, int opt, float lr, void* stream) {
     }
     NET_LAUNCH(net);
     net->global_step++;
+    return NC_OK;
+}
+
+// ---- per-stage timing of the next step(s): CUDA events recorded on the step's own stream around every layer's forward and
+// backward launches (bench.py's roofline of the dominant kernel comes from here)
+extern "C" int nc_net_profile(nc_net* net, int on) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    net->prof_on = on != 0;
+    net->prof_names.clear();
+    net->prof_used = 0;
+    return NC_OK;
+}
+
+// Closes the last stage, synchronises, and writes up to `max` stage durations (milliseconds) to ms[] and their names,
+// newline-separated, to names (capacity cap bytes).  *count = number of stages recorded since nc_net_profile(net, 1).
+extern "C" int nc_net_profile_read(nc_net* net, void* stream, float* ms, int max, char* names, size_t cap, int* count) {
+    if (!net || !count) return nc_set_error(net ? net->ctx : nullptr, NC_EINVAL, "NULL argument");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (net->prof_on && net->prof_used) prof_mark(net, st, "(end)");
+    NET_CUDA(net, cudaStreamSynchronize(st));
+    const int stages = net->prof_used ? (int)net->prof_used - 1 : 0;
+    *count = stages;
+    std::string all;
+    for (int i = 0; i < stages; ++i) {
+        float t = 0.0f;
+        NET_CUDA(net, cudaEventElapsedTime(&t, net->prof_events[i], net->prof_events[i + 1]));
+        if (ms && i < max) ms[i] = t;
+        all += net->prof_names[i];
+        all += '\n';
+    }
+    if (names && cap) { strncpy(names, all.c_str(), cap - 1); names[cap - 1] = 0; }
+    net->prof_names.clear();
+    net->prof_used = 0;
     return NC_OK;
 }
 
@@ -1135,18 +1320,10 @@ extern "C" int nc_nccl_unique_id(nc_ctx* ctx, const char* libnccl_path, unsigned
     return nc_nccl_unique_id_impl(ctx, out_id);
 }
 
-extern "C" int nc_net_attach_nccl(nc_net* net, const char* libnccl_path, const unsigned char id[128], int rank, int world) {
-    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
-    if (!id || world < 1 || rank < 0 || rank >= world) return net_err(net, NC_EINVAL, "bad rank %d / world %d", rank, world);
-    if (net->comm) return net_err(net, NC_EINVAL, "net is already attached to a communicator");
-    int rc = nc_nccl_load(net->ctx, libnccl_path);
-    if (rc != NC_OK) return rc;
-    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+static int attach_common(nc_net* net, int rank, int world) {
     int maxc = 0;
     for (auto& L : net->layers) if (L.kind == L_NORM && L.oc > maxc) maxc = L.oc;
     if (maxc && !net->dp_buf) NET_CUDA(net, cudaMalloc(&net->dp_buf, (size_t)2 * maxc * sizeof(float)));
-    rc = nc_nccl_comm_init(net->ctx, &net->comm, id, rank, world);
-    if (rc != NC_OK) return rc;
     net->rank = rank; net->world = world;
     // split point: the first layer (in forward order, not layer 0) from which on the parameters are at least half of all
     net->split_layer = -1;
@@ -1157,13 +1334,45 @@ extern "C" int nc_net_attach_nccl(nc_net* net, const char* libnccl_path, const u
             if (2 * (net->nparams - L.w_off) >= net->nparams) { net->split_layer = li; net->split_off = L.w_off; }
             else break;
         }
+        if (net->split_layer >= 0 && maxc) {
+            // nets with norm layers also exchange moments on the compute stream: that needs a communicator of its own
+            int rc = nc_nccl_comm_dup(net->ctx, net->comm, rank, &net->comm_norm);
+            if (rc != NC_OK) return rc;
+            if (!net->comm_norm) net->split_layer = -1;       // this NCCL cannot split: everything stays on one stream
+        }
         if (net->split_layer >= 0 && !net->comm_stream) {
             NET_CUDA(net, cudaStreamCreateWithFlags(&net->comm_stream, cudaStreamNonBlocking));
             NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_tail_ready, cudaEventDisableTiming));
             NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_tail_done, cudaEventDisableTiming));
+            NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_head_ready, cudaEventDisableTiming));
         }
     }
     return NC_OK;
+}
+
+extern "C" int nc_net_attach_nccl(nc_net* net, const char* libnccl_path, const unsigned char id[128], int rank, int world) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (!id || world < 1 || rank < 0 || rank >= world) return net_err(net, NC_EINVAL, "bad rank %d / world %d", rank, world);
+    if (net->comm) return net_err(net, NC_EINVAL, "net is already attached to a communicator");
+    int rc = nc_nccl_load(net->ctx, libnccl_path);
+    if (rc != NC_OK) return rc;
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    rc = nc_nccl_comm_init(net->ctx, &net->comm, id, rank, world);
+    if (rc != NC_OK) return rc;
+    net->comm_owned = true;
+    return attach_common(net, rank, world);
+}
+
+extern "C" int nc_net_attach_comm(nc_net* net, const char* libnccl_path, void* nccl_comm, int rank, int world) {
+    if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
+    if (!nccl_comm || world < 1 || rank < 0 || rank >= world) return net_err(net, NC_EINVAL, "bad communicator / rank %d / world %d", rank, world);
+    if (net->comm) return net_err(net, NC_EINVAL, "net is already attached to a communicator");
+    int rc = nc_nccl_load(net->ctx, libnccl_path);
+    if (rc != NC_OK) return rc;
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    net->comm = nccl_comm;
+    net->comm_owned = false;
+    return attach_common(net, rank, world);
 }
 
 extern "C" int nc_net_detach_nccl(nc_net* net) {
@@ -1171,10 +1380,11 @@ extern "C" int nc_net_detach_nccl(nc_net* net) {
     if (net->comm) {
         cudaSetDevice(net->ctx->device);
         cudaDeviceSynchronize();
-        nc_nccl_comm_destroy(net->comm);
+        if (net->comm_norm) { nc_nccl_comm_destroy(net->comm_norm); net->comm_norm = nullptr; }
+        if (net->comm_owned) nc_nccl_comm_destroy(net->comm);
         net->comm = nullptr;
     }
-    net->rank = 0; net->world = 1;
+    net->rank = 0; net->world = 1; net->split_layer = -1;
     return NC_OK;
 }
 
@@ -1185,11 +1395,16 @@ extern "C" int nc_net_allreduce_grads(nc_net* net, void* stream) {
     NET_CUDA(net, cudaSetDevice(net->ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
     if (net->tail_in_flight) {
-        // the tail went out during backward: only the head is left, then the step continues once both have landed
+        // the tail went out during backward: the head follows it on the SAME stream (one stream per communicator, one
+        // order of collectives on every rank), then the step continues once both have landed
         net->tail_in_flight = false;
-        int rc = NC_OK;
-        if (net->split_off > 0) rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads, (size_t)net->split_off, st);
-        if (rc != NC_OK) return rc;
+        if (net->split_off > 0) {
+            NET_CUDA(net, cudaEventRecord(net->ev_head_ready, st));
+            NET_CUDA(net, cudaStreamWaitEvent(net->comm_stream, net->ev_head_ready, 0));
+            const int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads, (size_t)net->split_off, net->comm_stream);
+            if (rc != NC_OK) return rc;
+            NET_CUDA(net, cudaEventRecord(net->ev_tail_done, net->comm_stream));
+        }
         NET_CUDA(net, cudaStreamWaitEvent(st, net->ev_tail_done, 0));
         return NC_OK;
     }

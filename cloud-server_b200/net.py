@@ -76,6 +76,22 @@ class Net:
         _lib.check(self.ctx.handle, _lib.lib().nc_net_get_params(self.handle, out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def profile(self, fn):
+        """Run fn() (forward / backward / train_step calls on this net) with per-stage CUDA-event timing on:
+        returns [(stage name, milliseconds), ...] in launch order."""
+        L = _lib.lib()
+        _lib.check(self.ctx.handle, L.nc_net_profile(self.handle, 1))
+        try:
+            fn()
+            ms = (C.c_float * 512)()
+            names = C.create_string_buffer(1 << 16)
+            cnt = C.c_int()
+            _lib.check(self.ctx.handle, L.nc_net_profile_read(self.handle, self.ctx._stream(), ms, 512, names, len(names), C.byref(cnt)))
+        finally:
+            L.nc_net_profile(self.handle, 0)
+        nm = names.value.decode().split("\n")
+        return [(nm[i], float(ms[i])) for i in range(min(cnt.value, 512))]
+
     def set_math(self, math):
         _lib.check(self.ctx.handle, _lib.lib().nc_net_set_math(self.handle, int(math)))
 
@@ -192,7 +208,9 @@ class Net:
 class GraphedTrainStep:
     """One sess.run(train_op) (construct_distribute.py:413) captured into a CUDA graph and replayed: the ~30 kernel
     launches of a LeNet step cost one graph launch.  Fixed batch size, loss and optimizer; Adagrad (what the reference
-    runs) or SGD only -- Adam's step size is a host-side function of global_step.  Single device.
+    runs) or SGD only -- Adam's step size is a host-side function of global_step.  On a net attached to a communicator
+    (attach_nccl) the captured step contains the NCCL all-reduces of the gradient buffer (issued on the library's side
+    stream, which joins the capture through events): every rank must build and replay its graph in step with the others.
 
         step = GraphedTrainStep(net, 256)
         loss, hits = step(x, y)          # x, y: CUDA tensors [256, features], [256, classes]; copied into the graph's inputs
@@ -202,8 +220,6 @@ class GraphedTrainStep:
         oid = 0 if opt == "compat" else (OPT[opt] if isinstance(opt, str) else int(opt))
         if oid == 2:
             raise ValueError("Adam's bias-corrected step size changes every step on the host: it cannot be replayed from a graph")
-        if net.world > 1:
-            raise ValueError("a net attached to a communicator is stepped eagerly")
         self.net, self.batch = net, int(batch)
         dev = net.ctx.tdev
         self.x = torch.zeros((self.batch, net.in_features), dtype=torch.float32, device=dev)

@@ -224,6 +224,13 @@ int64_t nc_net_global_step(nc_net* net);
  * keeps in tf.train.get_or_create_global_step() (:371).  Adam must not be captured: its step size
  * depends on global_step and is computed on the host. */
 int nc_net_advance_step(nc_net* net, int64_t k);
+/* Per-stage timing of a step, for benchmarks: after nc_net_profile(net, 1) every forward / backward call on this net
+ * records a CUDA event on its stream in front of each layer's launches (and of the loss head and the optimizer);
+ * nc_net_profile_read closes the last stage, synchronises `stream`, returns the stage durations in milliseconds (ms[0..max))
+ * and their names (newline separated) and clears the record.  The duration of the reference's sess.run(train_op)
+ * (construct_distribute.py:412-414) is the sum; the stages are this library's own kernels. */
+int nc_net_profile(nc_net* net, int on);
+int nc_net_profile_read(nc_net* net, void* stream, float* ms, int max, char* names, size_t cap, int* count);
 /* The library-owned activation arena, split-K workspace and im2col buffer grow on demand (a forward,
  * predict or backward with a larger batch than any before frees and re-allocates them).  A CUDA graph
  * captured earlier holds the OLD device addresses: replaying it would read and write freed memory.
@@ -258,6 +265,10 @@ int nc_net_reserve(nc_net* net, int max_batch);
 int nc_nccl_unique_id(nc_ctx* ctx, const char* libnccl_path, unsigned char out_id[128]);
 int nc_net_attach_nccl(nc_net* net, const char* libnccl_path, const unsigned char id[128], int rank, int world);
 int nc_net_allreduce_grads(nc_net* net, void* stream);
+/* Same as nc_net_attach_nccl for a host that already owns a communicator: nccl_comm is its ncclComm_t (one per
+ * process, spanning `world` ranks); the library uses it on its own side stream and never destroys it.  While the net is
+ * attached the host must not issue collectives on that communicator itself. */
+int nc_net_attach_comm(nc_net* net, const char* libnccl_path, void* nccl_comm, int rank, int world);
 int nc_net_detach_nccl(nc_net* net);
 /* optimizer state (Adagrad accumulator / Adam m,v) for checkpoints: float32[slots*param_count] */
 int nc_net_state_slots(nc_net* net, int opt);

@@ -55,6 +55,30 @@ def main():
         if dp.in_library:
             net.detach_nccl()
         net.close(); single.close()
+    # the data-parallel step replayed from a CUDA graph (NCCL all-reduces captured with it) == the eager single-device step
+    from cloud_server_b200.net import GraphedTrainStep
+    net = Net(LENET, ctx, seed=100 + rank)
+    dp = DataParallel(net, in_library=True)
+    w0 = net.get_params().copy()
+    single = Net(LENET, ctx, seed=5)
+    single.set_params(w0)
+    n = B // world
+    step = GraphedTrainStep(net, n, "entropy", "sgd", 0.05)
+    for s in range(3):
+        step(x[s, rank * n:(rank + 1) * n], y[s, rank * n:(rank + 1) * n])
+        single.train_step(x[s], y[s], "entropy", "sgd", 0.05)
+    a, b = net.get_params(), single.get_params()
+    err = np.abs(a - b).max() / np.abs(b - w0).max()
+    t = net.params.clone()
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    same = bool(torch.equal(t, net.params))
+    if rank == 0:
+        print("dp_check world=%d net=lenet opt=sgd CUDA graph (NCCL captured): |dp - single| / |update| = %.3e, ranks identical = %s, step %d"
+              % (world, err, same, net.global_step), flush=True)
+    ok = ok and err < 1e-3 and same and net.global_step == 3
+    del step
+    net.detach_nccl()
+    net.close(); single.close()
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
