@@ -1,18 +1,23 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the NJUCloud hot path on B200 (contract: see DESIGN.md section 6).
 
-Main line (one JSON object on stdout, rank 0):
-  workload C2 = BASELINE.json configs[1]: batch preprocess of 4096 synthetic 1024x768x3 uploads
-  -> 28x28 normalised float (train-side chain: cubic resize -> gray -> *1/255), per GPU.
-  value  = whole-job images/s with the uploads already resident in HBM (CUDA events, max over ranks)
-  e2e    = the same through the public API with HOST buffers (pinned), H2D + kernel + D2H inside
-  roofline / cpu_baseline / clocks / gpu_launches as the contract asks.
-Extra objects in the same line: "predict_chain" (the streaming, HBM-bound kernel of the preprocess
-half), "train" (LeNet train step, data parallel over the ranks), "predict" (LeNet inference).
+Main line (one JSON object on stdout, rank 0), the same workload at every N so that the driver's 1 -> 8 curve measures
+the gradient exchange:
+  workload C4 = BASELINE.json configs[3] (N = 1: its single-device reference point, configs[2]'s net at the same batch):
+  LeNet (2 conv + 2 dense) train step -- forward, softmax-CE, backward, Adagrad(1e-4) -- at GLOBAL batch 2048 split over the
+  ranks (strong scaling), gradients summed by NCCL inside the step, the step replayed from a CUDA graph.
+  value     = whole-job images/s with the 60 000-picture set resident in HBM (CUDA events, max over ranks)
+  e2e       = the same step with every batch coming from PINNED HOST memory (H2D of pictures and labels, loss read back)
+  roofline  = the dominant kernel of the step (per-stage CUDA events inside the library), tensor-bound
+  cpu_baseline / --impl reference = the same step in torch-CPU on all host cores (oracle/torchref.py, kind "port":
+              TensorFlow 1.x, what the reference runs, cannot be installed here)
+Sub-objects of the same line: "preprocess" (BASELINE configs[1], C2: the whole preprocess half over 4096 uploads, with its
+own roofline / e2e / cpu_baseline -- replicas, no collective), "train_b256" (C3), "train_weak" (256 pictures per GPU),
+"train_c5_deepnet" (C5), "predict*" (C1-style inference), "dp_parity" (N > 1: the data-parallel step against the
+single-device step at the global batch, asserted before anything is timed).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
-Under torchrun (N > 1) one rank per GPU; preprocess = independent replicas (no collective),
-training = NCCL all-reduce of the flat gradient buffer.
+Under torchrun (N > 1) one rank per GPU.
 """
 import argparse
 import json
@@ -113,11 +118,13 @@ class ClockSampler:
 _CPU_SAMPLE = None
 
 
-def _cpu_init(sample_n):
+def _cpu_init(sample_n, ipp=False):
     """worker initialiser: every process builds the same bounded sample once"""
     global _CPU_SAMPLE
     import cv2
+    from oracle import cvref  # noqa: F401  (importing it switches IPP off: the canonical arithmetic)
     cv2.setNumThreads(1)   # parallelism comes from one picture per worker process
+    cv2.ipp.setUseIPP(bool(ipp))
     _CPU_SAMPLE = np.random.default_rng(0).integers(0, 256, (sample_n, H, W, C), np.uint8)
 
 
@@ -132,13 +139,13 @@ def _cpu_work(i):
     return 1
 
 
-def _cpu_pool(procs, sample_n):
+def _cpu_pool(procs, sample_n, ipp=False):
     import multiprocessing as mp
-    return mp.get_context("fork").Pool(procs, initializer=_cpu_init, initargs=(sample_n,))
+    return mp.get_context("fork").Pool(procs, initializer=_cpu_init, initargs=(sample_n, ipp))
 
 
-def cpu_baseline_throughput(seconds, procs, sample_n=16):
-    with _cpu_pool(procs, sample_n) as pool:
+def cpu_baseline_throughput(seconds, procs, sample_n=16, ipp=False):
+    with _cpu_pool(procs, sample_n, ipp) as pool:
         pool.map(_cpu_work, range(procs))          # warm-up: sample built, libraries loaded
         done = 0
         t0 = time.perf_counter()
@@ -153,33 +160,47 @@ def cpu_baseline_throughput(seconds, procs, sample_n=16):
 WORKLOAD = ("C2 batch preprocess: %d synthetic 1024x768x3 uint8 uploads per GPU through the whole preprocess half -> "
             "28x28 float32: train-side chain (cv2-exact cubic resize -> gray -> *1/255) and predict-side chain "
             "(PIL-exact L -> antialiased bicubic 20x20 -> threshold -> canvas -> /255)")
+TRAIN_WORKLOAD = ("C4 LeNet train step (conv5x5x32-relu-pool-conv5x5x64-relu-pool-fc1024-relu-fc10, softmax-CE, Adagrad 1e-4 = "
+                  "what the reference runs), global batch %d over %d GPU(s), 60000 synthetic MNIST-shaped pictures")
+GLOBAL_BATCH = 2048
+
+
+def cpu_train_step_throughput(batch, steps, warmup, threads):
+    """The reference arm of the train-step benchmark: the same graph, loss and optimizer in torch-CPU on all host cores
+    (oracle.torchref.TorchStep; TensorFlow 1.x itself is not installable here).  Synthetic data of the benchmark's shape."""
+    import torch
+    from oracle.torchref import TorchStep
+    from oracle import tfref
+    torch.set_num_threads(threads)
+    ts = TorchStep(tfref.LENET, seed=2, threads=threads, opt="adagrad", lr=1e-4)
+    g = torch.Generator().manual_seed(99)
+    n_img = max(batch * 4, 8192)
+    xs = torch.rand((n_img, 784), generator=g)
+    ys = torch.nn.functional.one_hot(torch.randint(0, 10, (n_img,), generator=g), 10).float()
+    nb = n_img // batch
+    for i in range(warmup):
+        ts.step(xs[(i % nb) * batch:(i % nb + 1) * batch], ys[(i % nb) * batch:(i % nb + 1) * batch])
+    t0 = time.perf_counter()
+    for i in range(steps):
+        b = (i + warmup) % nb
+        ts.step(xs[b * batch:(b + 1) * batch], ys[b * batch:(b + 1) * batch])
+    dt = time.perf_counter() - t0
+    return batch * steps / dt, dt
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    per_step = 256
-    with _cpu_pool(threads, 16) as pool:
-        def step():
-            return sum(pool.map(_cpu_work, range(per_step), chunksize=2))
-        for _ in range(min(args.warmup, 1)):
-            step()
-        t0 = time.perf_counter()
-        n = 0
-        for _ in range(args.steps):
-            n += step()
-        dt = time.perf_counter() - t0
-    val = n / dt
+    val, dt = cpu_train_step_throughput(GLOBAL_BATCH, args.steps, min(args.warmup, 2), threads)
+    sample = ("%d steps of the same LeNet step at batch %d in torch-CPU (oracle/torchref.py: explicit asymmetric SAME padding, "
+              "mean softmax-CE, autograd, TF-1.x Adagrad acc0 = 0.1), %d threads" % (args.steps, GLOBAL_BATCH, threads))
     line = {
         "impl": "reference", "metric": "images/sec", "value": val, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD % per_step, "pictures_per_step": per_step},
-        "cpu_baseline": {"value": val, "unit": "images/s", "cores": threads, "kind": "port",
-                         "sample": "16 distinct 1024x768x3 pictures per worker cycled, %d per step; the reference's own cv2 / "
-                                   "Pillow calls for both chains, in memory (no JPEG), IPP off, one worker process per core"
-                                   % per_step},
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": TRAIN_WORKLOAD % (GLOBAL_BATCH, args.gpus), "global_batch": GLOBAL_BATCH},
+        "cpu_baseline": {"value": val, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     _emit(line)
@@ -223,19 +244,68 @@ def max_over_ranks(torch, ms, dist_on, device):
 # written, Adagrad reads g,w,acc and writes w,acc)
 LENET_FLOP_PER_IMG = 82.05e6
 LENET_PARAMS = 3274634
+MATH_NAMES = {0: "fp32 simt", 1: "tcgen05 3xTF32 (fp32-class accuracy)", 2: "tcgen05 1xTF32",
+              3: "tcgen05 3xTF32 forward + single rounded-TF32 products for the gradients"}
 
 
 def lenet_step_bytes(b):
     return 4 * b * (2 * 48858 + 2 * 48074) + 4 * 8 * LENET_PARAMS
 
 
-def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
-    """LeNet (BASELINE configs 2-3): train step images/s (data parallel over the ranks, NCCL
-    all-reduce of the flat gradient buffer) and inference images/s.  Synthetic MNIST-shaped data
-    resident in HBM (60 000 x 784 float32), random-init weights."""
+def lenet_stage_flops(name, b):
+    """algorithmic FLOPs of one profiled stage of the LeNet step at per-GPU batch b (2 * MACs of the contraction it holds)"""
+    if "conv 5x5x32->64" in name:
+        return 2.0 * b * 196 * 800 * 64
+    if "connect 3136->1024" in name:
+        return 2.0 * b * 3136 * 1024
+    if "conv 5x5x1->32" in name or "L2 pool" in name or "L0 conv" in name:      # the fused first block (conv1 + relu + pool)
+        return 2.0 * b * 784 * 25 * 32
+    return 0.0
+
+
+def dp_parity_check(torch, ctx, world, rank, device, math):
+    """N > 1, before anything is timed: two data-parallel steps (library communicator, exchange overlapped with backward)
+    against two single-device steps at the global batch, from the same weights.  Returns the error relative to the update."""
     from cloud_server_b200.net import Net, DataParallel
     from cloud_server_b200.configs import LENET
-    out = {}
+    g = torch.Generator(device=device)
+    g.manual_seed(7)
+    B = 256 * world if 256 * world <= 2048 else 2048
+    x = torch.rand((2, B, 784), device=device, generator=g)
+    y = torch.nn.functional.one_hot(torch.randint(0, 10, (2, B), device=device, generator=g), 10).float()
+    net = Net(LENET, ctx, seed=100 + rank)
+    net.set_math(math)
+    dp = DataParallel(net, in_library=True)
+    w0 = net.params.clone()
+    single = Net(LENET, ctx, seed=5)
+    single.set_math(math)
+    single.params.copy_(w0)
+    n = B // world
+    for s_ in range(2):
+        dp.train_step(x[s_, rank * n:(rank + 1) * n], y[s_, rank * n:(rank + 1) * n], "entropy", "sgd", 0.05)
+        single.train_step(x[s_], y[s_], "entropy", "sgd", 0.05)
+    upd = float((single.params - w0).abs().max().item())
+    err = float((net.params - single.params).abs().max().item()) / max(upd, 1e-30)
+    t = torch.tensor([err], dtype=torch.float64, device=device)
+    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    same = net.params.clone()
+    torch.distributed.all_reduce(same, op=torch.distributed.ReduceOp.MAX)
+    identical = bool(torch.equal(same, net.params))
+    net.detach_nccl()
+    net.close(); single.close()
+    err = float(t.item())
+    assert err < 1e-3 and identical, "data-parallel step differs from the single-device step: %.3e, identical ranks %s" % (err, identical)
+    return {"net": "LeNet", "global_batch": B, "steps": 2, "optimizer": "SGD 0.05", "error_relative_to_update": err,
+            "ranks_bit_identical": identical, "tolerance": 1e-3,
+            "target": "single-device step at the global batch (construct_distribute.py:413 with batch = global)"}
+
+
+def run_train_bench(torch, ctx, args, rank, world, device, peaks, dist_on, sampler):
+    """The main line (C4) and the other CNN sub-benchmarks.  Synthetic MNIST-shaped data resident in HBM
+    (60 000 x 784 float32 = 188 MB, larger than L2; a different batch every step), random-init weights."""
+    from cloud_server_b200.net import Net, DataParallel, GraphedTrainStep
+    from cloud_server_b200.configs import LENET, DEEPNET
+    main, out = {}, {}
     g = torch.Generator(device=device)
     g.manual_seed(99)        # same data on every rank; each rank takes its slice of the global batch
     n_img = 60000
@@ -243,91 +313,130 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
     ys = torch.nn.functional.one_hot(torch.randint(0, 10, (n_img,), device=device, generator=g), 10).float()
     net = Net(LENET, ctx, seed=2)
     net.set_math(args.math)
-    # N > 1: the gradient exchange runs in the library (its own NCCL communicator, tail of the buffer overlapped with the
-    # rest of backward) unless --dp torch asks for torch.distributed's all-reduce after backward
     dp = DataParallel(net, in_library=(args.dp == "library"))
-    steps = max(10, args.steps)
+    steps = args.steps
+    traffic = traffic_table()
 
-    def bench_train(global_batch, key):
+    def bench_train(global_batch, want_profile=False, want_e2e=False, clock=False):
         local = global_batch // world
         nb = n_img // global_batch
         state = {"i": 0}
 
-        def step():
+        def batch_of():
             b = state["i"] % nb
             state["i"] += 1
             lo = b * global_batch + rank * local
-            dp.train_step(xs[lo:lo + local], ys[lo:lo + local], "entropy", "compat")
+            return xs[lo:lo + local], ys[lo:lo + local]
+
+        def step():
+            xb, yb = batch_of()
+            dp.train_step(xb, yb, "entropy", "compat")
 
         cnt = [0]
-        ms = time_steps(torch, step, steps, args.warmup, dist_on, counter=lambda: ctx.launches, count_out=cnt)
-        ms = max_over_ranks(torch, ms, dist_on, device)
-        eager_per = ms / steps
+        ms = time_steps(torch, step, max(3, min(steps, 10)), args.warmup, dist_on, counter=lambda: ctx.launches, count_out=cnt)
+        eager_per = max_over_ranks(torch, ms, dist_on, device) / max(3, min(steps, 10))
+        launches_per_step = cnt[0] / max(3, min(steps, 10))
+        prof = None
+        if want_profile:
+            xb, yb = batch_of()
+            prof = net.profile(lambda: dp.train_step(xb, yb, "entropy", "compat"))
         graph = None
-        if world == 1 and not args.no_graph:
-            # the same step replayed from a CUDA graph (one graph launch instead of ~30 kernel launches); each step still
-            # copies its own batch into the graph's input buffers
-            from cloud_server_b200.net import GraphedTrainStep
+        per = eager_per
+        if clock and (args.no_graph or not (world == 1 or dp.in_library)):
+            sampler.start()
+            ms = time_steps(torch, step, steps, args.warmup, dist_on)
+            sampler.stop()
+            per = eager_per = max_over_ranks(torch, ms, dist_on, device) / steps
+        if not args.no_graph and (world == 1 or dp.in_library):
+            # the same step replayed from a CUDA graph (kernels and, for N > 1, the NCCL all-reduces captured once); each step
+            # still copies its own batch into the graph's input buffers
             graph = GraphedTrainStep(net, local, "entropy", "compat")
 
             def gstep():
-                b = state["i"] % nb
-                state["i"] += 1
-                lo = b * global_batch
-                graph(xs[lo:lo + local], ys[lo:lo + local])
+                xb, yb = batch_of()
+                graph(xb, yb)
 
+            if clock:
+                sampler.start()
             ms = time_steps(torch, gstep, steps, args.warmup, dist_on)
-        per = ms / steps
+            if clock:
+                t_end = time.perf_counter() + 0.5     # keep the same kernels running so the NVML sampler sees clocks under load
+                while time.perf_counter() < t_end:
+                    for _ in range(20):
+                        gstep()
+                    torch.cuda.synchronize()
+                sampler.stop()
+            per = max_over_ranks(torch, ms, dist_on, device) / steps
         byts = lenet_step_bytes(local)
-        out[key] = {
-            "value": global_batch * steps / (ms * 1e-3), "unit": "images/s", "ms_per_step": per, "global_batch": global_batch,
-            "per_gpu_batch": local, "optimizer": "Adagrad(1e-4) (what the reference runs)", "gpu_launches_per_step": cnt[0] / steps,
+        res = {
+            "value": global_batch / (per * 1e-3), "unit": "images/s", "ms_per_step": per, "global_batch": global_batch,
+            "per_gpu_batch": local, "optimizer": "Adagrad(1e-4) (what the reference runs)", "gpu_launches_per_step": launches_per_step,
             "cuda_graph": graph is not None, "ms_per_step_eager": eager_per,
-            "gradient_exchange": None if world == 1 else ("library NCCL communicator, dense-layer gradients overlapped with the "
-                                                          "convolution backward" if dp.in_library else "torch.distributed all-reduce after backward"),
-            "math": {0: "fp32 simt", 1: "tcgen05 3xTF32 (fp32-class accuracy)", 2: "tcgen05 1xTF32", 3: "tcgen05 3xTF32 forward + 1xTF32 gradients"}[args.math],
-            "roofline": {"bound": "hbm", "achieved": byts / (per * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": byts / (per * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts,
-                         "tflops": LENET_FLOP_PER_IMG * local / (per * 1e-3) / 1e12},
+            "gradient_exchange": None if world == 1 else ("library NCCL communicator on a side stream, dense-layer gradients overlapped "
+                                                          "with the convolution backward, captured in the graph" if dp.in_library
+                                                          else "torch.distributed all-reduce after backward"),
+            "math": MATH_NAMES[args.math],
+            "step_roofline": {"bound": "hbm", "achieved": byts / (per * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                              "frac": byts / (per * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts,
+                              "tflops": LENET_FLOP_PER_IMG * local / (per * 1e-3) / 1e12,
+                              "note": "layer-boundary byte model of SURVEY 8(d) for the whole step"},
         }
+        if prof:
+            total = sum(ms_ for _, ms_ in prof)
+            res["stages_ms"] = [[nm, round(ms_, 5)] for nm, ms_ in prof]
+            tens = [(nm, ms_) for nm, ms_ in prof if lenet_stage_flops(nm, local) > 0]
+            nm, ms_ = max(tens, key=lambda t: t[1])
+            fl = lenet_stage_flops(nm, local)
+            peak = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
+            res["roofline"] = {
+                "bound": "tensor", "achieved": fl / (ms_ * 1e-3) / 1e12, "peak": peak, "unit": "TFLOP/s",
+                "frac": fl / (ms_ * 1e-3) / 1e12 / peak, "traffic": traffic.get("train_dominant_b%d" % local),
+                "kernel": nm + (" (dominant stage: %.0f%% of the eager step's %.3f ms)" % (100 * ms_ / total, total)),
+                "algorithmic_flops_per_launch": fl, "launch_ms": ms_, "peak_source": "measured (cuBLAS bf16, sustained)",
+                "note": "peak is the dense bf16 rate; this contraction runs kind::tf32 (half that rate) and, in the forward pass, as "
+                        "3 TF32 products per fp32 product (hi.hi + lo.hi + hi.lo) to hold north_star's 1e-3 on logits: the ceiling of "
+                        "a forward stage is peak / 6, of a gradient stage peak / 2",
+            }
+        if want_e2e:
+            # end to end: the batch comes from PINNED HOST memory every step (pictures + one-hot labels), the loss goes back
+            hx = [xs[i * local:(i + 1) * local].cpu().pin_memory() for i in range(4)]
+            hy = [ys[i * local:(i + 1) * local].cpu().pin_memory() for i in range(4)]
+            lh = torch.zeros(1).pin_memory()
+            xd, yd = torch.empty_like(xs[:local]), torch.empty_like(ys[:local])
+            k = {"i": 0}
 
+            def e2e():
+                i = k["i"] % 4
+                k["i"] += 1
+                if graph is not None:
+                    graph.x.copy_(hx[i], non_blocking=True)
+                    graph.y.copy_(hy[i], non_blocking=True)
+                    graph.graph.replay()
+                    lh.copy_(graph.loss, non_blocking=True)
+                else:
+                    xd.copy_(hx[i], non_blocking=True)
+                    yd.copy_(hy[i], non_blocking=True)
+                    loss, _ = dp.train_step(xd, yd, "entropy", "compat")
+                    lh.copy_(loss, non_blocking=True)
+
+            ms = max_over_ranks(torch, time_steps(torch, e2e, steps, 3, dist_on), dist_on, device)
+            res["e2e"] = {"value": global_batch * steps / (ms * 1e-3), "unit": "images/s",
+                          "h2d_bytes_per_step": world * local * (784 + 10) * 4, "d2h_bytes_per_step": 4 * world,
+                          "mode": "per rank: pinned host batch (pictures + labels) -> H2D -> graph replay of the step -> loss D2H"}
+        del graph
+        return res
+
+    # ---- main line: C4, global batch 2048 over the ranks (strong scaling); N = 1 is its single-device point
+    m = bench_train(GLOBAL_BATCH, want_profile=True, want_e2e=True, clock=True)
+    main.update(m)
     if world == 1:
-        bench_train(256, "train")                     # C3: batch 256
-        bench_train(2048, "train_b2048")              # C4's single-device reference point
+        out["train_b256"] = bench_train(256, want_profile=True, want_e2e=True)       # C3
     else:
-        bench_train(2048, "train")                    # C4: global batch 2048 over the ranks (strong)
-        bench_train(256 * world, "train_weak")        # 256 per GPU (weak)
-
-    # e2e train step: host (pinned) batch in, loss out, every step
-    if world == 1:
-        xb = xs[:256].cpu().pin_memory()
-        yb = ys[:256].cpu().pin_memory()
-        xd, yd = torch.empty_like(xs[:256]), torch.empty_like(ys[:256])
-        lh = torch.zeros(1).pin_memory()
-
-        gstep = None
-        if not args.no_graph:
-            from cloud_server_b200.net import GraphedTrainStep
-            gstep = GraphedTrainStep(net, 256, "entropy", "compat")
-
-        def e2e():
-            if gstep is not None:      # pinned host batch -> the graph's input buffers -> replay -> loss back to the host
-                gstep.x.copy_(xb, non_blocking=True)
-                gstep.y.copy_(yb, non_blocking=True)
-                gstep.graph.replay()
-                lh.copy_(gstep.loss, non_blocking=True)
-                return
-            xd.copy_(xb, non_blocking=True)
-            yd.copy_(yb, non_blocking=True)
-            loss, _ = net.train_step(xd, yd, "entropy", "compat")
-            lh.copy_(loss, non_blocking=True)
-
-        ms = time_steps(torch, e2e, steps, 3, False)
-        out["train"]["e2e"] = {"value": 256 * steps / (ms * 1e-3), "unit": "images/s",
-                               "h2d_bytes_per_step": 256 * (784 + 10) * 4, "d2h_bytes_per_step": 4}
+        out["train_weak"] = bench_train(256 * world, want_profile=True)            # 256 per GPU
+    if dp.in_library and world > 1:
+        net.detach_nccl()
 
     # C5: the user-constructed deeper CNN (4 conv + 3 dense) on 32x32x3, global batch 512 over the ranks
-    from cloud_server_b200.configs import DEEPNET
     n5 = 8192
     x5 = torch.rand((n5, 32 * 32 * 3), device=device, generator=g)
     y5 = torch.nn.functional.one_hot(torch.randint(0, 10, (n5,), device=device, generator=g), 10).float()
@@ -337,23 +446,31 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
     gb5 = 512
     loc5 = gb5 // world
     st5 = {"i": 0}
+    graph5 = GraphedTrainStep(net5, loc5, "entropy", "compat") if (not args.no_graph and (world == 1 or dp5.in_library)) else None
 
     def step5():
         b = st5["i"] % (n5 // gb5)
         st5["i"] += 1
         lo = b * gb5 + rank * loc5
-        dp5.train_step(x5[lo:lo + loc5], y5[lo:lo + loc5], "entropy", "compat")
+        if graph5 is not None:
+            graph5(x5[lo:lo + loc5], y5[lo:lo + loc5])
+        else:
+            dp5.train_step(x5[lo:lo + loc5], y5[lo:lo + loc5], "entropy", "compat")
 
     ms5 = max_over_ranks(torch, time_steps(torch, step5, steps, args.warmup, dist_on), dist_on, device)
     byts5 = 4 * loc5 * (2 * 114442 + 2 * 111370) + 32 * 2297130          # SURVEY 8(d) C5 formula
     out["train_c5_deepnet"] = {
         "value": gb5 * steps / (ms5 * 1e-3), "unit": "images/s", "ms_per_step": ms5 / steps, "global_batch": gb5,
-        "per_gpu_batch": loc5, "input": "32x32x3", "params": net5.param_count,
-        "roofline": {"bound": "hbm", "achieved": byts5 / (ms5 / steps * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": byts5 / (ms5 / steps * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts5,
-                     "tflops": 158.5e6 * loc5 / (ms5 / steps * 1e-3) / 1e12}}
+        "per_gpu_batch": loc5, "input": "32x32x3", "params": net5.param_count, "cuda_graph": graph5 is not None,
+        "step_roofline": {"bound": "hbm", "achieved": byts5 / (ms5 / steps * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                          "frac": byts5 / (ms5 / steps * 1e-3) / 1e9 / peaks["hbm_gbs"], "algorithmic_bytes_per_step": byts5,
+                          "tflops": 158.5e6 * loc5 / (ms5 / steps * 1e-3) / 1e12}}
+    del graph5
+    if dp5.in_library and world > 1:
+        net5.detach_nccl()
+    net5.close()
 
-    # inference: sess.run(argmax) (construct_inference.py:335-342), batched
+    # inference: sess.run(argmax) (construct_inference.py:335-342), batched -- per-rank replicas
     for nb_, key in ((4096, "predict"), (99, "predict_c1_99_pictures"), (1, "predict_single")):
         xb = xs[:nb_]
 
@@ -363,24 +480,15 @@ def run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on):
         ms = time_steps(torch, pstep, steps, 3, dist_on)
         ms = max_over_ranks(torch, ms, dist_on, device)
         out[key] = {"value": world * nb_ * steps / (ms * 1e-3), "unit": "images/s", "ms_per_batch": ms / steps, "batch": nb_}
-    return out
+    net.close()
+    return main, out
 
 
-def run_ours(args, rank, local_rank, world):
-    import torch
-    from cloud_server_b200.context import Context
-
-    dist_on = world > 1
-    torch.cuda.set_device(local_rank)
-    device = torch.device("cuda", local_rank)
-    if dist_on:
-        torch.distributed.init_process_group("nccl", device_id=device)
-    ctx = Context(local_rank)
-    peaks, peak_src = measured_peaks()
+def run_preprocess_bench(torch, ctx, args, rank, world, device, peaks, peak_src, dist_on):
+    """BASELINE configs[1] (C2): the whole preprocess half over n uploads of 1024x768x3 resident in HBM (9.66 GB at the
+    default n = 4096: far larger than L2) -- independent per picture, so under torchrun these are replicas, no collective."""
     traffic = traffic_table()
     n = args.batch
-
-    # ---- synthetic uploads, resident in HBM (9.66 GB at the default batch: far larger than L2)
     g = torch.Generator(device=device)
     g.manual_seed(1234 + rank)
     batch = torch.randint(0, 256, (n, H, W, C), dtype=torch.uint8, device=device, generator=g)
@@ -397,46 +505,31 @@ def run_ours(args, rank, local_rank, world):
     def step_pred():
         ctx.predict_chain(batch, channel_order="BGR", out=outs[2])
 
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    steps = args.steps
     cnt = [0]
-    ms = time_steps(torch, step, args.steps, args.warmup, dist_on, counter=lambda: ctx.launches, count_out=cnt)
-    launches = cnt[0]
-    # keep the same kernels running ~0.5 s more so the NVML sampler sees clocks under this load
-    t_end = time.perf_counter() + 0.5
-    while time.perf_counter() < t_end:
-        for _ in range(5):
-            step()
-        torch.cuda.synchronize()
-    sampler.stop()
+    ms = time_steps(torch, step, steps, args.warmup, dist_on, counter=lambda: ctx.launches, count_out=cnt)
     ms_max = max_over_ranks(torch, ms, dist_on, device)
-    value = world * n * args.steps / (ms_max * 1e-3)
-    # the opt-in single-pass kernel (both chains from one read of every upload), same step, for the record
+    value = world * n * steps / (ms_max * 1e-3)
     os.environ["NC_FUSED_CHAINS"] = "1"
-    ms_fused = time_steps(torch, step, args.steps, 3, dist_on) / args.steps
+    ms_fused = time_steps(torch, step, steps, 3, dist_on) / steps
     del os.environ["NC_FUSED_CHAINS"]
-    # each kernel alone, same inputs (per-launch duration for the rooflines)
-    ms_t = time_steps(torch, step_train, args.steps, 3, dist_on) / args.steps
-    ms_p = time_steps(torch, step_pred, args.steps, 3, dist_on) / args.steps
+    ms_t = time_steps(torch, step_train, steps, 3, dist_on) / steps
+    ms_p = time_steps(torch, step_pred, steps, 3, dist_on) / steps
     ach_t = ALG_BYTES_TRAIN_CHAIN * n / (ms_t * 1e-3) / 1e9
     ach_p = ALG_BYTES_PREDICT_CHAIN * n / (ms_p * 1e-3) / 1e9
     tr_t, tr_p = traffic.get("train_chain_rows_kernel"), traffic.get("predict_chain_mma_kernel")
     peak = peaks["hbm_gbs"]
-
-    line = {
-        "metric": "images/sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+    sub = {
+        "metric": "images/sec", "value": value, "unit": "images/s", "ms_per_step": ms_max / steps, "scaling": "weak", "dtype": "u8",
         "config": {"workload": WORKLOAD % n, "pictures_per_gpu": n, "parallelism": "replicas x%d (no collective)" % world,
                    "l2": "inputs (%.2f GB) larger than L2" % (n * H * W * C / 1e9)},
-        "gpu_launches": launches,
+        "gpu_launches": cnt[0],
         "roofline": {"bound": "hbm", "achieved": ach_p, "peak": peak, "unit": "GB/s", "frac": ach_p / peak,
                      "traffic": tr_p * n if tr_p else None, "kernel": "predict_chain_mma_kernel (dominant: %.0f%% of the step)"
                      % (100 * ms_p / (ms_p + ms_t)), "peak_source": peak_src + " (burst copy bandwidth)",
                      "algorithmic_bytes_per_launch": ALG_BYTES_PREDICT_CHAIN * n, "launch_ms": ms_p,
                      "note": "peak = copy bandwidth (half reads, half writes); this kernel only reads (99.7 %), and a "
-                             "read-only stream can pass the copy figure: frac > 1 is possible.  CUDA events: 82-85 % of the 8.18 TB/s "
-                             "pin rate (profiles/r01n_ncu_preprocess.md)"},
+                             "read-only stream can pass the copy figure: frac > 1 is possible"},
         "train_side_chain": {"value": world * n / (ms_t * 1e-3), "unit": "images/s", "launch_ms": ms_t,
                              "roofline": {"bound": "hbm", "achieved": ach_t, "peak": peak, "unit": "GB/s", "frac": ach_t / peak,
                                           "traffic": tr_t * n if tr_t else None, "kernel": "train_chain_rows_kernel",
@@ -448,11 +541,8 @@ def run_ours(args, rank, local_rank, world):
         "single_pass_opt_in": {"value": world * n / (ms_fused * 1e-3), "unit": "images/s", "ms_per_step": ms_fused,
                                "note": "NC_FUSED_CHAINS=1: one kernel, every upload read once (13% less HBM traffic); "
                                        "not the default because it is no faster"},
-        "clocks": sampler.summary(),
     }
-
-    # ---- e2e: pinned host uploads through the public API (chunked H2D overlapped with the kernels),
-    #      all three results read back to the host
+    # ---- e2e: pinned host uploads through the public API (chunked H2D overlapped with the kernels), all results read back
     n_e = min(n, args.e2e_batch)
     host = torch.empty((n_e, H, W, C), dtype=torch.uint8).pin_memory()
     host.copy_(batch[:n_e])
@@ -464,39 +554,84 @@ def run_ours(args, rank, local_rank, world):
         for hbuf, dbuf in zip(res_host, r):
             hbuf.copy_(dbuf, non_blocking=True)
 
-    ks = max(3, min(args.steps, 10))
+    ks = max(3, min(steps, 10))
     ms_e = max_over_ranks(torch, time_steps(torch, e2e_step, ks, 3, dist_on), dist_on, device)
     torch.cuda.synchronize()
     assert all(torch.equal(hb, db.cpu()) for hb, db in zip(res_host, outs_e))
 
-    # train-side chain alone, zero copy: the kernel bulk-copies only the source rows it needs over PCIe
     def e2e_train_only():
         ctx.resize_gray_norm(host, out_u8=outs_e[0], out_f32=outs_e[1])
         res_host[1].copy_(outs_e[1], non_blocking=True)
 
     ms_z = max_over_ranks(torch, time_steps(torch, e2e_train_only, ks, 3, dist_on), dist_on, device)
-    line["e2e"] = {
+    sub["e2e"] = {
         "value": world * n_e * ks / (ms_e * 1e-3), "unit": "images/s", "h2d_bytes_per_step": int(n_e * H * W * C),
         "d2h_bytes_per_step": int(n_e * (784 + 3136 + 3136)), "pictures_per_step": n_e,
         "mode": "pinned host batch -> 256-picture chunks, H2D on a copy stream overlapped with both kernels -> D2H of all outputs",
     }
-    line["train_side_chain"]["e2e"] = {
+    sub["train_side_chain"]["e2e"] = {
         "value": world * n_e * ks / (ms_z * 1e-3), "unit": "images/s", "h2d_bytes_per_step": int(n_e * 112 * W * C),
         "d2h_bytes_per_step": int(n_e * 3136), "mode": "zero copy: cp.async.bulk of the 112 needed rows straight from pinned host memory"}
-    del host
+    del host, batch
+    torch.cuda.empty_cache()
+    return sub
 
-    # ---- CNN train / predict sub-benchmarks (filled in when the net library is present)
-    line.update(run_net_bench(torch, ctx, args, rank, world, device, peaks, dist_on))
 
-    # ---- CPU baseline on this box's host cores (rank 0, N == 1 only), bounded sample
+def run_ours(args, rank, local_rank, world):
+    import torch
+    from cloud_server_b200.context import Context
+
+    dist_on = world > 1
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if dist_on:
+        torch.distributed.init_process_group("nccl", device_id=device)
+    ctx = Context(local_rank)
+    peaks, peak_src = measured_peaks()
+    sampler = ClockSampler(local_rank)
+
+    parity = dp_parity_check(torch, ctx, world, rank, device, args.math) if dist_on else None
+    main, subs = run_train_bench(torch, ctx, args, rank, world, device, peaks, dist_on, sampler)
+    local = GLOBAL_BATCH // world
+    line = {
+        "metric": "images/sec", "value": main["value"], "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "tf32", "data": "synthetic",
+        "config": {"workload": TRAIN_WORKLOAD % (GLOBAL_BATCH, world), "global_batch": GLOBAL_BATCH, "per_gpu_batch": local,
+                   "parallelism": "single device" if world == 1 else "dp%d: NCCL all-reduce (sum) of the 13.1 MB flat gradient buffer inside the step" % world,
+                   "l2": "inputs: the 60000-picture set (188 MB float32) is larger than L2 and every step takes a different batch"},
+        "gpu_launches": int(round(main["gpu_launches_per_step"] * args.steps)),
+        "roofline": main.get("roofline"), "e2e": main.get("e2e"), "clocks": sampler.summary(),
+    }
+    for k in ("step_roofline", "stages_ms", "cuda_graph", "ms_per_step_eager", "gradient_exchange", "math", "optimizer", "gpu_launches_per_step"):
+        line[k] = main.get(k)
+    if parity:
+        line["dp_parity"] = parity
+    line.update(subs)
+
+    # ---- C2: the preprocess half (sub-object with its own roofline / e2e / cpu_baseline)
+    if not args.no_preprocess:
+        line["preprocess"] = run_preprocess_bench(torch, ctx, args, rank, world, device, peaks, peak_src, dist_on)
+
+    # ---- CPU baselines on this box's host cores (rank 0, N == 1 only), bounded samples
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        v, done, dt = cpu_baseline_throughput(args.cpu_seconds, threads)
+        ksteps = 8
+        v, dt = cpu_train_step_throughput(GLOBAL_BATCH, ksteps, 1, threads)
         line["cpu_baseline"] = {
             "value": v, "unit": "images/s", "cores": threads, "kind": "port",
-            "sample": "16 distinct 1024x768x3 pictures per worker cycled for %.1f s (%d pictures); the reference's own cv2 / "
-                      "Pillow calls for both chains (preprocess.py:29,40; construct_inference.py:312-330) in memory, IPP off, "
-                      "one worker process per core" % (dt, done)}
+            "sample": "%d steps of the same LeNet step at batch %d in torch-CPU (oracle/torchref.py; TensorFlow 1.x is not "
+                      "installable here), %.1f s" % (ksteps, GLOBAL_BATCH, dt)}
+        if "preprocess" in line:
+            pv, done, pdt = cpu_baseline_throughput(args.cpu_seconds, threads)
+            line["preprocess"]["cpu_baseline"] = {
+                "value": pv, "unit": "images/s", "cores": threads, "kind": "port",
+                "sample": "16 distinct 1024x768x3 pictures per worker cycled for %.1f s (%d pictures); the reference's own cv2 / "
+                          "Pillow calls for both chains (preprocess.py:29,40; construct_inference.py:312-330) in memory, IPP off, "
+                          "one worker process per core" % (pdt, done)}
+            pv2, done2, pdt2 = cpu_baseline_throughput(min(args.cpu_seconds, 6.0), threads, ipp=True)
+            line["preprocess"]["cpu_baseline_ipp_on"] = {"value": pv2, "unit": "images/s", "cores": threads, "kind": "port",
+                                                         "sample": "same, cv2 with its default IPP arithmetic, %.1f s (%d pictures)" % (pdt2, done2)}
     if rank == 0:
         _emit(line)
     if dist_on:
@@ -507,13 +642,14 @@ def run_ours(args, rank, local_rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=4096, help="uploads per GPU (C2: 4096)")
     ap.add_argument("--e2e-batch", type=int, default=1024, help="uploads per e2e step (host pinned)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-preprocess", action="store_true", help="skip the C2 preprocess sub-benchmark")
     ap.add_argument("--dp", default="library", choices=["library", "torch"], help="who sums the gradients when N > 1")
     ap.add_argument("--no-graph", action="store_true", help="time the train step eagerly only (default: eager and CUDA-graph replay)")
     ap.add_argument("--math", type=int, default=3, help="CNN math: 0 fp32 SIMT, 1 tcgen05 3xTF32, 2 tcgen05 1xTF32, 3 (default) 3xTF32 forward + 1xTF32 gradients")

@@ -22,6 +22,10 @@ _SIGS = {
     "nc_destroy": (C.c_int, [C.c_void_p]),
     "nc_last_error": (C.c_char_p, [C.c_void_p]),
     "nc_launch_count": (C.c_int64, [C.c_void_p]),
+    "nc_jpeg_info": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "nc_jpeg_entropy_decode": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
+    "nc_jpeg_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_int,
+                                 C.POINTER(C.c_int64), C.c_void_p]),
     "nc_pp_resize_gray_norm": (C.c_int, [C.c_void_p, c_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int,
                                          c_u8p, c_f32p, C.c_void_p]),
     "nc_pp_resize_cubic": (C.c_int, [C.c_void_p, c_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, c_u8p, C.c_void_p]),

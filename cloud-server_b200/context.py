@@ -90,6 +90,35 @@ class Context:
         _lib.check(self.handle, rc)
         return out
 
+    # ---------------------------------------------------------------- JPEG decode (P1)
+    @staticmethod
+    def jpeg_info(data):
+        """(width, height, components, hsamp, vsamp) of a JPEG file's bytes -- header only, host side"""
+        buf = (C.c_ubyte * len(data)).from_buffer_copy(data)
+        v = [C.c_int() for _ in range(5)]
+        _lib.check(None, _lib.lib().nc_jpeg_info(buf, len(data), *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)
+
+    def decode_jpegs(self, files, channel_order="BGR", channels=3, host_threads=0, out=None):
+        """files: list of bytes objects (JPEG files of ONE width x height).  Returns a uint8 CUDA tensor
+        [N, H, W, channels] (channels 1: [N, H, W]) equal to cv2.imread (BGR) / PIL.Image.open (RGB) of each file
+        (apps/preprocess/preprocess.py:28, construct_distribute.py:446).  self.last_jpeg_h2d_bytes = bytes that crossed PCIe."""
+        n = len(files)
+        if n == 0:
+            return torch.empty((0, 0, 0, channels), dtype=torch.uint8, device=self.tdev)
+        w, h, _, _, _ = self.jpeg_info(files[0])
+        keep = [(C.c_ubyte * len(f)).from_buffer_copy(f) for f in files]
+        ptrs = (C.c_void_p * n)(*[C.addressof(k) for k in keep])
+        sizes = (C.c_size_t * n)(*[len(f) for f in files])
+        if out is None:
+            out = torch.empty((n, h, w, channels), dtype=torch.uint8, device=self.tdev)
+        moved = C.c_int64(0)
+        rc = _lib.lib().nc_jpeg_decode(self.handle, ptrs, sizes, n, w, h, channels, {"RGB": 0, "BGR": 1}[channel_order],
+                                       C.c_void_p(out.data_ptr()), h * w * channels, int(host_threads), C.byref(moved), self._stream())
+        _lib.check(self.handle, rc)
+        self.last_jpeg_h2d_bytes = int(moved.value)
+        return out[..., 0] if channels == 1 else out
+
     # ---------------------------------------------------------------- predict-side chain (P5)
     def predict_chain(self, src, channel_order="RGB", compat=False, want_small20=False, out=None, status=None):
         """src: uint8 CUDA tensor [N,H,W,3] or [N,H,W] ('L').  Returns (f32[N,784], status[N] int32

@@ -352,6 +352,263 @@ head_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dz, flo
 }
 
 // ---------------------------------------------------------------------------------------------
+// The same head for K <= 1024, laid out for latency: the batch is small (256 rows per GPU under data parallel training)
+// and the whole problem is a few MB, so what counts is the length of the dependent chain, not bytes.
+//   * a thread owns k = t, t + 256, t + 512, t + 768 for EVERY row its CTA handles: its 4 x N weights live in registers
+//     (staged once through shared memory with coalesced 16-byte loads), x loads and dx stores are coalesced, and the column
+//     sums of dx (the bias gradient of the dense layer below) are four private accumulators -- no cross-warp reduction;
+//   * R = 4 rows per pass: 4 x N partial logits per thread, warp shuffles, one shared-memory hop across the 8 warps, then
+//     softmax / loss / dz in 16-lane groups (lane = class) and dz broadcast through shared memory.
+// ---------------------------------------------------------------------------------------------
+template <int NMAX>
+__global__ void __launch_bounds__(256)
+head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                 const float* __restrict__ y, float* __restrict__ logits, float* __restrict__ dz, float* __restrict__ dx,
+                 int M, int N, int K, int loss_name, float grad_scale, int relu_mask, int round_dx,
+                 float* __restrict__ cs_partial, float* __restrict__ db_out, float* __restrict__ loss_partial,
+                 int* __restrict__ hit_partial, unsigned* counter, float* __restrict__ loss_out, int* __restrict__ correct_out) {
+    static_assert(NMAX == 16, "16-lane class groups");
+    constexpr int R = 4;
+    extern __shared__ __align__(16) float sw[];      // W[K][N] staging
+    __shared__ float s_part[8][R][NMAX];
+    __shared__ float s_dz[R][NMAX];
+    __shared__ float s_l[R];
+    __shared__ int s_h[R];
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    {
+        const int total = K * N, total4 = ((reinterpret_cast<uintptr_t>(w) & 15) == 0) ? total / 4 : 0;
+        const float4* w4 = reinterpret_cast<const float4*>(w);
+        float4* s4 = reinterpret_cast<float4*>(sw);
+        for (int i = t; i < total4; i += 256) s4[i] = __ldg(w4 + i);
+        for (int j = total4 * 4 + t; j < total; j += 256) sw[j] = __ldg(w + j);
+    }
+    __syncthreads();
+    float wq[4][NMAX];
+    bool own[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        own[i] = t + 256 * i < K;
+#pragma unroll
+        for (int n = 0; n < NMAX; ++n) wq[i][n] = (own[i] && n < N) ? sw[(t + 256 * i) * N + n] : 0.0f;
+    }
+    float cs[4] = {0.f, 0.f, 0.f, 0.f};
+    float lsum = 0.0f; int hits = 0;           // meaningful in lane 0 / 16 of warps 0 and 1
+    for (int m0 = blockIdx.x * R; m0 < M; m0 += gridDim.x * R) {
+        float xv[R][4];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                xv[r][i] = (own[i] && m0 + r < M) ? __ldg(x + (long long)(m0 + r) * K + t + 256 * i) : 0.0f;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n) {
+                if (n < N) {
+                    float v = fmaf(xv[r][3], wq[3][n], fmaf(xv[r][2], wq[2][n], fmaf(xv[r][1], wq[1][n], xv[r][0] * wq[0][n])));
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                    if (lane == 0) s_part[warp][r][n] = v;
+                }
+            }
+        }
+        __syncthreads();
+        if (warp < 2) {
+            // 16-lane group per row: lane n of the group is class n
+            const int r = warp * 2 + (lane >> 4), n = lane & 15, m = m0 + r;
+            const bool live = n < N && m < M;
+            float z = -INFINITY, yv = -INFINITY;
+            if (live) {
+                float v = 0.0f;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) v += s_part[q][r][n];
+                z = v + (bias ? __ldg(bias + n) : 0.0f);
+                yv = __ldg(y + (long long)m * N + n);
+            }
+            // first maximum wins (argmax semantics of tf.argmax): compare (value, -index)
+            float zm = z, ym = yv; int za = n, ya = n;
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+                const float oz = __shfl_xor_sync(0xffffffffu, zm, o), oy = __shfl_xor_sync(0xffffffffu, ym, o);
+                const int oza = __shfl_xor_sync(0xffffffffu, za, o), oya = __shfl_xor_sync(0xffffffffu, ya, o);
+                if (oz > zm || (oz == zm && oza < za)) { zm = oz; za = oza; }
+                if (oy > ym || (oy == ym && oya < ya)) { ym = oy; ya = oya; }
+            }
+            float l = 0.0f, d = 0.0f;
+            if (loss_name == 0) {
+                float e = live ? expf(z - zm) : 0.0f, se = e;
+#pragma unroll
+                for (int o = 8; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+                const float lse = zm + logf(se);
+                if (live) {
+                    const float logp = z - lse;
+                    l = -yv * logp;
+                    d = (expf(logp) - yv) * grad_scale / (float)M;
+                }
+            } else if (live) {
+                const float e = z - yv;
+                l = e * e / (float)N;
+                d = 2.0f * e * grad_scale / ((float)M * (float)N);
+            }
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+            if (live) {
+                s_dz[r][n] = d;
+                logits[(long long)m * N + n] = z;
+                if (dz) dz[(long long)m * N + n] = d;
+            }
+            if (n == 0 && m < M) { lsum += l; hits += (za == ya); }
+        }
+        __syncthreads();
+        if (dx) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (m0 + r < M) {
+                    float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int n = 0; n < NMAX; ++n) {
+                        if (n < N) {
+                            const float d = s_dz[r][n];
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) o[i] = fmaf(d, wq[i][n], o[i]);
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        if (own[i]) {
+                            float v = o[i];
+                            if (relu_mask && !(xv[r][i] > 0.0f)) v = 0.0f;
+                            if (round_dx) v = rn_tf32(v);
+                            dx[(long long)(m0 + r) * K + t + 256 * i] = v;
+                            cs[i] += v;
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    if (warp < 2 && (lane & 15) == 0) { s_l[warp * 2 + (lane >> 4)] = lsum; s_h[warp * 2 + (lane >> 4)] = hits; }
+    if (cs_partial) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if (own[i]) cs_partial[(long long)blockIdx.x * K + t + 256 * i] = cs[i];
+    }
+    __syncthreads();
+    if (t == 0) {
+        float a = 0.0f; int hh = 0;
+        for (int i = 0; i < R; ++i) { a += s_l[i]; hh += s_h[i]; }
+        loss_partial[blockIdx.x] = a; hit_partial[blockIdx.x] = hh;
+    }
+    if (!last_block_arrives(counter, gridDim.x)) return;
+    const int G = gridDim.x;
+    if (warp == 0) {
+        float a = 0.0f; int hh = 0;
+        for (int b = lane; b < G; b += 32) { a += __ldcg(loss_partial + b); hh += __ldcg(hit_partial + b); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); hh += __shfl_xor_sync(0xffffffffu, hh, o); }
+        if (lane == 0) {
+            if (loss_out) *loss_out = a / (float)M;
+            if (correct_out) *correct_out = hh;
+        }
+    }
+    if (cs_partial && db_out) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (!own[i]) continue;
+            const int kk = t + 256 * i;
+            float a = 0.0f;
+            int b = 0;
+            for (; b + 7 < G; b += 8) {                // eight independent L2 loads in flight, summed in CTA order
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = __ldcg(cs_partial + (long long)(b + u) * K + kk);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) a += v[u];
+            }
+            for (; b < G; ++b) a += __ldcg(cs_partial + (long long)b * K + kk);
+            db_out[kk] = a;
+        }
+    }
+}
+
+// dW[K][N] = x^T . dz and db[N] without slice partials for small batches: a CTA owns 32 consecutive k and (a slice of) the
+// batch; lane = k, warp = row lane (32 of them: 1024 threads), dz rows are warp-uniform broadcast loads; the 32 row lanes are
+// summed through shared memory in warp order.  gridDim.y > 1 (large batches): slices summed by the last CTA of the k block.
+template <int NMAX>
+__global__ void __launch_bounds__(1024)
+head_wgrad_rows_kernel(const float* __restrict__ x, const float* __restrict__ dz, float* __restrict__ partial, float* __restrict__ dW,
+                       float* __restrict__ db, int M, int N, int K, int rows_per_slice, unsigned* counters) {
+    extern __shared__ float sred[];                   // [32 warps][32 k][N]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k = blockIdx.x * 32 + lane;
+    const int m0 = blockIdx.y * rows_per_slice, m1 = min(M, m0 + rows_per_slice);
+    float acc[NMAX];
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n) acc[n] = 0.0f;
+    if (k < K) {
+        int m = m0 + warp;
+        for (; m + 96 < m1; m += 128) {               // four independent x loads in flight per thread
+            float xv[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) xv[u] = __ldg(x + (long long)(m + 32 * u) * K + k);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float* dr = dz + (long long)(m + 32 * u) * N;
+#pragma unroll
+                for (int n = 0; n < NMAX; ++n)
+                    if (n < N) acc[n] = fmaf(xv[u], __ldg(dr + n), acc[n]);
+            }
+        }
+        for (; m < m1; m += 32) {
+            const float xv = __ldg(x + (long long)m * K + k);
+            const float* dr = dz + (long long)m * N;
+#pragma unroll
+            for (int n = 0; n < NMAX; ++n)
+                if (n < N) acc[n] = fmaf(xv, __ldg(dr + n), acc[n]);
+        }
+    }
+#pragma unroll
+    for (int n = 0; n < NMAX; ++n)
+        if (n < N) sred[(warp * 32 + lane) * N + n] = acc[n];
+    __syncthreads();
+    const int S = gridDim.y;
+    float* out = S > 1 ? partial + (long long)blockIdx.y * K * N : dW;
+    if ((int)threadIdx.x < 32 * N) {
+        const int kl = threadIdx.x / N, n = threadIdx.x - kl * N;
+        float v = 0.0f;
+#pragma unroll 8
+        for (int q = 0; q < 32; ++q) v += sred[(q * 32 + kl) * N + n];
+        if (blockIdx.x * 32 + kl < K) out[(long long)(blockIdx.x * 32 + kl) * N + n] = v;
+    }
+    if (S > 1) {
+        if (!last_block_arrives(counters + blockIdx.x, S)) return;
+        if ((int)threadIdx.x < 32 * N) {
+            const int kl = threadIdx.x / N, n = threadIdx.x - kl * N;
+            if (blockIdx.x * 32 + kl < K) {
+                float v = 0.0f;
+                for (int s = 0; s < S; ++s) v += __ldcg(partial + ((long long)s * K + blockIdx.x * 32 + kl) * N + n);
+                dW[(long long)(blockIdx.x * 32 + kl) * N + n] = v;
+            }
+        }
+    }
+    if (blockIdx.x == 0 && db) {
+        // column sums of dz over the WHOLE batch (every slice CTA of k block 0 that gets here computes the same bytes)
+        __syncthreads();
+        const int n = threadIdx.x & 15, r0 = threadIdx.x >> 4;           // 64 row lanes x 16 columns
+        float v = 0.0f;
+        if (n < N)
+            for (int m = r0; m < M; m += 64) v += __ldg(dz + (long long)m * N + n);
+        sred[r0 * 16 + n] = v;
+        __syncthreads();
+        if ((int)threadIdx.x < N) {
+            float u = 0.0f;
+            for (int r = 0; r < 64; ++r) u += sred[r * 16 + threadIdx.x];
+            db[threadIdx.x] = u;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // per-channel sums of what a vec4 elementwise kernel wrote: thread t only ever touches channel group t % c4n (the host
 // checks 256 % c4n == 0, which also makes the grid stride a multiple of c4n), so one float4 per thread accumulates them.
 // CTA partial -> partial[cta][C]; the last CTA sums the CTAs in order.
@@ -372,12 +629,12 @@ __device__ __forceinline__ void channel_sums_finish(float4 cs, int c4n, float* _
     const int g = threadIdx.x % c4n, r = threadIdx.x / c4n, R = 256 / c4n, G = gridDim.x;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     int b = r;
-    for (; b + 3 * R < G; b += 4 * R) {
-        float4 v[4];
+    for (; b + 7 * R < G; b += 8 * R) {                 // eight independent L2 loads in flight
+        float4 v[8];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = __ldcg(reinterpret_cast<const float4*>(partial + (long long)(b + u * R) * C) + g);
+        for (int u = 0; u < 8; ++u) v[u] = __ldcg(reinterpret_cast<const float4*>(partial + (long long)(b + u * R) * C) + g);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+        for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
     }
     for (; b < G; b += R) {
         const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (long long)b * C) + g);

@@ -309,8 +309,11 @@ size_t nc_tc_gemm_workspace(int sm_count, int M, int N, int K, int* splits_out, 
     const long long tiles = (long long)((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     const int nkb = (K + BK - 1) / BK;
     int splits = 1;
-    if (tiles < sm_count && nkb >= 8) {
-        splits = (int)((sm_count + tiles - 1) / tiles);
+    // narrow outputs (N <= 64: the convolution kernels, two CTAs per SM) aim at two CTAs per SM; wide ones split only when
+    // the tiles leave more than half of the SMs idle (at 128 tiles a 2-way split costs a second wave and a reduce pass)
+    const long long target = N <= 64 ? 2LL * sm_count : sm_count;
+    if ((N <= 64 ? tiles < target : 2 * tiles <= target) && nkb >= 8) {
+        splits = (int)((target + tiles - 1) / tiles);
         if (splits > nkb / 4) splits = nkb / 4;
         if (splits < 1) splits = 1;
     }

@@ -149,6 +149,7 @@ struct nc_net {
     float* params_hi = nullptr;
     // fused glue: ticket counters of the "last CTA sums" kernels (zero between launches), per-CTA loss / hit partials
     unsigned* counters = nullptr; float* red_f = nullptr; int* red_i = nullptr;
+    cudaStream_t aux_stream = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool head_fused = false;    // output layer + loss + its gradients run as head_fwd_bwd_kernel / head_wgrad_kernel
     // per-stage CUDA-event timing of one step (nc_net_profile): names[i] covers events[i] .. events[i + 1]
     bool prof_on = false; std::vector<std::string> prof_names; std::vector<cudaEvent_t> prof_events; size_t prof_used = 0;
@@ -374,6 +375,9 @@ static void free_net(nc_net* net) {
     if (net->ev_tail_ready) cudaEventDestroy(net->ev_tail_ready);
     if (net->ev_tail_done) cudaEventDestroy(net->ev_tail_done);
     if (net->ev_head_ready) cudaEventDestroy(net->ev_head_ready);
+    if (net->aux_stream) cudaStreamDestroy(net->aux_stream);
+    if (net->ev_fork) cudaEventDestroy(net->ev_fork);
+    if (net->ev_join) cudaEventDestroy(net->ev_join);
     cudaFree(net->dp_buf);
     cudaFree(net->params_hi); cudaFree(net->counters); cudaFree(net->red_f); cudaFree(net->red_i);
     for (cudaEvent_t e : net->prof_events) cudaEventDestroy(e);
@@ -885,9 +889,17 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
     const bool round_bwd = net->math == 3;
     if (round_bwd) {
         if (!net->params_hi) NET_CUDA(net, cudaMalloc(&net->params_hi, (size_t)net->nparams * sizeof(float)));
-        PROF(net, st, "split weights (hi = rn_tf32)");
-        split_params_kernel<<<grid_for(net->nparams / 4 + 1, sms), 256, 0, st>>>(net->params, net->params_hi, nullptr, net->nparams);
+        // on a side stream, next to the forward pass: the copy is first read by the first input-gradient GEMM
+        if (!net->aux_stream) {
+            NET_CUDA(net, cudaStreamCreateWithFlags(&net->aux_stream, cudaStreamNonBlocking));
+            NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_fork, cudaEventDisableTiming));
+            NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_join, cudaEventDisableTiming));
+        }
+        NET_CUDA(net, cudaEventRecord(net->ev_fork, st));
+        NET_CUDA(net, cudaStreamWaitEvent(net->aux_stream, net->ev_fork, 0));
+        split_params_kernel<<<grid_for(net->nparams / 4 + 1, sms), 256, 0, net->aux_stream>>>(net->params, net->params_hi, nullptr, net->nparams);
         NET_LAUNCH(net);
+        NET_CUDA(net, cudaEventRecord(net->ev_join, net->aux_stream));
     }
     rc = forward_impl(net, x, n, st, true);
     if (rc != NC_OK) return rc;
@@ -910,7 +922,8 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         float* dz = dn;          // [M][N], consumed by head_wgrad_kernel right behind
         bool cs = false;
         if (below >= 0 && net->layers[below].kind == L_CONNECT && net->layers[below].b_off >= 0 && K <= 1024 && net->layers[below].oc == K) cs = true;
-        const int G = (M + 7) / 8 < 2 * sms ? (M + 7) / 8 : 2 * sms;
+        const int G = (M + 7) / 8 < 2 * sms ? (M + 7) / 8 : 2 * sms;                 // CTAs of the shared-memory variant
+        const int Gmax = (M + 3) / 4 < 2 * sms ? (M + 3) / 4 : 2 * sms;           // CTAs of the register variant (>= G)
         int slices = (sms * 2 + (K + 255) / 256 - 1) / ((K + 255) / 256);          // K blocks x batch slices of the weight gradient
         if (slices > (M + 15) / 16) slices = (M + 15) / 16;
         if (slices < 1) slices = 1;
@@ -920,7 +933,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         if ((K + 255) / 256 > 512) return net_err(net, NC_EUNSUPPORTED, "output layer with %d inputs", K);
         {
             // one workspace, used by the two launches one after the other: the head's column sums, then the slice partials
-            const size_t a = cs ? (size_t)G * K * sizeof(float) : 0, b = (size_t)slices * K * N * sizeof(float);
+            const size_t a = cs ? (size_t)Gmax * K * sizeof(float) : 0, b = (size_t)slices * K * N * sizeof(float);
             rc = reserve_ws(net, a > b ? a : b);
             if (rc != NC_OK) return rc;
         }
@@ -935,14 +948,33 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                                       loss_name, grad_scale, relu_mask, round_bwd ? 1 : 0, net->ws, dbp, net->red_f, net->red_i,   \
                                       net->counters, loss_out, (int*)correct_out);                                          \
         } while (0)
-        if (N <= 16) { if (cs) NC_HEAD(16, true); else NC_HEAD(16, false); }
+        // small K (the usual dense hidden layer in front): the register-resident variant, four rows per CTA pass
+        const bool rows_variant = N <= 16 && K <= 1024 && (size_t)K * N * sizeof(float) <= 48 * 1024 && !getenv("NC_HEAD_SMEM");
+        if (rows_variant) {
+            const int Gr = (M + 3) / 4 < 2 * sms ? (M + 3) / 4 : 2 * sms;          // <= G of the reservation above
+            head_rows_kernel<16><<<Gr, 256, (size_t)K * N * sizeof(float), st>>>(in, net->params + O.w_off, net->params + O.b_off, y_onehot, act_ptr(net, O), dz, dx, M, N, K,
+                                                      loss_name, grad_scale, relu_mask, round_bwd ? 1 : 0, cs ? net->ws : nullptr, dbp,
+                                                      net->red_f, net->red_i, net->counters, loss_out, (int*)correct_out);
+        }
+        else if (N <= 16) { if (cs) NC_HEAD(16, true); else NC_HEAD(16, false); }
         else { if (cs) NC_HEAD(32, true); else NC_HEAD(32, false); }
 #undef NC_HEAD
         NET_LAUNCH(net);
         if (cs) bias_done = below;
-        {
+        PROF(net, st, "head: output layer wgrad + bias grad");
+        if (N <= 16 && (size_t)32 * 32 * N * sizeof(float) <= 48 * 1024 && !getenv("NC_HEAD_SMEM")) {
+            // a CTA per 32 k, 32 row lanes; large batches are cut into a few slices summed by the last CTA of the k block
+            int ms = M >= 1024 ? (M + 511) / 512 : 1;
+            if (ms > 8) ms = 8;
+            const int rps2 = ((M + ms - 1) / ms + 31) / 32 * 32;
+            ms = (M + rps2 - 1) / rps2;
+            if (ms > 1) { rc = reserve_ws(net, (size_t)ms * K * N * sizeof(float)); if (rc != NC_OK) return rc; }
+            dim3 grid((K + 31) / 32, ms);
+            head_wgrad_rows_kernel<16><<<grid, 1024, (size_t)32 * 32 * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off,
+                                                                                                 M, N, K, rps2, net->counters + 16);
+            NET_LAUNCH(net);
+        } else {
             dim3 grid((K + 255) / 256, slices);
-            PROF(net, st, "head: output layer wgrad + bias grad");
             if (N <= 16) head_wgrad_kernel<16><<<grid, 256, (size_t)rps * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off, M, N, K, rps, net->counters + 16);
             else head_wgrad_kernel<32><<<grid, 256, (size_t)rps * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off, M, N, K, rps, net->counters + 16);
             NET_LAUNCH(net);
@@ -953,11 +985,12 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         loss_kernel<<<1, 1024, 0, st>>>(act_ptr(net, net->layers.back()), y_onehot, d, n, net->classes, loss_name, grad_scale, loss_out, (int*)correct_out);
         NET_LAUNCH(net);
     }
+    if (round_bwd) NET_CUDA(net, cudaStreamWaitEvent(st, net->ev_join, 0));      // params_hi is ready
     bool skip_fused_relu = false;
     const float* first_relu_y = nullptr;
     for (int li = start; li >= 0; --li) {
         Layer& L = net->layers[li];
-        if (net->prof_on) PROF(net, st, stage_name("bwd", li, L).c_str());
+        if (net->prof_on) PROF(net, st, (stage_name("bwd", li, L) + ((L.kind == L_CONV || L.kind == L_CONNECT) ? " wgrad" : "")).c_str());
         if (L.kind == L_ACT && L.relu_into_pool && skip_fused_relu) { skip_fused_relu = false; continue; }   // done inside the pool backward
         // the input of a layer that follows a fused relu is that relu's (never materialised) output: pool kernels take the pre-activation
         const float* in = li == 0 ? x : act_ptr(net, net->layers[li - 1]);
@@ -1030,6 +1063,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             if (rc != NC_OK) return rc;
             if (li != bias_done) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
             if (need_dx) {   // dX[M][K] = dY[M][N] * W^T[N][K]   (W[in][out] is already the K-major B operand)
+                if (net->prof_on) PROF(net, st, (stage_name("bwd", li, L) + " dgrad").c_str());
                 rc = tc_try(net, d, round_bwd ? net->params_hi + L.w_off : W, dn, nullptr, M, K, N, false, false, st, &done, true);
                 if (rc != NC_OK) return rc;
                 if (!done) rc = run_gemm<true, false>(net, M, K, N, RowMajor{d, N}, ColMajor{W, N}, dn, nullptr, st);
@@ -1093,6 +1127,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             if (rc != NC_OK) return rc;
             if (dB && !bias_done_here && li != bias_done) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
             if (need_dx) {
+                if (net->prof_on) PROF(net, st, (stage_name("bwd", li, L) + " dgrad").c_str());
                 const int Mi = n * L.ih * L.iw, Ki = L.fh * L.fw * L.oc;
                 rc = tc_conv_try(net, 1, L, n, d, round_bwd ? net->params_hi + L.w_off : W, dn, nullptr, st, &done);
                 if (rc != NC_OK) return rc;
@@ -1118,7 +1153,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                     const bool want_cs = tgt >= 0 && net->layers[tgt].kind == L_CONV && net->layers[tgt].b_off >= 0 && net->layers[tgt].oc == L.ic &&
                                          !(net->fuse_first && tgt == 0) && ((net->layers[tgt].b_off & 3) == 0);
                     int blocks = grid_for(total_out / 4, sms);
-                    if (want_cs && blocks > 4 * sms) blocks = 4 * sms;            // the last CTA sums one partial row per CTA
+                    if (want_cs && blocks > (total_out / 4 > (1 << 20) ? 6 : 2) * sms) blocks = (total_out / 4 > (1 << 20) ? 6 : 2) * sms;   // the last CTA sums one partial row per CTA
                     if (want_cs) { rc = reserve_ws(net, (size_t)blocks * L.ic * sizeof(float)); if (rc != NC_OK) return rc; }
                     maxpool_bwd_tiled_vec4_cs_kernel<<<blocks, 256, 0, st>>>(d, argp, dn, pgeom(L), total_out / 4, fused ? out : nullptr,
                                                                               round_bwd ? 1 : 0, want_cs ? net->ws : nullptr,
@@ -1145,7 +1180,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                     const bool want_cs = (B.kind == L_CONV || B.kind == L_CONNECT) && B.b_off >= 0 && B.oc == C && (B.b_off & 3) == 0 &&
                                          !(net->fuse_first && li - 1 == 0) && !(li - 1 == 0 && B.kind == L_CONV && B.ic <= 4 && B.fh * B.fw * B.ic <= 32);
                     int blocks = grid_for(total / 4, sms);
-                    if (want_cs && blocks > 4 * sms) blocks = 4 * sms;
+                    if (want_cs && blocks > (total / 4 > (1 << 20) ? 6 : 2) * sms) blocks = (total / 4 > (1 << 20) ? 6 : 2) * sms;
                     if (want_cs) { rc = reserve_ws(net, (size_t)blocks * C * sizeof(float)); if (rc != NC_OK) return rc; }
                     act_bwd_vec4_cs_kernel<<<blocks, 256, 0, st>>>(xin, out, d, dn, total / 4, c4n, L.act, L.slope, round_bwd ? 1 : 0,
                                                                     want_cs ? net->ws : nullptr, want_cs ? net->grads + B.b_off : nullptr, net->counters + 8);

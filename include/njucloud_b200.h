@@ -51,6 +51,29 @@ const char* nc_last_error(nc_ctx* ctx);
 /* number of kernels this ctx has launched so far (bench.py's gpu_launches) */
 int64_t nc_launch_count(nc_ctx* ctx);
 
+/* ---- P1: JPEG decode ---------------------------------------------------------------------
+ * Replaces cv2.imread(dir) (apps/preprocess/preprocess.py:28, :40 -- BGR) and PIL.Image.open
+ * (apps/construction/util/construct_distribute.py:446, construct_inference.py:312 -- RGB / L) for baseline
+ * (sequential Huffman, 8-bit, 1 or 3 components, chroma 4:4:4 / 4:2:2 / 4:2:0) files, bit for bit with the
+ * libjpeg-turbo both wheels embed: "islow" integer IDCT, "fancy" triangle chroma upsampling, fixed-point
+ * YCbCr -> RGB.  Progressive / arithmetic files: NC_EUNSUPPORTED (decode those on the host).
+ *   nc_jpeg_info    header only (host): width, height, components, chroma subsampling factors (1 or 2).
+ *   nc_jpeg_decode  count pictures of the SAME width x height: host_jpegs[i] / sizes[i] are the files' bytes in host
+ *                   memory.  Huffman decoding runs on the host (host_threads threads, <= 0: all cores); the
+ *                   nonzero coefficients cross PCIe (*h2d_bytes, nullable, reports how many bytes did) and
+ *                   dequantisation, IDCT, upsampling and colour conversion run on the device.
+ *                   out[i] (device) = uint8 [height][width][out_channels]; out_channels 3: channel_order 0 = RGB
+ *                   (PIL), 1 = BGR (cv2; a gray file is replicated as cv2.imread(dir) does); out_channels 1: the
+ *                   luma plane (what both libraries return for a single-component file).
+ *                   Synchronises `stream` once (the pinned staging buffer of the previous call). */
+int nc_jpeg_info(const uint8_t* host_jpeg, size_t size, int* width, int* height, int* components, int* hsamp, int* vsamp);
+/* Host only: the Huffman stage of nc_jpeg_decode alone, expanded to dense quantised coefficients coefs[block][64]
+ * (natural order; component planes back to back, blocks row-major, MCU padded).  coefs NULL: *nblocks only. */
+int nc_jpeg_entropy_decode(const uint8_t* host_jpeg, size_t size, int16_t* coefs, int64_t capacity_blocks, int64_t* nblocks);
+int nc_jpeg_decode(nc_ctx* ctx, const uint8_t* const* host_jpegs, const size_t* sizes, int count, int width, int height,
+                   int out_channels, int channel_order, uint8_t* out, int64_t img_stride, int host_threads,
+                   int64_t* h2d_bytes, void* stream);
+
 /* ---- P2+P3+P4: train-side preprocess chain ---------------------------------------------
  * Replaces, fused and batched, for n decoded uploads src[n][h][w][c] (uint8, c == 3 BGR as
  * cv2.imread returns it, or c == 1):
