@@ -38,6 +38,7 @@ _SIGS = {
     "nc_pp_op": (C.c_int, [C.c_void_p, C.c_int, c_u8p, c_u8p, C.c_int, C.c_double, C.c_double, C.c_int,
                            C.c_void_p, C.c_int64, C.c_void_p]),
     "nc_pp_cubic_table": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p]),
+    "nc_pp_cubic_table_f32": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p]),
     "nc_pp_pil_table": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "nc_pp_gaussian_q8": (C.c_int, [C.c_int, C.c_void_p]),
     "nc_crc32c": (C.c_uint32, [C.c_void_p, C.c_size_t, C.c_uint32]),

@@ -43,13 +43,15 @@ class Context:
         return int(_lib.lib().nc_launch_count(self.handle))
 
     # ---------------------------------------------------------------- train-side chain (P2-P4)
-    def resize_gray_norm(self, src, out_u8=None, out_f32=None, want_u8=True, want_f32=True):
+    def resize_gray_norm(self, src, out_u8=None, out_f32=None, want_u8=True, want_f32=True, mode=0):
         """src: uint8 tensor [N,H,W,3] (BGR, as cv2.imread) or [N,H,W] / [N,H,W,1].
 
         CUDA tensor -> nc_pp_resize_gray_norm; CPU tensor (pinned or not) ->
         nc_pp_resize_gray_norm_host.  Returns (u8[N,28,28] | None, f32[N,784] | None) on device.
         Stands in for preprocess.resize + imread(,0) + DataSet normalise
-        (apps/preprocess/preprocess.py:28-30,40; construct_distribute.py:503-504)."""
+        (apps/preprocess/preprocess.py:28-30,40; construct_distribute.py:503-504).
+        mode 0: OpenCV's own resize arithmetic (cv2 with IPP disabled; bit exact), mode 1: the arithmetic of the wheel's
+        default (Intel IPP) as a float model (>= 99.9 % of the outputs equal)."""
         if src.dtype != torch.uint8:
             raise ValueError("src must be uint8")
         if src.dim() == 3:
@@ -68,16 +70,16 @@ class Context:
         p_f32 = C.c_void_p(out_f32.data_ptr()) if out_f32 is not None else None
         L = _lib.lib()
         if src.is_cuda:
-            rc = L.nc_pp_resize_gray_norm(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, stride, 0,
+            rc = L.nc_pp_resize_gray_norm(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, stride, int(mode),
                                           p_u8, p_f32, self._stream())
         else:
             staged = C.c_int(0)
-            rc = L.nc_pp_resize_gray_norm_host(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, stride, 0,
+            rc = L.nc_pp_resize_gray_norm_host(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, stride, int(mode),
                                                p_u8, p_f32, C.byref(staged), self._stream())
         _lib.check(self.handle, rc)
         return out_u8, out_f32
 
-    def resize_cubic(self, src):
+    def resize_cubic(self, src, mode=0):
         """uint8 CUDA [N,H,W,C] -> uint8 [N,28,28,C]: cv2.resize(.., (28,28), INTER_CUBIC) alone
         (what preprocess.resize writes back, apps/preprocess/preprocess.py:29-30)."""
         if src.dtype != torch.uint8 or not src.is_cuda or src.dim() != 4:
@@ -85,7 +87,7 @@ class Context:
         n, h, w, c = src.shape
         src = src.contiguous()
         out = torch.empty((n, 28, 28, c), dtype=torch.uint8, device=self.tdev)
-        rc = _lib.lib().nc_pp_resize_cubic(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, h * w * c, 0,
+        rc = _lib.lib().nc_pp_resize_cubic(self.handle, C.c_void_p(src.data_ptr()), n, h, w, c, h * w * c, int(mode),
                                            C.c_void_p(out.data_ptr()), self._stream())
         _lib.check(self.handle, rc)
         return out

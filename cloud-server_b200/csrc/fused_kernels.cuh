@@ -360,15 +360,17 @@ head_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dz, flo
 //   * R = 4 rows per pass: 4 x N partial logits per thread, warp shuffles, one shared-memory hop across the 8 warps, then
 //     softmax / loss / dz in 16-lane groups (lane = class) and dz broadcast through shared memory.
 // ---------------------------------------------------------------------------------------------
-template <int NMAX>
+// R rows per pass (1 for small batches: more CTAs, a shorter dependent stream per warp); N is a compile-time constant
+// (10 classes, construct_distribute.py:261-264) so that the class loops carry no predicates.
+template <int R, int N>
 __global__ void __launch_bounds__(256)
 head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                  const float* __restrict__ y, float* __restrict__ logits, float* __restrict__ dz, float* __restrict__ dx,
-                 int M, int N, int K, int loss_name, float grad_scale, int relu_mask, int round_dx,
+                 int M, int K, int loss_name, float grad_scale, int relu_mask, int round_dx,
                  float* __restrict__ cs_partial, float* __restrict__ db_out, float* __restrict__ loss_partial,
                  int* __restrict__ hit_partial, unsigned* counter, float* __restrict__ loss_out, int* __restrict__ correct_out) {
-    static_assert(NMAX == 16, "16-lane class groups");
-    constexpr int R = 4;
+    constexpr int NMAX = 16;
+    static_assert(N <= NMAX && R <= 4, "16-lane class groups, at most four rows per pass");
     extern __shared__ __align__(16) float sw[];      // W[K][N] staging
     __shared__ float s_part[8][R][NMAX];
     __shared__ float s_dz[R][NMAX];
@@ -383,13 +385,13 @@ head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const
         for (int j = total4 * 4 + t; j < total; j += 256) sw[j] = __ldg(w + j);
     }
     __syncthreads();
-    float wq[4][NMAX];
+    float wq[4][N];
     bool own[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         own[i] = t + 256 * i < K;
 #pragma unroll
-        for (int n = 0; n < NMAX; ++n) wq[i][n] = (own[i] && n < N) ? sw[(t + 256 * i) * N + n] : 0.0f;
+        for (int n = 0; n < N; ++n) wq[i][n] = own[i] ? sw[(t + 256 * i) * N + n] : 0.0f;
     }
     float cs[4] = {0.f, 0.f, 0.f, 0.f};
     float lsum = 0.0f; int hits = 0;           // meaningful in lane 0 / 16 of warps 0 and 1
@@ -403,20 +405,18 @@ head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const
 #pragma unroll
         for (int r = 0; r < R; ++r) {
 #pragma unroll
-            for (int n = 0; n < NMAX; ++n) {
-                if (n < N) {
-                    float v = fmaf(xv[r][3], wq[3][n], fmaf(xv[r][2], wq[2][n], fmaf(xv[r][1], wq[1][n], xv[r][0] * wq[0][n])));
+            for (int n = 0; n < N; ++n) {
+                float v = fmaf(xv[r][3], wq[3][n], fmaf(xv[r][2], wq[2][n], fmaf(xv[r][1], wq[1][n], xv[r][0] * wq[0][n])));
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                    if (lane == 0) s_part[warp][r][n] = v;
-                }
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) s_part[warp][r][n] = v;
             }
         }
         __syncthreads();
         if (warp < 2) {
             // 16-lane group per row: lane n of the group is class n
             const int r = warp * 2 + (lane >> 4), n = lane & 15, m = m0 + r;
-            const bool live = n < N && m < M;
+            const bool live = n < N && r < R && m < M;
             float z = -INFINITY, yv = -INFINITY;
             if (live) {
                 float v = 0.0f;
@@ -457,7 +457,7 @@ head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const
                 logits[(long long)m * N + n] = z;
                 if (dz) dz[(long long)m * N + n] = d;
             }
-            if (n == 0 && m < M) { lsum += l; hits += (za == ya); }
+            if (n == 0 && r < R && m < M) { lsum += l; hits += (za == ya); }
         }
         __syncthreads();
         if (dx) {
@@ -466,12 +466,10 @@ head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const
                 if (m0 + r < M) {
                     float o[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                    for (int n = 0; n < NMAX; ++n) {
-                        if (n < N) {
-                            const float d = s_dz[r][n];
+                    for (int n = 0; n < N; ++n) {
+                        const float d = s_dz[r][n];
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) o[i] = fmaf(d, wq[i][n], o[i]);
-                        }
+                        for (int i = 0; i < 4; ++i) o[i] = fmaf(d, wq[i][n], o[i]);
                     }
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
@@ -488,7 +486,7 @@ head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const
         }
         __syncthreads();
     }
-    if (warp < 2 && (lane & 15) == 0) { s_l[warp * 2 + (lane >> 4)] = lsum; s_h[warp * 2 + (lane >> 4)] = hits; }
+    if (warp < 2 && (lane & 15) == 0 && warp * 2 + (lane >> 4) < R) { s_l[warp * 2 + (lane >> 4)] = lsum; s_h[warp * 2 + (lane >> 4)] = hits; }
     if (cs_partial) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) if (own[i]) cs_partial[(long long)blockIdx.x * K + t + 256 * i] = cs[i];

@@ -70,6 +70,11 @@ struct CvCubicAxis {      // OpenCV INTER_CUBIC, one axis, dst == 28
     short coef[28][4];    // round(c * 2048)
 };
 void nc_cv_cubic_axis(int src, int dst, CvCubicAxis* out);
+struct IppCubicAxis {     // the same resize in the IPP arithmetic of the wheel's default: float32 coefficients
+    int ofs[28][4];
+    float coef[28][4];
+};
+void nc_ipp_cubic_axis(int src, int dst, IppCubicAxis* out);
 
 struct PilAxisHost {      // Pillow BICUBIC antialias tables for one axis
     int out_size = 0, ksize = 0;

@@ -923,7 +923,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         bool cs = false;
         if (below >= 0 && net->layers[below].kind == L_CONNECT && net->layers[below].b_off >= 0 && K <= 1024 && net->layers[below].oc == K) cs = true;
         const int G = (M + 7) / 8 < 2 * sms ? (M + 7) / 8 : 2 * sms;                 // CTAs of the shared-memory variant
-        const int Gmax = (M + 3) / 4 < 2 * sms ? (M + 3) / 4 : 2 * sms;           // CTAs of the register variant (>= G)
+        const int Gmax = M < 4 * sms ? M : 4 * sms;                               // CTAs of the register variant (>= G)
         int slices = (sms * 2 + (K + 255) / 256 - 1) / ((K + 255) / 256);          // K blocks x batch slices of the weight gradient
         if (slices > (M + 15) / 16) slices = (M + 15) / 16;
         if (slices < 1) slices = 1;
@@ -949,12 +949,19 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                                       net->counters, loss_out, (int*)correct_out);                                          \
         } while (0)
         // small K (the usual dense hidden layer in front): the register-resident variant, four rows per CTA pass
-        const bool rows_variant = N <= 16 && K <= 1024 && (size_t)K * N * sizeof(float) <= 48 * 1024 && !getenv("NC_HEAD_SMEM");
+        const bool rows_variant = N == 10 && K <= 1024 && !getenv("NC_HEAD_SMEM");
         if (rows_variant) {
-            const int Gr = (M + 3) / 4 < 2 * sms ? (M + 3) / 4 : 2 * sms;          // <= G of the reservation above
-            head_rows_kernel<16><<<Gr, 256, (size_t)K * N * sizeof(float), st>>>(in, net->params + O.w_off, net->params + O.b_off, y_onehot, act_ptr(net, O), dz, dx, M, N, K,
-                                                      loss_name, grad_scale, relu_mask, round_bwd ? 1 : 0, cs ? net->ws : nullptr, dbp,
-                                                      net->red_f, net->red_i, net->counters, loss_out, (int*)correct_out);
+            // one row per CTA pass while the batch is small (a CTA per row up to 4 CTAs per SM), two beyond
+            const int R = M <= 4 * sms ? 1 : 2;
+            const int Gr = (M + R - 1) / R < 4 * sms ? (M + R - 1) / R : 4 * sms;        // <= Gmax of the reservation above
+            if (R == 1)
+                head_rows_kernel<1, 10><<<Gr, 256, (size_t)K * N * sizeof(float), st>>>(in, net->params + O.w_off, net->params + O.b_off, y_onehot, act_ptr(net, O), dz, dx, M, K,
+                                                          loss_name, grad_scale, relu_mask, round_bwd ? 1 : 0, cs ? net->ws : nullptr, dbp,
+                                                          net->red_f, net->red_i, net->counters, loss_out, (int*)correct_out);
+            else
+                head_rows_kernel<2, 10><<<Gr, 256, (size_t)K * N * sizeof(float), st>>>(in, net->params + O.w_off, net->params + O.b_off, y_onehot, act_ptr(net, O), dz, dx, M, K,
+                                                          loss_name, grad_scale, relu_mask, round_bwd ? 1 : 0, cs ? net->ws : nullptr, dbp,
+                                                          net->red_f, net->red_i, net->counters, loss_out, (int*)correct_out);
         }
         else if (N <= 16) { if (cs) NC_HEAD(16, true); else NC_HEAD(16, false); }
         else { if (cs) NC_HEAD(32, true); else NC_HEAD(32, false); }

@@ -155,6 +155,38 @@ extern "C" int nc_pp_cubic_table(int src, int32_t* ofs, int16_t* coef) {
     return NC_OK;
 }
 
+// IPP arithmetic of cv2.resize INTER_CUBIC (the wheel's default): position and Keys cubic in double, coefficients rounded to
+// float32, never quantised (model fitted to the live call, see oracle/pp_restate.py:cv_resize_cubic_ipp)
+void nc_ipp_cubic_axis(int src, int dst, IppCubicAxis* out) {
+    const double scale = (double)src / (double)dst;
+    const double A = -0.75;
+    for (int d = 0; d < dst && d < 28; ++d) {
+        const double f = (d + 0.5) * scale - 0.5;
+        const int s = (int)std::floor(f);
+        const double x = f - s;
+        const double c0 = ((A * (x + 1) - 5 * A) * (x + 1) + 8 * A) * (x + 1) - 4 * A;
+        const double c1 = ((A + 2) * x - (A + 3)) * x * x + 1;
+        const double c2 = ((A + 2) * (1 - x) - (A + 3)) * (1 - x) * (1 - x) + 1;
+        const double c3 = 1.0 - c0 - c1 - c2;
+        const double cs[4] = {c0, c1, c2, c3};
+        for (int k = 0; k < 4; ++k) {
+            int o = s - 1 + k;
+            o = o < 0 ? 0 : (o > src - 1 ? src - 1 : o);
+            out->ofs[d][k] = o;
+            out->coef[d][k] = (float)cs[k];
+        }
+    }
+}
+
+extern "C" int nc_pp_cubic_table_f32(int src, int32_t* ofs, float* coef) {
+    if (src <= 0 || !ofs || !coef) return nc_set_error(nullptr, NC_EINVAL, "bad arguments");
+    IppCubicAxis ax;
+    nc_ipp_cubic_axis(src, 28, &ax);
+    for (int d = 0; d < 28; ++d)
+        for (int k = 0; k < 4; ++k) { ofs[d * 4 + k] = ax.ofs[d][k]; coef[d * 4 + k] = ax.coef[d][k]; }
+    return NC_OK;
+}
+
 extern "C" int nc_pp_pil_table(int in_size, int out_size, int32_t* xmin, int32_t* cnt, int32_t* kk, int kk_capacity) {
     if (in_size <= 0 || out_size <= 0) return nc_set_error(nullptr, NC_EINVAL, "bad arguments");
     PilAxisHost ax;

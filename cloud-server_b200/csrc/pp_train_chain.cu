@@ -20,14 +20,19 @@ namespace {
 struct TrainTabs {
     CvCubicAxis x, y;
 };
+struct IppTabs {          // mode 1: float32 coefficients of the IPP arithmetic
+    IppCubicAxis x, y;
+};
 
 constexpr int kThreads = 256;
 
-template <int C>
+// IPP = true: the arithmetic of the wheel's default cv2.resize (Intel IPP): float32 coefficients that are never quantised,
+// float32 products and sums tap by tap in both passes (horizontal first), round half to even, saturate.
+template <int C, bool IPP>
 __global__ void __launch_bounds__(kThreads)
 train_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h, int w,
                    const __grid_constant__ TrainTabs tabs, uint8_t* __restrict__ out_u8,
-                   float* __restrict__ out_f32, int identity, uint8_t* __restrict__ out_color) {
+                   float* __restrict__ out_f32, int identity, uint8_t* __restrict__ out_color, const IppTabs* __restrict__ ft) {
     constexpr int E = 28 * C;               // interleaved elements per output row
     constexpr int NSIMD = (E / 8) * 8;      // OpenCV v_int16x8 body
     __shared__ int hp[112][E];
@@ -42,10 +47,17 @@ train_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h,
 
     if (!identity) {
         for (int i = tid; i < 112; i += kThreads) {
-            s_xofs[i >> 2][i & 3] = tabs.x.ofs[i >> 2][i & 3] * C;
-            s_xcoef[i >> 2][i & 3] = tabs.x.coef[i >> 2][i & 3];
-            s_yofs[i >> 2][i & 3] = tabs.y.ofs[i >> 2][i & 3];
-            s_ycoef[i >> 2][i & 3] = tabs.y.coef[i >> 2][i & 3];
+            if (IPP) {
+                s_xofs[i >> 2][i & 3] = ft->x.ofs[i >> 2][i & 3] * C;
+                s_xcoef[i >> 2][i & 3] = __float_as_int(ft->x.coef[i >> 2][i & 3]);
+                s_yofs[i >> 2][i & 3] = ft->y.ofs[i >> 2][i & 3];
+                s_ycoef[i >> 2][i & 3] = __float_as_int(ft->y.coef[i >> 2][i & 3]);
+            } else {
+                s_xofs[i >> 2][i & 3] = tabs.x.ofs[i >> 2][i & 3] * C;
+                s_xcoef[i >> 2][i & 3] = tabs.x.coef[i >> 2][i & 3];
+                s_yofs[i >> 2][i & 3] = tabs.y.ofs[i >> 2][i & 3];
+                s_ycoef[i >> 2][i & 3] = tabs.y.coef[i >> 2][i & 3];
+            }
         }
         __syncthreads();
 
@@ -64,14 +76,28 @@ train_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h,
 #pragma unroll
                 for (int c = 0; c < C; ++c) px[t][c] = __ldg(p + c);
             }
+            if (IPP) {
+                float fa[C];
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                const int a = s_xcoef[dx][t];
+                for (int c = 0; c < C; ++c) fa[c] = 0.0f;
 #pragma unroll
-                for (int c = 0; c < C; ++c) acc[c] += (int)px[t][c] * a;
+                for (int t = 0; t < 4; ++t) {
+                    const float a = __int_as_float(s_xcoef[dx][t]);
+#pragma unroll
+                    for (int c = 0; c < C; ++c) fa[c] = __fadd_rn(fa[c], __fmul_rn((float)px[t][c], a));
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) hp[slot][dx * C + c] = __float_as_int(fa[c]);
+            } else {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int a = s_xcoef[dx][t];
+#pragma unroll
+                    for (int c = 0; c < C; ++c) acc[c] += (int)px[t][c] * a;
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) hp[slot][dx * C + c] = acc[c];
             }
-#pragma unroll
-            for (int c = 0; c < C; ++c) hp[slot][dx * C + c] = acc[c];
         }
         __syncthreads();
 
@@ -83,7 +109,13 @@ train_chain_kernel(const uint8_t* __restrict__ src, long long img_stride, int h,
             const int S2 = hp[dy * 4 + 2][e], S3 = hp[dy * 4 + 3][e];
             const int b0 = s_ycoef[dy][0], b1 = s_ycoef[dy][1], b2 = s_ycoef[dy][2], b3 = s_ycoef[dy][3];
             int v;
-            if (e < NSIMD) {
+            if (IPP) {
+                float t = __fmul_rn(__int_as_float(S0), __int_as_float(b0));        // (0 + S0 b0) + S1 b1 ...: tap order
+                t = __fadd_rn(t, __fmul_rn(__int_as_float(S1), __int_as_float(b1)));
+                t = __fadd_rn(t, __fmul_rn(__int_as_float(S2), __int_as_float(b2)));
+                t = __fadd_rn(t, __fmul_rn(__int_as_float(S3), __int_as_float(b3)));
+                v = __float2int_rn(fminf(fmaxf(t, -1.0f), 256.0f));
+            } else if (e < NSIMD) {
                 // v_round(f(S0)*b0 + (f(S1)*b1 + (f(S2)*b2 + f(S3)*b3))), separate mul / add
                 const float f0 = __fmul_rn((float)b0, scale), f1 = __fmul_rn((float)b1, scale);
                 const float f2 = __fmul_rn((float)b2, scale), f3 = __fmul_rn((float)b3, scale);
@@ -244,9 +276,27 @@ train_chain_rows_kernel(const uint8_t* __restrict__ src, long long img_stride, i
 
 static int launch_train_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
                               int64_t img_stride, uint8_t* out_u8, float* out_f32, cudaStream_t st,
-                              uint8_t* out_color = nullptr) {
+                              uint8_t* out_color = nullptr, int mode = 0) {
     TrainTabs tabs;
     const int identity = (h == 28 && w == 28) ? 1 : 0;
+    if (mode == 1 && !identity) {
+        // IPP arithmetic: float tables per shape, cached on the device like the Pillow tables (key: negative sizes)
+        nc_dev_table& t = ctx->pil_tables[std::make_pair(-h, -w)];
+        if (!t.dptr) {
+            IppTabs ft;
+            nc_ipp_cubic_axis(w, 28, &ft.x);
+            nc_ipp_cubic_axis(h, 28, &ft.y);
+            NC_CUDA(ctx, cudaMalloc(&t.dptr, sizeof(IppTabs)));
+            NC_CUDA(ctx, cudaMemcpy(t.dptr, &ft, sizeof(IppTabs), cudaMemcpyHostToDevice));
+            t.bytes = sizeof(IppTabs);
+        }
+        memset(&tabs, 0, sizeof(tabs));
+        const IppTabs* dft = static_cast<const IppTabs*>(t.dptr);
+        if (c == 3) train_chain_kernel<3, true><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, 0, out_color, dft);
+        else train_chain_kernel<1, true><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, 0, out_color, dft);
+        NC_LAUNCH_CHECK(ctx);
+        return NC_OK;
+    }
     if (!identity) {
         nc_cv_cubic_axis(w, 28, &tabs.x);
         nc_cv_cubic_axis(h, 28, &tabs.y);
@@ -266,9 +316,9 @@ static int launch_train_chain(nc_ctx* ctx, const uint8_t* src, int n, int h, int
         return NC_OK;
     }
     if (c == 3)
-        train_chain_kernel<3><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity, out_color);
+        train_chain_kernel<3, false><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity, out_color, nullptr);
     else
-        train_chain_kernel<1><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity, out_color);
+        train_chain_kernel<1, false><<<n, kThreads, 0, st>>>(src, img_stride, h, w, tabs, out_u8, out_f32, identity, out_color, nullptr);
     NC_LAUNCH_CHECK(ctx);
     return NC_OK;
 }
@@ -279,7 +329,7 @@ static int check_train_args(nc_ctx* ctx, const void* src, int n, int h, int w, i
     if (n < 0 || h <= 0 || w <= 0) return nc_set_error(ctx, NC_EINVAL, "bad shape n=%d h=%d w=%d", n, h, w);
     if (c != 1 && c != 3) return nc_set_error(ctx, NC_EINVAL, "channels must be 1 or 3, got %d", c);
     if (img_stride < (int64_t)h * w * c) return nc_set_error(ctx, NC_EINVAL, "img_stride %lld < h*w*c", (long long)img_stride);
-    if (mode != 0) return nc_set_error(ctx, NC_EUNSUPPORTED, "resize mode %d (only 0 = OpenCV-native arithmetic)", mode);
+    if (mode != 0 && mode != 1) return nc_set_error(ctx, NC_EINVAL, "resize mode %d (0 = OpenCV-native arithmetic, 1 = IPP arithmetic)", mode);
     if (n > 0 && !src) return nc_set_error(ctx, NC_EINVAL, "src is NULL");
     if (n > 0 && !o1 && !o2) return nc_set_error(ctx, NC_EINVAL, "both outputs are NULL");
     return NC_OK;
@@ -292,7 +342,7 @@ extern "C" int nc_pp_resize_gray_norm(nc_ctx* ctx, const uint8_t* src, int n, in
     if (rc != NC_OK) return rc;
     if (n == 0) return NC_OK;
     NC_CUDA(ctx, cudaSetDevice(ctx->device));
-    return launch_train_chain(ctx, src, n, h, w, c, img_stride, out_u8, out_f32, (cudaStream_t)stream);
+    return launch_train_chain(ctx, src, n, h, w, c, img_stride, out_u8, out_f32, (cudaStream_t)stream, nullptr, mode);
 }
 
 extern "C" int nc_pp_resize_gray_norm_host(nc_ctx* ctx, const uint8_t* host_src, int n, int h, int w, int c,
@@ -309,7 +359,7 @@ extern "C" int nc_pp_resize_gray_norm_host(nc_ctx* ctx, const uint8_t* host_src,
     if (e != cudaSuccess) { cudaGetLastError(); attr.type = cudaMemoryTypeUnregistered; }
     if (attr.type == cudaMemoryTypeHost && attr.devicePointer != nullptr) {
         // pinned + mapped: gather the taps straight from host memory over PCIe (zero copy)
-        return launch_train_chain(ctx, (const uint8_t*)attr.devicePointer, n, h, w, c, img_stride, out_u8, out_f32, st);
+        return launch_train_chain(ctx, (const uint8_t*)attr.devicePointer, n, h, w, c, img_stride, out_u8, out_f32, st, nullptr, mode);
     }
     // pageable: stage the whole batch through the workspace
     // (the caller's buffer may end right behind the last picture: copy (n-1) strides + one picture, not n strides)
@@ -318,7 +368,7 @@ extern "C" int nc_pp_resize_gray_norm_host(nc_ctx* ctx, const uint8_t* host_src,
     if (rc != NC_OK) return rc;
     NC_CUDA(ctx, cudaMemcpyAsync(ctx->ws, host_src, bytes, cudaMemcpyHostToDevice, st));
     if (staged) *staged = 1;
-    return launch_train_chain(ctx, (const uint8_t*)ctx->ws, n, h, w, c, img_stride, out_u8, out_f32, st);
+    return launch_train_chain(ctx, (const uint8_t*)ctx->ws, n, h, w, c, img_stride, out_u8, out_f32, st, nullptr, mode);
 }
 
 extern "C" int nc_pp_resize_cubic(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c, int64_t img_stride,
@@ -327,5 +377,5 @@ extern "C" int nc_pp_resize_cubic(nc_ctx* ctx, const uint8_t* src, int n, int h,
     if (rc != NC_OK) return rc;
     if (n == 0) return NC_OK;
     NC_CUDA(ctx, cudaSetDevice(ctx->device));
-    return launch_train_chain(ctx, src, n, h, w, c, img_stride, nullptr, nullptr, (cudaStream_t)stream, out);
+    return launch_train_chain(ctx, src, n, h, w, c, img_stride, nullptr, nullptr, (cudaStream_t)stream, out, mode);
 }

@@ -82,7 +82,11 @@ int nc_jpeg_decode(nc_ctx* ctx, const uint8_t* const* host_jpegs, const size_t* 
  *   images.astype(float32) * (1/255)    apps/construction/util/construct_distribute.py:503-504
  * img_stride = bytes between consecutive images (>= h*w*c).  mode 0 = OpenCV's own arithmetic
  * (cv2 4.13 with IPP disabled: int32 horizontal pass, float32 SIMD-body / integer-tail
- * vertical pass) -- bit exact.  Other modes: NC_EUNSUPPORTED.
+ * vertical pass) -- bit exact.  mode 1 = the arithmetic the opencv-python wheel uses by DEFAULT
+ * (Intel IPP, closed source; requirment.txt:14 does not pin the wheel): unquantised float32
+ * coefficients, float32 products and sums tap by tap, horizontal pass first, round half to even
+ * -- a float model fitted to the live call, 100 % equal on 94 080 probed outputs, gated at 99.9 %.
+ * The two modes differ by +-1 on 3-5 % of the outputs.
  * out_u8[n][28][28] and/or out_f32[n][784] (either may be NULL). */
 int nc_pp_resize_gray_norm(nc_ctx* ctx, const uint8_t* src, int n, int h, int w, int c,
                            int64_t img_stride, int mode, uint8_t* out_u8, float* out_f32,
@@ -165,11 +169,13 @@ int nc_pp_op(nc_ctx* ctx, int op_id, const uint8_t* in, uint8_t* out, int n, dou
  * needed; used by the CPU tests to check the host logic against the oracle).
  *  nc_pp_cubic_table: OpenCV INTER_CUBIC taps for one axis src -> 28 (preprocess.py:29):
  *                     ofs[28*4] clamped source indices, coef[28*4] = round(c*2048).
+ *  nc_pp_cubic_table_f32: the same taps in the IPP arithmetic of mode 1: ofs[28*4], float32 coef[28*4].
  *  nc_pp_pil_table:   Pillow BICUBIC antialias taps for one axis in_size -> out_size
  *                     (construct_inference.py:315): xmin[out], cnt[out], kk[out*ksize] 22-bit
  *                     fixed point; returns ksize (or a negative error); kk may be NULL to query.
  *  nc_pp_gaussian_q8: cv2.GaussianBlur(k,k,0) 8-bit fixed-point kernel (preprocess.py:134). */
 int nc_pp_cubic_table(int src, int32_t* ofs, int16_t* coef);
+int nc_pp_cubic_table_f32(int src, int32_t* ofs, float* coef);
 int nc_pp_pil_table(int in_size, int out_size, int32_t* xmin, int32_t* cnt, int32_t* kk, int kk_capacity);
 int nc_pp_gaussian_q8(int k, int32_t* q);
 

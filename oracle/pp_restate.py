@@ -107,6 +107,56 @@ def cv_resize_cubic_u8(img: np.ndarray, dh: int = 28, dw: int = 28, simd_lanes: 
     return out[:, :, 0] if squeeze else out
 
 
+def ipp_cubic_tables(src: int, dst: int):
+    """Tap offsets and float32 coefficients of the IPP path of cv2.resize INTER_CUBIC (one axis): position and Keys cubic
+    (A = -0.75) evaluated in float64, coefficients then rounded to float32 -- NOT quantised to 11 bits."""
+    scale = src / dst
+    ofs = np.zeros((dst, 4), np.int32)
+    coef = np.zeros((dst, 4), F32)
+    A = -0.75
+    for d in range(dst):
+        f = (d + 0.5) * scale - 0.5
+        s = int(np.floor(f))
+        x = f - s
+        c0 = ((A * (x + 1) - 5 * A) * (x + 1) + 8 * A) * (x + 1) - 4 * A
+        c1 = ((A + 2) * x - (A + 3)) * x * x + 1
+        c2 = ((A + 2) * (1 - x) - (A + 3)) * (1 - x) * (1 - x) + 1
+        c3 = 1.0 - c0 - c1 - c2
+        coef[d] = np.array([c0, c1, c2, c3], np.float64).astype(F32)
+        ofs[d] = np.clip(np.arange(s - 1, s + 3), 0, src - 1)
+    return ofs, coef
+
+
+def cv_resize_cubic_ipp(img: np.ndarray, dh: int = 28, dw: int = 28) -> np.ndarray:
+    """``cv2.resize(img,(dw,dh),INTER_CUBIC)`` for uint8 as the opencv-python wheel computes it BY DEFAULT (IPP enabled,
+    ippiResizeCubic; closed source).  Float model fitted to the live call: horizontal pass then vertical pass, float32
+    coefficients (ipp_cubic_tables), float32 products and sums taken tap by tap in order (no FMA), round half to even,
+    saturate.  0 mismatches over 94 080 outputs (40 pictures, 8 shapes) against cv2 4.13.0 / IPP 2022.2 in this image
+    (tests/test_oracle_pp.py); the reference's requirment.txt does not pin the wheel, so this is the arithmetic its
+    preprocess.resize (apps/preprocess/preprocess.py:29) runs with unless the host disables IPP."""
+    assert img.dtype == np.uint8
+    squeeze = img.ndim == 2
+    if squeeze:
+        img = img[:, :, None]
+    H, W, C = img.shape
+    if (H, W) == (dh, dw):
+        return img[:, :, 0].copy() if squeeze else img.copy()
+    xo, xa = ipp_cubic_tables(W, dw)
+    yo, ya = ipp_cubic_tables(H, dh)
+    rows = np.unique(yo)
+    pos = {int(r): i for i, r in enumerate(rows)}
+    I = img[rows].astype(F32)
+    t = np.zeros((len(rows), dw, C), F32)
+    for k in range(4):
+        t = t + I[:, xo[:, k], :] * xa[:, k][None, :, None]
+    ridx = np.vectorize(lambda r: pos[int(r)])(yo)
+    o = np.zeros((dh, dw, C), F32)
+    for k in range(4):
+        o = o + t[ridx[:, k]] * ya[:, k][:, None, None]
+    out = np.clip(np.rint(o), 0, 255).astype(np.uint8)
+    return out[:, :, 0] if squeeze else out
+
+
 # --------------------------------------------------------------------------------------
 # P3: gray conversion of cv2.imread(dir, 0) on the resized BGR file
 #     apps/preprocess/preprocess.py:40 (and every op's first line)
@@ -133,10 +183,11 @@ def dataset_normalise(gray_u8: np.ndarray) -> np.ndarray:
     return np.multiply(flat, F32(1.0 / 255.0))
 
 
-def train_chain(img_bgr: np.ndarray):
+def train_chain(img_bgr: np.ndarray, mode: int = 0):
     """resize (preprocess.py:28-30) -> gray (:40) -> normalise (construct_distribute.py:503-504)
-    composed in memory (no JPEG round trip).  Returns (u8[28,28], f32[784])."""
-    small = cv_resize_cubic_u8(img_bgr, 28, 28)
+    composed in memory (no JPEG round trip).  Returns (u8[28,28], f32[784]).  mode 0: OpenCV's own resize arithmetic
+    (IPP disabled), mode 1: the wheel's default (IPP) arithmetic."""
+    small = cv_resize_cubic_ipp(img_bgr, 28, 28) if mode == 1 else cv_resize_cubic_u8(img_bgr, 28, 28)
     gray = cv_bgr2gray(small) if small.ndim == 3 else small
     return gray, dataset_normalise(gray[None])[0]
 

@@ -146,6 +146,56 @@ def test_train_chain_bad_arguments(ctx):
         ctx.resize_gray_norm(torch.zeros((1, 30, 30, 3), dtype=torch.float32, device="cuda"))
 
 
+def test_train_chain_ipp_arithmetic_mode1(ctx):
+    """P2 mode 1 (the wheel's default arithmetic, Intel IPP): the kernel equals the oracle's float model bit for bit, the
+    committed golden outputs of the IPP-enabled wheel to >= 99.9 % (measured 100 %), and -- on a box whose cv2 has IPP --
+    the live call; pageable host input and the colour output take the same mode."""
+    g = golden("train_chain_ipp.npz")
+    same = tot = 0
+    for seed, h, w, nat in g["cases"]:
+        if nat and not cvref.have_cv2():
+            continue
+        img = synth_upload(int(seed), int(h), int(w), bool(nat))
+        u8, f32 = ctx.resize_gray_norm(dev(img[None]), mode=1)
+        e8, ef = R.train_chain(img, mode=1)
+        assert np.array_equal(u8[0].cpu().numpy(), e8) and np.array_equal(f32[0].cpu().numpy(), ef), (seed, h, w)
+        col = ctx.resize_cubic(dev(img[None]), mode=1)[0].cpu().numpy()
+        assert np.array_equal(col, R.cv_resize_cubic_ipp(img))
+        same += int((col == g[f"bgr_{seed}"]).sum())
+        tot += col.size
+    assert same >= 0.999 * tot, (same, tot)
+    rng = np.random.default_rng(31)
+    for it in range(12):
+        h, w = int(rng.integers(29, 500)), int(rng.integers(29, 500))
+        imgs = rng.integers(0, 256, (2, h, w, 3), np.uint8)
+        u8, _ = ctx.resize_gray_norm(dev(imgs), mode=1)
+        for i in range(2):
+            assert np.array_equal(u8[i].cpu().numpy(), R.train_chain(imgs[i], mode=1)[0]), (h, w)
+    gray = rng.integers(0, 256, (2, 90, 70), np.uint8)
+    u8, _ = ctx.resize_gray_norm(dev(gray), mode=1)
+    assert np.array_equal(u8[0].cpu().numpy(), R.cv_resize_cubic_ipp(gray[0]))
+    host = torch.from_numpy(imgs)                                  # pageable host memory: staged, same arithmetic
+    u8h, _ = ctx.resize_gray_norm(host, mode=1)
+    assert torch.equal(u8h, u8.new_tensor(np.stack([R.train_chain(imgs[i], mode=1)[0] for i in range(2)])))
+    if cvref.have_cv2():
+        import cv2
+        try:
+            cv2.ipp.setUseIPP(True)
+            if cv2.ipp.useIPP():
+                same = tot = 0
+                for h, w in ((768, 1024), (480, 640), (255, 257)):
+                    img = rng.integers(0, 256, (h, w, 3), np.uint8)
+                    want = cv2.resize(img, (28, 28), interpolation=cv2.INTER_CUBIC)
+                    got = ctx.resize_cubic(dev(img[None]), mode=1)[0].cpu().numpy()
+                    same += int((got == want).sum())
+                    tot += want.size
+                assert same >= 0.999 * tot, (same, tot)
+        finally:
+            cv2.ipp.setUseIPP(False)
+    with pytest.raises(ValueError):
+        ctx.resize_gray_norm(dev(imgs), mode=2)
+
+
 # ------------------------------------------------------------------ predict-side chain (P5)
 def test_predict_chain_bundled_pictures(ctx):
     p = golden("pics.npz")
