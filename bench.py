@@ -275,6 +275,16 @@ def dp_parity_check(torch, ctx, world, rank, device, math):
     y = torch.nn.functional.one_hot(torch.randint(0, 10, (2, B), device=device, generator=g), 10).float()
     net = Net(LENET, ctx, seed=100 + rank)
     net.set_math(math)
+    if rank == 0:
+        # damped start (dense x0.1, filters x0.3): at the reference's sigma-0.1 initial values SGD 0.05 is chaotic and any
+        # last-bit difference (the summation order of the W partial gradients) grows by orders of magnitude in two steps
+        w = net.get_params()
+        for off, size, shape in net.tensors:
+            if len(shape) == 2:
+                w[off:off + size] *= 0.1
+            elif len(shape) == 4:
+                w[off:off + size] *= 0.3
+        net.set_params(w)
     dp = DataParallel(net, in_library=True)
     w0 = net.params.clone()
     single = Net(LENET, ctx, seed=5)

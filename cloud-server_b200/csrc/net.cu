@@ -167,6 +167,8 @@ struct nc_net {
     // it is all-reduced on comm_stream while the convolution gradients are still being computed
     cudaStream_t comm_stream = nullptr; cudaEvent_t ev_tail_ready = nullptr, ev_tail_done = nullptr, ev_head_ready = nullptr;
     int split_layer = -1; int64_t split_off = 0; bool tail_in_flight = false;
+    bool tail_applied = false;  // this step's update of [split_off, nparams) already ran on comm_stream behind the tail exchange
+    int dp_opt = -1; float dp_lr = 0.0f;     // set by nc_net_train_step: the update may follow the tail exchange on the side stream
     bool dp_step = false;       // set by nc_net_train_step around its backward pass: the exchange may start early
     std::string err;
 };
@@ -872,6 +874,29 @@ extern "C" int nc_net_predict(nc_net* net, const float* x, int n, int32_t* label
 // ------------------------------------------------------------------------------------------------
 // backward
 // ------------------------------------------------------------------------------------------------
+static int apply_range(nc_net* net, int opt, float lr, int64_t off, int64_t count, cudaStream_t st);
+static int ensure_state(nc_net* net, int opt, cudaStream_t st);
+
+// Data-parallel step: the tail of the flat gradient buffer (from the split layer's weights to the end) is final -- sum it
+// over the ranks on the side stream while backward goes on.  When the remaining backward kernels no longer read those
+// parameters themselves (math 3: the input-gradient GEMMs read the rounded copy params_hi), the optimizer update of the tail
+// follows the exchange on the side stream too, so only the small head is left for the end of the step.
+static int dp_send_tail(nc_net* net, cudaStream_t st, bool params_copy_in_use) {
+    if (!(net->dp_step && net->world > 1 && net->comm_stream && net->split_layer >= 0) || net->tail_in_flight) return NC_OK;
+    NET_CUDA(net, cudaEventRecord(net->ev_tail_ready, st));
+    NET_CUDA(net, cudaStreamWaitEvent(net->comm_stream, net->ev_tail_ready, 0));
+    int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads + net->split_off, (size_t)(net->nparams - net->split_off), net->comm_stream);
+    if (rc != NC_OK) return rc;
+    if (params_copy_in_use && net->dp_opt >= 0 && (net->split_off & 3) == 0 && !getenv("NC_DP_NO_EARLY_APPLY")) {
+        rc = apply_range(net, net->dp_opt, net->dp_lr, net->split_off, net->nparams - net->split_off, net->comm_stream);
+        if (rc != NC_OK) return rc;
+        net->tail_applied = true;
+    }
+    NET_CUDA(net, cudaEventRecord(net->ev_tail_done, net->comm_stream));
+    net->tail_in_flight = true;
+    return NC_OK;
+}
+
 extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_onehot, int n, int loss_name, float grad_scale,
                                float* loss_out, int32_t* correct_out, void* stream) {
     int rc = check_io(net, x, n);
@@ -1069,11 +1094,16 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             if (!done) rc = run_gemm<false, true>(net, K, N, M, ColMajor{in, K}, RowMajor{d, N}, dW, nullptr, st);
             if (rc != NC_OK) return rc;
             if (li != bias_done) { rc = run_colsum(net, d, M, N, dB, st); if (rc != NC_OK) return rc; }
+            // every gradient from this layer's weights to the end of the flat buffer is final now: the exchange can start
+            // under this layer's own input-gradient GEMM
+            if (li == net->split_layer) { rc = dp_send_tail(net, st, round_bwd); if (rc != NC_OK) return rc; }
             if (need_dx) {   // dX[M][K] = dY[M][N] * W^T[N][K]   (W[in][out] is already the K-major B operand)
                 if (net->prof_on) PROF(net, st, (stage_name("bwd", li, L) + " dgrad").c_str());
-                rc = tc_try(net, d, round_bwd ? net->params_hi + L.w_off : W, dn, nullptr, M, K, N, false, false, st, &done, true);
+                // math 3 reads the rounded copy (also on the SIMT fallback: the side stream may already be updating `params`)
+                const float* Wd = round_bwd ? net->params_hi + L.w_off : W;
+                rc = tc_try(net, d, Wd, dn, nullptr, M, K, N, false, false, st, &done, true);
                 if (rc != NC_OK) return rc;
-                if (!done) rc = run_gemm<true, false>(net, M, K, N, RowMajor{d, N}, ColMajor{W, N}, dn, nullptr, st);
+                if (!done) rc = run_gemm<true, false>(net, M, K, N, RowMajor{d, N}, ColMajor{Wd, N}, dn, nullptr, st);
                 if (rc != NC_OK) return rc;
             }
             break;
@@ -1136,9 +1166,10 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             if (need_dx) {
                 if (net->prof_on) PROF(net, st, (stage_name("bwd", li, L) + " dgrad").c_str());
                 const int Mi = n * L.ih * L.iw, Ki = L.fh * L.fw * L.oc;
-                rc = tc_conv_try(net, 1, L, n, d, round_bwd ? net->params_hi + L.w_off : W, dn, nullptr, st, &done);
+                const float* Wd = round_bwd ? net->params_hi + L.w_off : W;
+                rc = tc_conv_try(net, 1, L, n, d, Wd, dn, nullptr, st, &done);
                 if (rc != NC_OK) return rc;
-                if (!done) rc = run_gemm<true, false>(net, Mi, L.ic, Ki, DgradA{d, geom(L)}, DgradB{W, geom(L)}, dn, nullptr, st);
+                if (!done) rc = run_gemm<true, false>(net, Mi, L.ic, Ki, DgradA{d, geom(L)}, DgradB{Wd, geom(L)}, dn, nullptr, st);
                 if (rc != NC_OK) return rc;
             }
             break;
@@ -1217,15 +1248,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         }
         }
         if (need_dx) { float* t = d; d = dn; dn = t; }
-        if (net->dp_step && net->world > 1 && li == net->split_layer && net->comm_stream) {
-            // everything from this layer to the end of the flat gradient buffer is final: send it while backward goes on
-            NET_CUDA(net, cudaEventRecord(net->ev_tail_ready, st));
-            NET_CUDA(net, cudaStreamWaitEvent(net->comm_stream, net->ev_tail_ready, 0));
-            rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads + net->split_off, (size_t)(net->nparams - net->split_off), net->comm_stream);
-            if (rc != NC_OK) return rc;
-            NET_CUDA(net, cudaEventRecord(net->ev_tail_done, net->comm_stream));
-            net->tail_in_flight = true;
-        }
+        if (li == net->split_layer && !net->tail_in_flight) { rc = dp_send_tail(net, st, round_bwd); if (rc != NC_OK) return rc; }
     }
     return NC_OK;
 }
@@ -1247,6 +1270,22 @@ static int ensure_state(nc_net* net, int opt, cudaStream_t st) {
     return NC_OK;
 }
 
+// the update of parameters [off, off + count) (elementwise: any sub-range is the same arithmetic); does not touch global_step
+static int apply_range(nc_net* net, int opt, float lr, int64_t off, int64_t count, cudaStream_t st) {
+    if (count <= 0) return NC_OK;
+    const int grid = grid_for(count, net->ctx->sm_count);
+    if (opt == 0) adagrad_kernel<<<grid, 256, 0, st>>>(net->params + off, net->grads + off, net->st_adagrad + off, count, lr);
+    else if (opt == 1) sgd_kernel<<<grid, 256, 0, st>>>(net->params + off, net->grads + off, count, lr);
+    else {
+        const double t = (double)(net->global_step + 1);
+        const double b1 = 0.9, b2 = 0.999;
+        const float lr_t = (float)((double)lr * std::sqrt(1.0 - std::pow(b2, t)) / (1.0 - std::pow(b1, t)));
+        adam_kernel<<<grid, 256, 0, st>>>(net->params + off, net->grads + off, net->st_adam + off, net->st_adam + net->nparams + off, count, lr_t, 0.9f, 0.999f, 1e-8f);
+    }
+    NET_LAUNCH(net);
+    return NC_OK;
+}
+
 extern "C" int nc_net_apply(nc_net* net, int opt, float lr, void* stream) {
     if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
     if (opt < 0 || opt > 2) return net_err(net, NC_EINVAL, "optimizer must be 0 (Adagrad), 1 (SGD) or 2 (Adam)");
@@ -1254,17 +1293,13 @@ extern "C" int nc_net_apply(nc_net* net, int opt, float lr, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     int rc = ensure_state(net, opt, st);
     if (rc != NC_OK) return rc;
-    const int grid = grid_for(net->nparams, net->ctx->sm_count);
     PROF(net, st, "optimizer");
-    if (opt == 0) adagrad_kernel<<<grid, 256, 0, st>>>(net->params, net->grads, net->st_adagrad, net->nparams, lr);
-    else if (opt == 1) sgd_kernel<<<grid, 256, 0, st>>>(net->params, net->grads, net->nparams, lr);
-    else {
-        const double t = (double)(net->global_step + 1);
-        const double b1 = 0.9, b2 = 0.999;
-        const float lr_t = (float)((double)lr * std::sqrt(1.0 - std::pow(b2, t)) / (1.0 - std::pow(b1, t)));
-        adam_kernel<<<grid, 256, 0, st>>>(net->params, net->grads, net->st_adam, net->st_adam + net->nparams, net->nparams, lr_t, 0.9f, 0.999f, 1e-8f);
-    }
-    NET_LAUNCH(net);
+    // a data-parallel step whose tail (the dense layers) was exchanged AND updated on the side stream during backward:
+    // only the head is left
+    const int64_t count = net->tail_applied ? net->split_off : net->nparams;
+    net->tail_applied = false;
+    rc = apply_range(net, opt, lr, 0, count, st);
+    if (rc != NC_OK) return rc;
     net->global_step++;
     return NC_OK;
 }
@@ -1314,10 +1349,18 @@ extern "C" int nc_net_train_step(nc_net* net, const float* x, const float* y_one
                                  float* loss_out, int32_t* correct_out, void* stream) {
     if (!net) return nc_set_error(nullptr, NC_EINVAL, "net is NULL");
     // attached to a communicator: this rank's slice of the global batch; the loss is a batch mean, so scale by 1/world and sum
+    if (opt < 0 || opt > 2) return net_err(net, NC_EINVAL, "optimizer must be 0 (Adagrad), 1 (SGD) or 2 (Adam)");
     net->dp_step = net->world > 1;
-    int rc = nc_net_backward(net, x, y_onehot, n, loss_name, 1.0f / (float)net->world, loss_out, correct_out, stream);
-    net->dp_step = false;
-    if (rc != NC_OK) { net->tail_in_flight = false; return rc; }
+    int rc = NC_OK;
+    if (net->dp_step) {
+        NET_CUDA(net, cudaSetDevice(net->ctx->device));
+        rc = ensure_state(net, opt, (cudaStream_t)stream);          // the tail's update may run on the side stream during backward
+        if (rc != NC_OK) return rc;
+        net->dp_opt = opt; net->dp_lr = lr;
+    }
+    rc = nc_net_backward(net, x, y_onehot, n, loss_name, 1.0f / (float)net->world, loss_out, correct_out, stream);
+    net->dp_step = false; net->dp_opt = -1;
+    if (rc != NC_OK) { net->tail_in_flight = false; net->tail_applied = false; return rc; }
     if (net->world > 1) { rc = nc_net_allreduce_grads(net, stream); if (rc != NC_OK) return rc; }
     return nc_net_apply(net, opt, lr, stream);
 }
