@@ -61,7 +61,7 @@ template <int BN, int MODE, bool X3>
 __global__ void __launch_bounds__(kThreads, BN <= 64 ? 2 : 1)
 conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const I2cArgs ia,
                 float* __restrict__ C, const float* __restrict__ bias, int M, int N, int nkb_total, int kb_per_slice,
-                float* __restrict__ partial, int act) {
+                float* __restrict__ partial, int act, const __grid_constant__ CUtensorMap tmC, int tstore) {
     constexpr bool DGRAD = MODE == 1, WGRAD = MODE == 2;
     constexpr bool A_MN = WGRAD;                 // wgrad: the im2col rows are k-rows (pixels) of an MN-major tile
     constexpr bool B_MN = !DGRAD;
@@ -286,7 +286,19 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
                 for (int j = 0; j < 32; ++j) r[j] = 0u;
             }
-            if (row < M) {
+            if (tstore) {
+                // finished tile -> shared memory (the operand ring is idle by now) -> one TMA tensor store per 32-column chunk
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int col = n0 + c0 + j;
+                    float t = __uint_as_float(r[j]);
+                    if (bias && col < N) t += __ldg(bias + col);
+                    if (act == 1) t = fmaxf(t, 0.0f);
+                    v[j] = t;
+                }
+                stage_row_chunk(smem_u32(smem), c0 >> 5, (unsigned)(q * 32 + lane), v);
+            } else if (row < M) {
                 float* po = out + (size_t)row * N + n0 + c0;
                 if (n0 + c0 + 32 <= N && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(po) & 15) == 0 &&
                     (partial || !bias || (reinterpret_cast<uintptr_t>(bias) & 15) == 0)) {
@@ -314,6 +326,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 }
             }
         }
+        if (tstore) store_staged_tile(&tmC, smem_u32(smem), (BN + 31) / 32, n0, m0, N, warp == 2);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -349,14 +362,14 @@ int get_encode_i2c(nc_ctx* ctx) {
 
 template <int BN, int MODE, bool X3>
 int launch_i2c(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, const I2cArgs& ia, float* C, const float* bias, int M,
-               int N, int nkb, int kbps, int splits, float* partial, cudaStream_t st, int act) {
+               int N, int nkb, int kbps, int splits, float* partial, cudaStream_t st, int act, const CUtensorMap& mc, int tstore) {
     const bool ta = X3 && MODE != 2 && NC_TMEM_A;
     const size_t smem = (size_t)StageCount<BN, X3>::value * (BM * BK * 4 + BN * BK * 4) +
                         (X3 ? (ta ? (size_t)(BN <= 64 ? NC_I2C_X3_LOS : 4) * BN * BK * 4 : (size_t)LO_SLOTS * (BM * BK * 4 + BN * BK * 4)) : 0) + 1024;
     auto kfn = conv_i2c_kernel<BN, MODE, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);
-    kfn<<<grid, kThreads, smem, st>>>(ma, mb, ia, C, bias, M, N, nkb, kbps, partial, act);
+    kfn<<<grid, kThreads, smem, st>>>(ma, mb, ia, C, bias, M, N, nkb, kbps, partial, act, mc, tstore);
     NC_LAUNCH_CHECK(ctx);
     return NC_OK;
 }
@@ -422,9 +435,12 @@ int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, con
     if (rc != NC_OK) return rc;
     const int nkb = (K + BK - 1) / BK;
     float* partial = splits > 1 ? ws : nullptr;
-#define NC_I2C(BN_, MODE_)                                                                                        \
-    rc = x3 ? launch_i2c<BN_, MODE_, true>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act)  \
-            : launch_i2c<BN_, MODE_, false>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act)
+    CUtensorMap mc = mb;
+    const int tstore = (!partial && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 && !getenv("NC_NO_TMA_STORE")) ? 1 : 0;
+    if (tstore) { rc = make_map(ctx, &mc, out, M, N, BM, false, N); if (rc != NC_OK) return rc; }
+#define NC_I2C(BN_, MODE_)                                                                                                    \
+    rc = x3 ? launch_i2c<BN_, MODE_, true>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act, mc, tstore)  \
+            : launch_i2c<BN_, MODE_, false>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act, mc, tstore)
     if (BN == 32) { if (mode == 0) NC_I2C(32, 0); else if (mode == 1) NC_I2C(32, 1); else NC_I2C(32, 2); }
     else if (BN == 64) { if (mode == 0) NC_I2C(64, 0); else if (mode == 1) NC_I2C(64, 1); else NC_I2C(64, 2); }
     else { if (mode == 0) NC_I2C(128, 0); else if (mode == 1) NC_I2C(128, 1); else NC_I2C(128, 2); }

@@ -381,7 +381,13 @@ head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const
         const int total = K * N, total4 = ((reinterpret_cast<uintptr_t>(w) & 15) == 0) ? total / 4 : 0;
         const float4* w4 = reinterpret_cast<const float4*>(w);
         float4* s4 = reinterpret_cast<float4*>(sw);
-        for (int i = t; i < total4; i += 256) s4[i] = __ldg(w4 + i);
+        // K * N / 4 <= 2560 float4 (K <= 1024, N = 10): at most 10 per thread, all in flight at once
+        float4 v[10];
+#pragma unroll
+        for (int u = 0; u < 10; ++u) if (t + 256 * u < total4) v[u] = __ldg(w4 + t + 256 * u);
+#pragma unroll
+        for (int u = 0; u < 10; ++u) if (t + 256 * u < total4) s4[t + 256 * u] = v[u];
+        for (int i = t + 2560; i < total4; i += 256) s4[i] = __ldg(w4 + i);
         for (int j = total4 * 4 + t; j < total; j += 256) sw[j] = __ldg(w + j);
     }
     __syncthreads();
@@ -497,11 +503,38 @@ head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const
         for (int i = 0; i < R; ++i) { a += s_l[i]; hh += s_h[i]; }
         loss_partial[blockIdx.x] = a; hit_partial[blockIdx.x] = hh;
     }
-    if (!last_block_arrives(counter, gridDim.x)) return;
-    const int G = gridDim.x;
+    // Two-level, fixed-order sum over the CTAs (one CTA summing every partial row alone is a chain of G dependent-latency
+    // loads per column -- measured 30-70 us at G = 256-592): the last CTA of each group of 16 sums its group, the last
+    // group to finish sums the group rows.  group counters: counter[1 + group]; cs_partial rows [G, G + ngroups) and
+    // loss_partial / hit_partial entries [G, G + ngroups) hold the group sums.
+    const int G = gridDim.x, ngroups = (G + 15) / 16, grp = blockIdx.x >> 4;
+    const int g0 = grp * 16, gsize = min(16, G - g0);
+    if (!last_block_arrives(counter + 1 + grp, gsize)) return;
     if (warp == 0) {
         float a = 0.0f; int hh = 0;
-        for (int b = lane; b < G; b += 32) { a += __ldcg(loss_partial + b); hh += __ldcg(hit_partial + b); }
+        if (lane < gsize) { a = __ldcg(loss_partial + g0 + lane); hh = __ldcg(hit_partial + g0 + lane); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); hh += __shfl_xor_sync(0xffffffffu, hh, o); }
+        if (lane == 0) { loss_partial[G + grp] = a; hit_partial[G + grp] = hh; }
+    }
+    if (cs_partial) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (!own[i]) continue;
+            const int kk = t + 256 * i;
+            float v[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) v[u] = u < gsize ? __ldcg(cs_partial + (long long)(g0 + u) * K + kk) : 0.0f;
+            float a = 0.0f;
+#pragma unroll
+            for (int u = 0; u < 16; ++u) a += v[u];
+            cs_partial[(long long)(G + grp) * K + kk] = a;
+        }
+    }
+    if (!last_block_arrives(counter, ngroups)) return;
+    if (warp == 0) {
+        float a = 0.0f; int hh = 0;
+        for (int b = lane; b < ngroups; b += 32) { a += __ldcg(loss_partial + G + b); hh += __ldcg(hit_partial + G + b); }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); hh += __shfl_xor_sync(0xffffffffu, hh, o); }
         if (lane == 0) {
@@ -516,14 +549,14 @@ head_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const
             const int kk = t + 256 * i;
             float a = 0.0f;
             int b = 0;
-            for (; b + 7 < G; b += 8) {                // eight independent L2 loads in flight, summed in CTA order
+            for (; b + 7 < ngroups; b += 8) {          // eight independent L2 loads in flight, summed in group order
                 float v[8];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) v[u] = __ldcg(cs_partial + (long long)(b + u) * K + kk);
+                for (int u = 0; u < 8; ++u) v[u] = __ldcg(cs_partial + (long long)(G + b + u) * K + kk);
 #pragma unroll
                 for (int u = 0; u < 8; ++u) a += v[u];
             }
-            for (; b < G; ++b) a += __ldcg(cs_partial + (long long)b * K + kk);
+            for (; b < ngroups; ++b) a += __ldcg(cs_partial + (long long)(G + b) * K + kk);
             db_out[kk] = a;
         }
     }

@@ -20,6 +20,7 @@
 #include "nc_internal.h"
 #include "tc_gemm.h"
 #include "tc_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -42,7 +43,7 @@ template <int BN, bool A_MN, bool B_MN, bool X3>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ C,
                  const float* __restrict__ bias, int M, int N, int K, int kb_per_slice, int act, float slope,
-                 float* __restrict__ partial) {
+                 float* __restrict__ partial, const __grid_constant__ CUtensorMap tmC, int tstore) {
     constexpr int STAGES = StageCount<BN, X3>::value;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     constexpr unsigned A_BYTES = BM * BK * 4, B_BYTES = BN * BK * 4;
@@ -241,7 +242,21 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                 for (int j = 0; j < 32; ++j) r[j] = 0u;
             }
-            if (row < M) {
+            if (tstore) {
+                // finished tile -> shared memory (the operand ring is idle by now) -> one TMA tensor store per 32-column chunk
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int col = n0 + c0 + j;
+                    float t = __uint_as_float(r[j]);
+                    if (bias && col < N) t += __ldg(bias + col);
+                    if (act == 1) t = fmaxf(t, 0.0f);
+                    else if (act == 2) t = 1.0f / (1.0f + expf(-t));
+                    else if (act == 3) t = fmaxf(t, slope * t);
+                    v[j] = t;
+                }
+                stage_row_chunk(smem_u32(smem), c0 >> 5, (unsigned)(q * 32 + lane), v);
+            } else if (row < M) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const int col = n0 + c0 + j;
@@ -258,6 +273,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
             }
         }
+        if (tstore) store_staged_tile(&tmC, smem_u32(smem), BN / 32, n0, m0, N, warp == 2);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -282,14 +298,14 @@ __global__ void tc_reduce_kernel(float* __restrict__ dst, const float* __restric
 
 template <int BN, bool A_MN, bool B_MN, bool X3>
 int launch(nc_ctx* ctx, const CUtensorMap& ma, const CUtensorMap& mb, float* C, const float* bias, int M, int N, int K,
-           int kbps, int splits, int act, float slope, float* partial, cudaStream_t st) {
+           int kbps, int splits, int act, float slope, float* partial, cudaStream_t st, const CUtensorMap& mc, int tstore) {
     const bool ta = X3 && !A_MN && NC_TMEM_A;
     const size_t smem = (size_t)StageCount<BN, X3>::value * (BM * BK * 4 + BN * BK * 4) +
                         (X3 ? (ta ? (size_t)4 * BN * BK * 4 : (size_t)LO_SLOTS * (BM * BK * 4 + BN * BK * 4)) : 0) + 1024;
     auto kfn = gemm_tf32_kernel<BN, A_MN, B_MN, X3>;
     NC_CUDA(ctx, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, splits);
-    kfn<<<grid, kThreads, smem, st>>>(ma, mb, C, bias, M, N, K, kbps, act, slope, partial);
+    kfn<<<grid, kThreads, smem, st>>>(ma, mb, C, bias, M, N, K, kbps, act, slope, partial, mc, tstore);
     NC_LAUNCH_CHECK(ctx);
     return NC_OK;
 }
@@ -347,9 +363,13 @@ int nc_tc_gemm_ex(nc_ctx* ctx, const float* A, const float* B, float* C, const f
     rc = b_mn ? make_map(ctx, &mb, B, kb, N, 32, true, ldb) : make_map(ctx, &mb, B, N, kb, BN, false, ldb);
     if (rc != NC_OK) return rc;
     float* partial = splits > 1 ? ws : nullptr;
+    // un-split outputs leave through shared memory and a TMA tensor store (row pitch and base 16-byte aligned)
+    CUtensorMap mc = ma;
+    const int tstore = (!partial && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 && !getenv("NC_NO_TMA_STORE")) ? 1 : 0;
+    if (tstore) { rc = make_map(ctx, &mc, C, M, N, BM, false, N); if (rc != NC_OK) return rc; }
 #define NC_TC_LAUNCH(BN_, AM, BMJ)                                                                                          \
-    rc = x3 ? launch<BN_, AM, BMJ, true>(ctx, ma, mb, C, bias, M, N, K, kbps, splits, act, slope, partial, st)                \
-            : launch<BN_, AM, BMJ, false>(ctx, ma, mb, C, bias, M, N, K, kbps, splits, act, slope, partial, st)
+    rc = x3 ? launch<BN_, AM, BMJ, true>(ctx, ma, mb, C, bias, M, N, K, kbps, splits, act, slope, partial, st, mc, tstore)    \
+            : launch<BN_, AM, BMJ, false>(ctx, ma, mb, C, bias, M, N, K, kbps, splits, act, slope, partial, st, mc, tstore)
     if (BN == 64) {
         if (!a_mn && !b_mn) NC_TC_LAUNCH(64, false, false);
         else if (!a_mn && b_mn) NC_TC_LAUNCH(64, false, true);

@@ -958,7 +958,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         if ((K + 255) / 256 > 512) return net_err(net, NC_EUNSUPPORTED, "output layer with %d inputs", K);
         {
             // one workspace, used by the two launches one after the other: the head's column sums, then the slice partials
-            const size_t a = cs ? (size_t)Gmax * K * sizeof(float) : 0, b = (size_t)slices * K * N * sizeof(float);
+            const size_t a = cs ? (size_t)(Gmax + (Gmax + 15) / 16) * K * sizeof(float) : 0, b = (size_t)slices * K * N * sizeof(float);
             rc = reserve_ws(net, a > b ? a : b);
             if (rc != NC_OK) return rc;
         }
@@ -977,8 +977,8 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         const bool rows_variant = N == 10 && K <= 1024 && !getenv("NC_HEAD_SMEM");
         if (rows_variant) {
             // one row per CTA pass while the batch is small (a CTA per row up to 4 CTAs per SM), two beyond
-            const int R = M <= 4 * sms ? 1 : 2;
-            const int Gr = (M + R - 1) / R < 4 * sms ? (M + R - 1) / R : 4 * sms;        // <= Gmax of the reservation above
+            const int R = M <= 2 * sms ? 1 : 2;
+            const int Gr = (M + R - 1) / R < 2 * sms ? (M + R - 1) / R : 2 * sms;        // <= Gmax of the reservation above
             if (R == 1)
                 head_rows_kernel<1, 10><<<Gr, 256, (size_t)K * N * sizeof(float), st>>>(in, net->params + O.w_off, net->params + O.b_off, y_onehot, act_ptr(net, O), dz, dx, M, K,
                                                           loss_name, grad_scale, relu_mask, round_bwd ? 1 : 0, cs ? net->ws : nullptr, dbp,
@@ -1003,12 +1003,12 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             if (ms > 1) { rc = reserve_ws(net, (size_t)ms * K * N * sizeof(float)); if (rc != NC_OK) return rc; }
             dim3 grid((K + 31) / 32, ms);
             head_wgrad_rows_kernel<16><<<grid, 1024, (size_t)32 * 32 * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off,
-                                                                                                 M, N, K, rps2, net->counters + 16);
+                                                                                                 M, N, K, rps2, net->counters + 64);
             NET_LAUNCH(net);
         } else {
             dim3 grid((K + 255) / 256, slices);
-            if (N <= 16) head_wgrad_kernel<16><<<grid, 256, (size_t)rps * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off, M, N, K, rps, net->counters + 16);
-            else head_wgrad_kernel<32><<<grid, 256, (size_t)rps * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off, M, N, K, rps, net->counters + 16);
+            if (N <= 16) head_wgrad_kernel<16><<<grid, 256, (size_t)rps * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off, M, N, K, rps, net->counters + 64);
+            else head_wgrad_kernel<32><<<grid, 256, (size_t)rps * N * sizeof(float), st>>>(in, dz, net->ws, net->grads + O.w_off, net->grads + O.b_off, M, N, K, rps, net->counters + 64);
             NET_LAUNCH(net);
         }
         start = below;
@@ -1195,7 +1195,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                     if (want_cs) { rc = reserve_ws(net, (size_t)blocks * L.ic * sizeof(float)); if (rc != NC_OK) return rc; }
                     maxpool_bwd_tiled_vec4_cs_kernel<<<blocks, 256, 0, st>>>(d, argp, dn, pgeom(L), total_out / 4, fused ? out : nullptr,
                                                                               round_bwd ? 1 : 0, want_cs ? net->ws : nullptr,
-                                                                              want_cs ? net->grads + net->layers[tgt].b_off : nullptr, net->counters + 8);
+                                                                              want_cs ? net->grads + net->layers[tgt].b_off : nullptr, net->counters + 900);
                     if (want_cs) bias_done = tgt;
                 }
                 else if (v4) maxpool_bwd_tiled_vec4_kernel<<<grid_for(total_out / 4, sms), 256, 0, st>>>(d, argp, dn, pgeom(L), total_out / 4, fused ? out : nullptr);
@@ -1221,7 +1221,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
                     if (want_cs && blocks > (total / 4 > (1 << 20) ? 6 : 2) * sms) blocks = (total / 4 > (1 << 20) ? 6 : 2) * sms;
                     if (want_cs) { rc = reserve_ws(net, (size_t)blocks * C * sizeof(float)); if (rc != NC_OK) return rc; }
                     act_bwd_vec4_cs_kernel<<<blocks, 256, 0, st>>>(xin, out, d, dn, total / 4, c4n, L.act, L.slope, round_bwd ? 1 : 0,
-                                                                    want_cs ? net->ws : nullptr, want_cs ? net->grads + B.b_off : nullptr, net->counters + 8);
+                                                                    want_cs ? net->ws : nullptr, want_cs ? net->grads + B.b_off : nullptr, net->counters + 900);
                     if (want_cs) bias_done = li - 1;
                 } else {
                     act_bwd_kernel<<<grid_for(total, sms), 256, 0, st>>>(xin, out, d, dn, total, L.act, L.slope);

@@ -783,7 +783,7 @@ first_conv_relu_pool_fwd_kernel(const float* __restrict__ x, const float* __rest
 // pooled pixel is read with 8-byte shared loads into registers (18 loads instead of 100 for 5x5) and every weight is used
 // four times from its register.  Same fma order per output as the generic kernel: identical bytes.
 template <int FH, int FW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 first_conv_relu_pool_fwd_c1_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                                    float* __restrict__ y, uint8_t* __restrict__ arg, FirstGeom g, int n, int ob) {
     extern __shared__ __align__(16) float tile[];

@@ -40,6 +40,39 @@ __device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map
                  ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
 }
 
+// TMA tensor store of one 128-row x 32-float box (128-byte-swizzled rows in shared memory) to [c1 .. c1+128) x [c0 .. c0+32) of
+// the mapped matrix; rows / columns outside the matrix are clipped by the unit
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, unsigned src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit_and_wait_read() {
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");       // shared memory may be reused / the CTA may exit
+}
+
+// Epilogue through shared memory + TMA store.  Called by the 8 epilogue warps (256 threads) for each 32-column chunk they
+// read from TMEM: v[32] = this thread's row (tile row r) of chunk `chunk`, already biased / activated.  The chunk is staged as a
+// [128][32] fp32 box whose 16-byte pieces are XOR-swizzled by (row & 7) -- conflict-free 128-bit shared stores, and the layout
+// CU_TENSOR_MAP_SWIZZLE_128B expects.
+__device__ __forceinline__ void stage_row_chunk(unsigned stage_base, int chunk, unsigned r, const float* v) {
+    const unsigned row = stage_base + (unsigned)chunk * 16384u + r * 128u;
+#pragma unroll
+    for (unsigned j = 0; j < 8; ++j)
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row + ((j ^ (r & 7u)) << 4)), "f"(v[4 * j]), "f"(v[4 * j + 1]),
+                     "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+}
+// after the last chunk: make the staged tile visible to the TMA unit, meet the other epilogue warps, one thread stores
+__device__ __forceinline__ void store_staged_tile(const CUtensorMap* map, unsigned stage_base, int chunks, int n0, int m0, int N, bool leader_warp) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (leader_warp && elect_one()) {
+        for (int c = 0; c < chunks; ++c)
+            if (n0 + c * 32 < N) tma_store_2d(map, stage_base + (unsigned)c * 16384u, n0 + c * 32, m0);
+        tma_store_commit_and_wait_read();
+    }
+}
+
 // shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start>>4 [0,14), LBO>>4 [16,30),
 // SBO>>4 [32,46), version=1 [46,48), layout SWIZZLE_128B = 2 [61,64)
 __device__ __forceinline__ unsigned long long umma_desc(unsigned saddr, unsigned lbo_bytes, unsigned sbo_bytes,

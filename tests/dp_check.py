@@ -41,15 +41,24 @@ def main():
     norm_net = {"middle_layer": [{"layer": "conv", "filter": [3, 3, 8], "isBias": "True"}, {"layer": "norm"},
                                  {"layer": "active", "active_func": "relu"}, {"layer": "pool"},
                                  {"layer": "connect", "hidden": 64}, {"layer": "norm"}, {"layer": "active", "active_func": "relu"}]}
-    cases = [(LENET, "compat", 1e-4, None), (LENET, "sgd", 0.05, None), (LENET, "sgd", 0.05, True),
-             (API_EXAMPLE, "sgd", 0.05, None), (norm_net, "sgd", 0.05, None), (norm_net, "compat", 1e-4, None)]
-    for cfg, opt, lr, in_library in cases:
+    # (net, optimizer, lr, in_library, math (None = the library default, 3), tolerance relative to the update).  The norm net under
+    # SGD 0.05 is the sensitive one: in the default math the activation gradients are rounded to TF32 where they are produced, so
+    # a last-bit difference of the all-reduced batch moments (summation order over the ranks) can become a 2^-11 difference of a
+    # few elements; with fp32 kernels (math 0) the same case holds 1e-3.
+    cases = [(LENET, "compat", 1e-4, None, None, 1e-3), (LENET, "sgd", 0.05, None, None, 1e-3), (LENET, "sgd", 0.05, True, None, 1e-3),
+             (API_EXAMPLE, "sgd", 0.05, None, None, 1e-3), (norm_net, "sgd", 0.05, None, 0, 1e-3), (norm_net, "sgd", 0.05, None, None, 5e-3),
+             (norm_net, "compat", 1e-4, None, None, 1e-3)]
+    for cfg, opt, lr, in_library, math, tol in cases:
         net = Net(cfg, ctx, seed=100 + rank)                     # different init per rank: broadcast must fix it
+        if math is not None:
+            net.set_math(math)
         if rank == 0:
             damp(net)
         dp = DataParallel(net, in_library=in_library)
         w0 = net.get_params().copy()
         single = Net(cfg, ctx, seed=5)
+        if math is not None:
+            single.set_math(math)
         single.set_params(w0)
         n = B // world
         for s in range(3):
@@ -64,9 +73,9 @@ def main():
         same = bool(torch.equal(t, net.params))
         if rank == 0:
             name = "lenet" if cfg is LENET else "api_example(norm)" if cfg is API_EXAMPLE else "conv-norm-dense-norm"
-            print("dp_check world=%d net=%s opt=%s in_library=%s: |dp - single| / |update| = %.3e, ranks identical = %s"
-                  % (world, name, opt, dp.in_library, err, same), flush=True)
-        ok = ok and err < 1e-3 and same
+            print("dp_check world=%d net=%s opt=%s in_library=%s math=%s: |dp - single| / |update| = %.3e (tolerance %.0e), ranks identical = %s"
+                  % (world, name, opt, dp.in_library, "default" if math is None else math, err, tol, same), flush=True)
+        ok = ok and err < tol and same
         if dp.in_library:
             net.detach_nccl()
         net.close(); single.close()
