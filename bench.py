@@ -40,6 +40,15 @@ def _emit(line):
     print(json.dumps(line), flush=True)
 
 
+_T0 = time.time()
+
+
+def note(msg):
+    """progress on stderr (stdout carries exactly one JSON line)"""
+    if int(os.environ.get("RANK", "0")) == 0:
+        print("[bench %6.1fs] %s" % (time.time() - _T0, msg), file=sys.stderr, flush=True)
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -141,7 +150,9 @@ def _cpu_work(i):
 
 def _cpu_pool(procs, sample_n, ipp=False):
     import multiprocessing as mp
-    return mp.get_context("fork").Pool(procs, initializer=_cpu_init, initargs=(sample_n, ipp))
+    # spawn, not fork: by now this process owns CUDA, NCCL and OpenCV / OpenMP worker threads, and a forked child that
+    # touches any of their locks can hang
+    return mp.get_context("spawn").Pool(procs, initializer=_cpu_init, initargs=(sample_n, ipp))
 
 
 def cpu_baseline_throughput(seconds, procs, sample_n=16, ipp=False):
@@ -438,6 +449,7 @@ def run_train_bench(torch, ctx, args, rank, world, device, peaks, dist_on, sampl
 
     # ---- main line: C4, global batch 2048 over the ranks (strong scaling); N = 1 is its single-device point
     m = bench_train(GLOBAL_BATCH, want_profile=True, want_e2e=True, clock=True)
+    note("main line done; other train configurations")
     main.update(m)
     if world == 1:
         out["train_b256"] = bench_train(256, want_profile=True, want_e2e=True)       # C3
@@ -583,10 +595,12 @@ def run_preprocess_bench(torch, ctx, args, rank, world, device, peaks, peak_src,
         "value": world * n_e * ks / (ms_z * 1e-3), "unit": "images/s", "h2d_bytes_per_step": int(n_e * 112 * W * C),
         "d2h_bytes_per_step": int(n_e * 3136), "mode": "zero copy: cp.async.bulk of the 112 needed rows straight from pinned host memory"}
     del host
+    note("preprocess: e2e from JPEG files")
     # ---- e2e from the FILES the platform really holds: JPEG uploads (cv2.imread, preprocess.py:28) -> both chains.
     #      Huffman decoding on the host cores, coefficients over PCIe, IDCT / upsampling / colour + both chains on the device.
     try:
         import cv2
+        cv2.setNumThreads(1)
         rng = np.random.default_rng(5)
         distinct = 16
         files = []
@@ -648,7 +662,9 @@ def run_ours(args, rank, local_rank, world):
     peaks, peak_src = measured_peaks()
     sampler = ClockSampler(local_rank)
 
+    note("context up; data-parallel parity check" if dist_on else "context up")
     parity = dp_parity_check(torch, ctx, world, rank, device, args.math) if dist_on else None
+    note("train benchmarks")
     main, subs = run_train_bench(torch, ctx, args, rank, world, device, peaks, dist_on, sampler)
     local = GLOBAL_BATCH // world
     line = {
@@ -669,18 +685,21 @@ def run_ours(args, rank, local_rank, world):
 
     # ---- C2: the preprocess half (sub-object with its own roofline / e2e / cpu_baseline)
     if not args.no_preprocess:
+        note("preprocess benchmark (C2)")
         line["preprocess"] = run_preprocess_bench(torch, ctx, args, rank, world, device, peaks, peak_src, dist_on)
 
     # ---- CPU baselines on this box's host cores (rank 0, N == 1 only), bounded samples
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         ksteps = 8
+        note("cpu baseline: torch-CPU train step, %d threads" % threads)
         v, dt = cpu_train_step_throughput(GLOBAL_BATCH, ksteps, 1, threads)
         line["cpu_baseline"] = {
             "value": v, "unit": "images/s", "cores": threads, "kind": "port",
             "sample": "%d steps of the same LeNet step at batch %d in torch-CPU (oracle/torchref.py; TensorFlow 1.x is not "
                       "installable here), %.1f s" % (ksteps, GLOBAL_BATCH, dt)}
         if "preprocess" in line:
+            note("cpu baseline: cv2 / Pillow preprocess chains, %d worker processes" % threads)
             pv, done, pdt = cpu_baseline_throughput(args.cpu_seconds, threads)
             line["preprocess"]["cpu_baseline"] = {
                 "value": pv, "unit": "images/s", "cores": threads, "kind": "port",
@@ -690,6 +709,7 @@ def run_ours(args, rank, local_rank, world):
             pv2, done2, pdt2 = cpu_baseline_throughput(min(args.cpu_seconds, 6.0), threads, ipp=True)
             line["preprocess"]["cpu_baseline_ipp_on"] = {"value": pv2, "unit": "images/s", "cores": threads, "kind": "port",
                                                          "sample": "same, cv2 with its default IPP arithmetic, %.1f s (%d pictures)" % (pdt2, done2)}
+    note("done")
     if rank == 0:
         _emit(line)
     if dist_on:

@@ -264,7 +264,8 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             mbar_wait(smem_u32(&s_tmem_full), 0);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
-        float* out = partial ? partial + (size_t)blockIdx.z * M * N : C;
+        const int Mpad = (M + BM - 1) / BM * BM;                    // rows per K slice of the partial buffer: whole tiles
+        float* out = partial ? partial + (size_t)blockIdx.z * Mpad * N : C;
         // warps 2-5 take the even 32-column chunks, warps 6-9 the odd ones (a warp reads the TMEM lane quarter warp % 4)
 #pragma unroll 1
         for (int c0 = (warp >= 6 ? 32 : 0); c0 < BN; c0 += 64) {
@@ -293,8 +294,10 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 for (int j = 0; j < 32; ++j) {
                     const int col = n0 + c0 + j;
                     float t = __uint_as_float(r[j]);
-                    if (bias && col < N) t += __ldg(bias + col);
-                    if (act == 1) t = fmaxf(t, 0.0f);
+                    if (!partial) {
+                        if (bias && col < N) t += __ldg(bias + col);
+                        if (act == 1) t = fmaxf(t, 0.0f);
+                    }
                     v[j] = t;
                 }
                 stage_row_chunk(smem_u32(smem), c0 >> 5, (unsigned)(q * 32 + lane), v);
@@ -326,7 +329,7 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 }
             }
         }
-        if (tstore) store_staged_tile(&tmC, smem_u32(smem), (BN + 31) / 32, n0, m0, N, warp == 2);
+        if (tstore) store_staged_tile(&tmC, smem_u32(smem), (BN + 31) / 32, n0, (partial ? (int)blockIdx.z * Mpad : 0) + m0, N, warp == 2);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -334,11 +337,11 @@ conv_i2c_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 }
 
 __global__ void i2c_reduce_kernel(float* __restrict__ dst, const float* __restrict__ ws, int splits, long long count,
-                                  const float* __restrict__ bias, int ncols, int act) {
+                                  const float* __restrict__ bias, int ncols, int act, long long slice_stride) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
         float s = 0.0f;
-        for (int k = 0; k < splits; ++k) s += ws[(long long)k * count + i];
+        for (int k = 0; k < splits; ++k) s += ws[(long long)k * slice_stride + i];
         if (bias) s += __ldg(bias + (int)(i % ncols));
         if (act == 1) s = fmaxf(s, 0.0f);
         dst[i] = s;
@@ -436,8 +439,10 @@ int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, con
     const int nkb = (K + BK - 1) / BK;
     float* partial = splits > 1 ? ws : nullptr;
     CUtensorMap mc = mb;
-    const int tstore = (!partial && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 && !getenv("NC_NO_TMA_STORE")) ? 1 : 0;
-    if (tstore) { rc = make_map(ctx, &mc, out, M, N, BM, false, N); if (rc != NC_OK) return rc; }
+    const long long Mpad = (long long)(M + BM - 1) / BM * BM;      // K slices of the partial buffer are padded to whole tiles
+    float* dstp = partial ? partial : out;
+    const int tstore = ((N & 3) == 0 && (reinterpret_cast<uintptr_t>(dstp) & 15) == 0 && !getenv("NC_NO_TMA_STORE")) ? 1 : 0;
+    if (tstore) { rc = make_map(ctx, &mc, dstp, partial ? Mpad * splits : M, N, BM, false, N); if (rc != NC_OK) return rc; }
 #define NC_I2C(BN_, MODE_)                                                                                                    \
     rc = x3 ? launch_i2c<BN_, MODE_, true>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act, mc, tstore)  \
             : launch_i2c<BN_, MODE_, false>(ctx, ma, mb, ia, out, bias, M, N, nkb, kbps, splits, partial, st, act, mc, tstore)
@@ -450,7 +455,7 @@ int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, con
         const long long count = (long long)M * N;
         long long blocks = (count + 255) / 256;
         if (blocks > (long long)ctx->sm_count * 8) blocks = (long long)ctx->sm_count * 8;
-        i2c_reduce_kernel<<<(int)blocks, 256, 0, st>>>(out, ws, splits, count, bias, N, act);
+        i2c_reduce_kernel<<<(int)blocks, 256, 0, st>>>(out, ws, splits, count, bias, N, act, Mpad * N);
         NC_LAUNCH_CHECK(ctx);
     }
     return NC_OK;

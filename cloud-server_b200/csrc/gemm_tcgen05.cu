@@ -221,7 +221,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait(smem_u32(&s_tmem_full), 0);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         }
-        float* out = partial ? partial + (size_t)blockIdx.z * M * N : C;
+        const int Mpad = (M + BM - 1) / BM * BM;                    // rows per K slice of the partial buffer: whole tiles
+        float* out = partial ? partial + (size_t)blockIdx.z * Mpad * N : C;
         // warps 2-5 take the even 32-column chunks, warps 6-9 the odd ones (a warp reads the TMEM lane quarter warp % 4)
 #pragma unroll 1
         for (int c0 = (warp >= 6 ? 32 : 0); c0 < BN; c0 += 64) {
@@ -249,10 +250,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 for (int j = 0; j < 32; ++j) {
                     const int col = n0 + c0 + j;
                     float t = __uint_as_float(r[j]);
-                    if (bias && col < N) t += __ldg(bias + col);
-                    if (act == 1) t = fmaxf(t, 0.0f);
-                    else if (act == 2) t = 1.0f / (1.0f + expf(-t));
-                    else if (act == 3) t = fmaxf(t, slope * t);
+                    if (!partial) {
+                        if (bias && col < N) t += __ldg(bias + col);
+                        if (act == 1) t = fmaxf(t, 0.0f);
+                        else if (act == 2) t = 1.0f / (1.0f + expf(-t));
+                        else if (act == 3) t = fmaxf(t, slope * t);
+                    }
                     v[j] = t;
                 }
                 stage_row_chunk(smem_u32(smem), c0 >> 5, (unsigned)(q * 32 + lane), v);
@@ -273,7 +276,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
             }
         }
-        if (tstore) store_staged_tile(&tmC, smem_u32(smem), BN / 32, n0, m0, N, warp == 2);
+        if (tstore) store_staged_tile(&tmC, smem_u32(smem), BN / 32, n0, (partial ? (int)blockIdx.z * Mpad : 0) + m0, N, warp == 2);
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -283,11 +286,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 }
 
 __global__ void tc_reduce_kernel(float* __restrict__ dst, const float* __restrict__ ws, int splits, long long count,
-                                 const float* __restrict__ bias, int ncols, int act, float slope) {
+                                 const float* __restrict__ bias, int ncols, int act, float slope, long long slice_stride) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
         float s = 0.0f;
-        for (int k = 0; k < splits; ++k) s += ws[(long long)k * count + i];
+        for (int k = 0; k < splits; ++k) s += ws[(long long)k * slice_stride + i];
         if (bias) s += __ldg(bias + (int)(i % ncols));
         if (act == 1) s = fmaxf(s, 0.0f);
         else if (act == 2) s = 1.0f / (1.0f + expf(-s));
@@ -337,7 +340,7 @@ size_t nc_tc_gemm_workspace(int sm_count, int M, int N, int K, int* splits_out, 
     splits = (nkb + kbps - 1) / kbps;
     if (splits_out) *splits_out = splits;
     if (kbps_out) *kbps_out = kbps;
-    return splits > 1 ? (size_t)splits * M * N * sizeof(float) : 0;
+    return splits > 1 ? (size_t)splits * ((M + BM - 1) / BM * BM) * N * sizeof(float) : 0;        // slices padded to whole tiles
 }
 
 int nc_tc_gemm(nc_ctx* ctx, const float* A, const float* B, float* C, const float* bias, int M, int N, int K, bool a_mn,
@@ -365,8 +368,11 @@ int nc_tc_gemm_ex(nc_ctx* ctx, const float* A, const float* B, float* C, const f
     float* partial = splits > 1 ? ws : nullptr;
     // un-split outputs leave through shared memory and a TMA tensor store (row pitch and base 16-byte aligned)
     CUtensorMap mc = ma;
-    const int tstore = (!partial && (N & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 && !getenv("NC_NO_TMA_STORE")) ? 1 : 0;
-    if (tstore) { rc = make_map(ctx, &mc, C, M, N, BM, false, N); if (rc != NC_OK) return rc; }
+    // (split-K partials too: their slices are padded to whole tiles, so a tile's rows never reach into the next slice)
+    const long long Mpad = (long long)(M + BM - 1) / BM * BM;
+    float* dstp = partial ? partial : C;
+    const int tstore = ((N & 3) == 0 && (reinterpret_cast<uintptr_t>(dstp) & 15) == 0 && !getenv("NC_NO_TMA_STORE")) ? 1 : 0;
+    if (tstore) { rc = make_map(ctx, &mc, dstp, partial ? Mpad * splits : M, N, BM, false, N); if (rc != NC_OK) return rc; }
 #define NC_TC_LAUNCH(BN_, AM, BMJ)                                                                                          \
     rc = x3 ? launch<BN_, AM, BMJ, true>(ctx, ma, mb, C, bias, M, N, K, kbps, splits, act, slope, partial, st, mc, tstore)    \
             : launch<BN_, AM, BMJ, false>(ctx, ma, mb, C, bias, M, N, K, kbps, splits, act, slope, partial, st, mc, tstore)
@@ -387,7 +393,7 @@ int nc_tc_gemm_ex(nc_ctx* ctx, const float* A, const float* B, float* C, const f
         const long long count = (long long)M * N;
         long long blocks = (count + 255) / 256;
         if (blocks > (long long)ctx->sm_count * 8) blocks = (long long)ctx->sm_count * 8;
-        tc_reduce_kernel<<<(int)blocks, 256, 0, st>>>(C, ws, splits, count, bias, N, act, slope);
+        tc_reduce_kernel<<<(int)blocks, 256, 0, st>>>(C, ws, splits, count, bias, N, act, slope, Mpad * N);
         NC_LAUNCH_CHECK(ctx);
     }
     return NC_OK;
