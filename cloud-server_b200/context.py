@@ -109,8 +109,8 @@ class Context:
         if n == 0:
             return torch.empty((0, 0, 0, channels), dtype=torch.uint8, device=self.tdev)
         w, h, _, _, _ = self.jpeg_info(files[0])
-        keep = [(C.c_ubyte * len(f)).from_buffer_copy(f) for f in files]
-        ptrs = (C.c_void_p * n)(*[C.addressof(k) for k in keep])
+        files = [f if isinstance(f, bytes) else bytes(f) for f in files]
+        ptrs = (C.c_void_p * n)(*[C.cast(C.c_char_p(f), C.c_void_p).value for f in files])       # no copies: bytes are immutable and kept alive by `files`
         sizes = (C.c_size_t * n)(*[len(f) for f in files])
         if out is None:
             out = torch.empty((n, h, w, channels), dtype=torch.uint8, device=self.tdev)
