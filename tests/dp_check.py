@@ -45,9 +45,10 @@ def main():
     # SGD 0.05 is the sensitive one: in the default math the activation gradients are rounded to TF32 where they are produced, so
     # a last-bit difference of the all-reduced batch moments (summation order over the ranks) can become a 2^-11 difference of a
     # few elements; with fp32 kernels (math 0) the same case holds 1e-3.
-    cases = [(LENET, "compat", 1e-4, None, None, 1e-3), (LENET, "sgd", 0.05, None, None, 1e-3), (LENET, "sgd", 0.05, True, None, 1e-3),
+    cases = [(LENET, "compat", 1e-4, None, None, 3e-3),      # Adagrad 1e-4 moves a 0.1-sized weight by ~1e-5: the update is read back through fp32 rounding of the weights
+             (LENET, "sgd", 0.05, None, None, 1e-3), (LENET, "sgd", 0.05, True, None, 1e-3),
              (API_EXAMPLE, "sgd", 0.05, None, None, 1e-3), (norm_net, "sgd", 0.05, None, 0, 1e-3), (norm_net, "sgd", 0.05, None, None, 5e-3),
-             (norm_net, "compat", 1e-4, None, None, 1e-3)]
+             (norm_net, "compat", 1e-4, None, None, 3e-3)]
     for cfg, opt, lr, in_library, math, tol in cases:
         net = Net(cfg, ctx, seed=100 + rank)                     # different init per rank: broadcast must fix it
         if math is not None:
