@@ -672,7 +672,8 @@ def run_ours(args, rank, local_rank, world):
         "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "tf32", "data": "synthetic",
         "config": {"workload": TRAIN_WORKLOAD % (GLOBAL_BATCH, world), "global_batch": GLOBAL_BATCH, "per_gpu_batch": local,
-                   "parallelism": "single device" if world == 1 else "dp%d: NCCL all-reduce (sum) of the 13.1 MB flat gradient buffer inside the step" % world,
+                   "parallelism": "single device" if world == 1 else "dp%d: %s all-reduce (sum) of the 13.1 MB flat gradient buffer inside the step" % (
+                       world, "NVLink peer-memory (own kernel)" if getattr(dp, "p2p", False) else "NCCL"),
                    "l2": "inputs: the 60000-picture set (188 MB float32) is larger than L2 and every step takes a different batch"},
         "gpu_launches": int(round(main["gpu_launches_per_step"] * args.steps)),
         "roofline": main.get("roofline"), "e2e": main.get("e2e"), "clocks": sampler.summary(),

@@ -76,6 +76,9 @@ _SIGS = {
     "nc_net_attach_nccl": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int]),
     "nc_net_allreduce_grads": (C.c_int, [C.c_void_p, C.c_void_p]),
     "nc_net_detach_nccl": (C.c_int, [C.c_void_p]),
+    "nc_net_p2p_handles": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "nc_net_p2p_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "nc_net_p2p_status": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "nc_net_state_slots": (C.c_int, [C.c_void_p, C.c_int]),
     "nc_net_get_state": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "nc_net_set_state": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int64]),

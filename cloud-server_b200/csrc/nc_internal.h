@@ -47,6 +47,15 @@ int nc_nccl_comm_dup(nc_ctx* ctx, void* comm, int rank, void** out);
 void nc_nccl_comm_destroy(void* comm);
 int nc_nccl_allreduce_sum_f32(nc_ctx* ctx, void* comm, float* buf, size_t count, cudaStream_t st);
 
+// ---- gradient all-reduce over NVLink peer memory (p2p_allreduce.cu) ---------------------------
+struct nc_p2p;
+int nc_p2p_export(nc_ctx* ctx, nc_p2p** pp, float* grads, unsigned char out[128]);
+int nc_p2p_attach(nc_ctx* ctx, nc_p2p* p, float* grads, const unsigned char* all_handles, int rank, int world);
+bool nc_p2p_ready(const nc_p2p* p);
+int nc_p2p_allreduce(nc_ctx* ctx, nc_p2p* p, long long off, long long count, cudaStream_t st);
+int nc_p2p_error(nc_ctx* ctx, nc_p2p* p, int* out);
+void nc_p2p_destroy(nc_p2p* p);
+
 #define NC_CUDA(ctx, call)                                                                     \
     do {                                                                                       \
         cudaError_t e__ = (call);                                                              \

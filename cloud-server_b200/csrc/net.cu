@@ -161,6 +161,7 @@ struct nc_net {
     // second communicator over the same ranks for the small batch-norm moment exchanges on the compute stream: the
     // gradient exchange owns `comm` on comm_stream, and two streams must not share one communicator
     void* comm_norm = nullptr;
+    nc_p2p* p2p = nullptr;      // peer-memory all-reduce of the gradient buckets (nc_net_p2p_attach); NCCL otherwise
     float* dp_buf = nullptr;
     // overlap of the gradient exchange with the rest of backward: the tail of the flat gradient buffer (the dense layers
     // at the end of the net: 98 % of LeNet's parameters) is final as soon as backward has passed layer `split_layer`;
@@ -370,6 +371,7 @@ static double trunc_normal(uint64_t& s) {
 
 static void free_net(nc_net* net) {
     if (!net) return;
+    if (net->p2p) { nc_p2p_destroy(net->p2p); net->p2p = nullptr; }
     if (net->comm_norm) { nc_nccl_comm_destroy(net->comm_norm); net->comm_norm = nullptr; }
     if (net->comm && net->comm_owned) nc_nccl_comm_destroy(net->comm);
     net->comm = nullptr;
@@ -881,11 +883,17 @@ static int ensure_state(nc_net* net, int opt, cudaStream_t st);
 // over the ranks on the side stream while backward goes on.  When the remaining backward kernels no longer read those
 // parameters themselves (math 3: the input-gradient GEMMs read the rounded copy params_hi), the optimizer update of the tail
 // follows the exchange on the side stream too, so only the small head is left for the end of the step.
+// sum grads[off, off + count) over the ranks on stream `cs`: peer-memory kernel when the ranks have mapped each other, else NCCL
+static int dp_sum(nc_net* net, int64_t off, int64_t count, cudaStream_t cs) {
+    if (nc_p2p_ready(net->p2p) && (off & 3) == 0) return nc_p2p_allreduce(net->ctx, net->p2p, off, count, cs);
+    return nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads + off, (size_t)count, cs);
+}
+
 static int dp_send_tail(nc_net* net, cudaStream_t st, bool params_copy_in_use) {
     if (!(net->dp_step && net->world > 1 && net->comm_stream && net->split_layer >= 0) || net->tail_in_flight) return NC_OK;
     NET_CUDA(net, cudaEventRecord(net->ev_tail_ready, st));
     NET_CUDA(net, cudaStreamWaitEvent(net->comm_stream, net->ev_tail_ready, 0));
-    int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads + net->split_off, (size_t)(net->nparams - net->split_off), net->comm_stream);
+    int rc = dp_sum(net, net->split_off, net->nparams - net->split_off, net->comm_stream);
     if (rc != NC_OK) return rc;
     if (params_copy_in_use && net->dp_opt >= 0 && (net->split_off & 3) == 0 && !getenv("NC_DP_NO_EARLY_APPLY")) {
         rc = apply_range(net, net->dp_opt, net->dp_lr, net->split_off, net->nparams - net->split_off, net->comm_stream);
@@ -1465,12 +1473,34 @@ extern "C" int nc_net_detach_nccl(nc_net* net) {
     if (net->comm) {
         cudaSetDevice(net->ctx->device);
         cudaDeviceSynchronize();
+        if (net->p2p) { nc_p2p_destroy(net->p2p); net->p2p = nullptr; }
         if (net->comm_norm) { nc_nccl_comm_destroy(net->comm_norm); net->comm_norm = nullptr; }
         if (net->comm_owned) nc_nccl_comm_destroy(net->comm);
         net->comm = nullptr;
     }
     net->rank = 0; net->world = 1; net->split_layer = -1;
     return NC_OK;
+}
+
+// ---- peer-memory all-reduce: every rank exports the CUDA IPC handles of its gradient buffer and flag words, the host gathers
+// them (any channel: torch.distributed.all_gather_object, a file), every rank maps the others'
+extern "C" int nc_net_p2p_handles(nc_net* net, unsigned char out[128]) {
+    if (!net || !out) return nc_set_error(net ? net->ctx : nullptr, NC_EINVAL, "NULL argument");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    return nc_p2p_export(net->ctx, &net->p2p, net->grads, out);
+}
+
+extern "C" int nc_net_p2p_attach(nc_net* net, const unsigned char* all_handles, int rank, int world) {
+    if (!net || !all_handles) return nc_set_error(net ? net->ctx : nullptr, NC_EINVAL, "NULL argument");
+    if (!net->comm || rank != net->rank || world != net->world) return net_err(net, NC_EINVAL, "attach the communicator first (nc_net_attach_nccl) with the same rank / world");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    return nc_p2p_attach(net->ctx, net->p2p, net->grads, all_handles, rank, world);
+}
+
+extern "C" int nc_net_p2p_status(nc_net* net, int* timed_out) {
+    if (!net || !timed_out) return nc_set_error(net ? net->ctx : nullptr, NC_EINVAL, "NULL argument");
+    NET_CUDA(net, cudaSetDevice(net->ctx->device));
+    return nc_p2p_error(net->ctx, net->p2p, timed_out);
 }
 
 extern "C" int nc_net_allreduce_grads(nc_net* net, void* stream) {
@@ -1486,12 +1516,12 @@ extern "C" int nc_net_allreduce_grads(nc_net* net, void* stream) {
         if (net->split_off > 0) {
             NET_CUDA(net, cudaEventRecord(net->ev_head_ready, st));
             NET_CUDA(net, cudaStreamWaitEvent(net->comm_stream, net->ev_head_ready, 0));
-            const int rc = nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads, (size_t)net->split_off, net->comm_stream);
+            const int rc = dp_sum(net, 0, net->split_off, net->comm_stream);
             if (rc != NC_OK) return rc;
             NET_CUDA(net, cudaEventRecord(net->ev_tail_done, net->comm_stream));
         }
         NET_CUDA(net, cudaStreamWaitEvent(st, net->ev_tail_done, 0));
         return NC_OK;
     }
-    return nc_nccl_allreduce_sum_f32(net->ctx, net->comm, net->grads, (size_t)net->nparams, st);
+    return dp_sum(net, 0, net->nparams, st);
 }

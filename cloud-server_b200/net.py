@@ -185,6 +185,7 @@ class Net:
 
     # ---- data parallel inside the library (nc_net_attach_nccl)
     world = 1
+    rank = 0
 
     def attach_nccl(self, unique_id, rank, world, libnccl_path=None):
         """Collective: joins this net to an NCCL communicator of `world` processes (one per GPU).
@@ -195,7 +196,28 @@ class Net:
         path = (libnccl_path or find_libnccl()).encode()
         with torch.cuda.device(self.ctx.tdev):
             _lib.check(self.ctx.handle, _lib.lib().nc_net_attach_nccl(self.handle, path, buf, int(rank), int(world)))
-        self.world = int(world)
+        self.world, self.rank = int(world), int(rank)
+
+    def attach_p2p(self, gather):
+        """Map the other ranks' gradient buffers (CUDA IPC) so that the gradient sum runs as the library's own NVLink
+        peer-memory kernel instead of ncclAllReduce.  `gather(bytes) -> [bytes per rank, rank order]` is the host's channel
+        (DataParallel passes torch.distributed.all_gather_object).  Returns False (and stays on NCCL) where the GPUs
+        cannot map each other."""
+        buf = (C.c_ubyte * 128)()
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_p2p_handles(self.handle, buf))
+        parts = gather(bytes(buf))
+        blob = b"".join(parts)
+        arr = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        rc = _lib.lib().nc_net_p2p_attach(self.handle, arr, int(self.rank), int(self.world))
+        if rc == _lib.NC_EUNSUPPORTED:
+            return False
+        _lib.check(self.ctx.handle, rc)
+        return True
+
+    def p2p_timed_out(self):
+        v = C.c_int(0)
+        _lib.check(self.ctx.handle, _lib.lib().nc_net_p2p_status(self.handle, C.byref(v)))
+        return bool(v.value)
 
     def detach_nccl(self):
         _lib.check(self.ctx.handle, _lib.lib().nc_net_detach_nccl(self.handle))
@@ -310,6 +332,7 @@ class DataParallel:
         if in_library is None:
             in_library = has_norm and not allow_local_norm
         self.in_library = bool(in_library) and self.world > 1
+        self.p2p = False          # True: gradient sums run as the library's NVLink peer-memory kernel (in_library only)
         src0 = dist.get_global_rank(group, 0) if (group is not None and self.world > 1) else 0
         if self.world > 1:
             dist.broadcast(net.params, src=src0, group=group)  # identical initial weights
@@ -321,6 +344,19 @@ class DataParallel:
             box = [new_nccl_unique_id(net.ctx) if rank == 0 else None]
             dist.broadcast_object_list(box, src=src0, group=group)
             net.attach_nccl(box[0], rank, self.world)
+            import os
+            if self.world <= 8 and not os.environ.get("NC_DP_NO_P2P"):
+                def gather(b):
+                    parts = [None] * self.world
+                    dist.all_gather_object(parts, b, group=group)
+                    return parts
+                ok = net.attach_p2p(gather)
+                # every rank must take the same path
+                flag = torch.tensor([1 if ok else 0], device=net.ctx.tdev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+                self.p2p = bool(flag.item())
+                if not self.p2p and ok:
+                    raise RuntimeError("peer mapping succeeded on this rank but not on all: set NC_DP_NO_P2P=1")
 
     def train_step(self, x_local, y_local, loss_name="entropy", opt="compat", lr=1e-4):
         if self.in_library:

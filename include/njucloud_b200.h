@@ -299,6 +299,18 @@ int nc_net_allreduce_grads(nc_net* net, void* stream);
  * attached the host must not issue collectives on that communicator itself. */
 int nc_net_attach_comm(nc_net* net, const char* libnccl_path, void* nccl_comm, int rank, int world);
 int nc_net_detach_nccl(nc_net* net);
+/* Gradient all-reduce over NVLink peer memory instead of ncclAllReduce (one node, 2..8 ranks, one process per GPU).  At the
+ * bucket sizes of this path NCCL is latency-bound (8 B200: 30 us for the 0.2 MB convolution bucket, 76-90 us for the 12.9 MB
+ * dense bucket); the library's own two-shot kernel reads and writes the peers' gradient buffers directly, sums in rank order
+ * (bit-identical on every rank) and can be captured in a CUDA graph.
+ *   nc_net_p2p_handles  after nc_net_attach_nccl: 128 bytes = the CUDA IPC handles of this rank's gradient buffer and flag words
+ *   nc_net_p2p_attach   all_handles = world x 128 bytes in rank order (gathered by the host through any channel); maps the
+ *                       peers (NC_EUNSUPPORTED if two GPUs have no peer access: the net then keeps using NCCL)
+ *   nc_net_p2p_status   *timed_out = 1 if a wait inside the kernel gave up (~2 s: a peer never launched its step)
+ * Every rank must call nc_net_train_step / nc_net_allreduce_grads in the same order, as with NCCL. */
+int nc_net_p2p_handles(nc_net* net, unsigned char out[128]);
+int nc_net_p2p_attach(nc_net* net, const unsigned char* all_handles, int rank, int world);
+int nc_net_p2p_status(nc_net* net, int* timed_out);
 /* optimizer state (Adagrad accumulator / Adam m,v) for checkpoints: float32[slots*param_count] */
 int nc_net_state_slots(nc_net* net, int opt);
 int nc_net_get_state(nc_net* net, int opt, float* host_state);

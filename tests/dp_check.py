@@ -74,9 +74,12 @@ def main():
         same = bool(torch.equal(t, net.params))
         if rank == 0:
             name = "lenet" if cfg is LENET else "api_example(norm)" if cfg is API_EXAMPLE else "conv-norm-dense-norm"
-            print("dp_check world=%d net=%s opt=%s in_library=%s math=%s: |dp - single| / |update| = %.3e (tolerance %.0e), ranks identical = %s"
-                  % (world, name, opt, dp.in_library, "default" if math is None else math, err, tol, same), flush=True)
+            print("dp_check world=%d net=%s opt=%s in_library=%s exchange=%s math=%s: |dp - single| / |update| = %.3e (tolerance %.0e), ranks identical = %s"
+                  % (world, name, opt, dp.in_library, "peer-memory" if getattr(dp, "p2p", False) else "nccl",
+                     "default" if math is None else math, err, tol, same), flush=True)
         ok = ok and err < tol and same
+        if getattr(dp, "p2p", False):
+            ok = ok and not net.p2p_timed_out()
         if dp.in_library:
             net.detach_nccl()
         net.close(); single.close()
@@ -100,8 +103,8 @@ def main():
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     same = bool(torch.equal(t, net.params))
     if rank == 0:
-        print("dp_check world=%d net=lenet opt=sgd CUDA graph (NCCL captured): |dp - single| / |update| = %.3e, ranks identical = %s, step %d"
-              % (world, err, same, net.global_step), flush=True)
+        print("dp_check world=%d net=lenet opt=sgd CUDA graph (%s exchange captured): |dp - single| / |update| = %.3e, ranks identical = %s, step %d"
+              % (world, "peer-memory" if getattr(dp, "p2p", False) else "NCCL", err, same, net.global_step), flush=True)
     ok = ok and err < 1e-3 and same and net.global_step == 3
     del step
     net.detach_nccl()
