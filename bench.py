@@ -451,6 +451,7 @@ def run_train_bench(torch, ctx, args, rank, world, device, peaks, dist_on, sampl
     m = bench_train(GLOBAL_BATCH, want_profile=True, want_e2e=True, clock=True)
     note("main line done; other train configurations")
     main.update(m)
+    main["grad_exchange"] = "p2p" if getattr(dp, "p2p", False) else ("nccl" if world > 1 else None)
     if world == 1:
         out["train_b256"] = bench_train(256, want_profile=True, want_e2e=True)       # C3
     else:
@@ -673,7 +674,7 @@ def run_ours(args, rank, local_rank, world):
         "vs_baseline": None, "dtype": "tf32", "data": "synthetic",
         "config": {"workload": TRAIN_WORKLOAD % (GLOBAL_BATCH, world), "global_batch": GLOBAL_BATCH, "per_gpu_batch": local,
                    "parallelism": "single device" if world == 1 else "dp%d: %s all-reduce (sum) of the 13.1 MB flat gradient buffer inside the step" % (
-                       world, "NVLink peer-memory (own kernel)" if getattr(dp, "p2p", False) else "NCCL"),
+                       world, "NVLink peer-memory (own kernel)" if main.get("grad_exchange") == "p2p" else "NCCL"),
                    "l2": "inputs: the 60000-picture set (188 MB float32) is larger than L2 and every step takes a different batch"},
         "gpu_launches": int(round(main["gpu_launches_per_step"] * args.steps)),
         "roofline": main.get("roofline"), "e2e": main.get("e2e"), "clocks": sampler.summary(),

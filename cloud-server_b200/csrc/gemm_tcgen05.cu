@@ -327,14 +327,22 @@ size_t nc_tc_gemm_workspace(int sm_count, int M, int N, int K, int* splits_out, 
     const int BN = N <= 64 ? 64 : 128;
     const long long tiles = (long long)((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     const int nkb = (K + BK - 1) / BK;
+    // Split-K by a small cost model in units of one k-block iteration (~0.4 us): whole waves of CTAs over the resident slots
+    // (narrow outputs, N <= 64: two CTAs per SM) x (k blocks per CTA + the fixed cost of a CTA: TMEM allocation, ring fill,
+    // epilogue) + the reduce pass over the partial slices.  Counting waves is the point: 7 tiles x 43 slices = 301 CTAs on
+    // 296 slots, or 16 x 10 = 160 on 148, run as two waves and take twice as long as 294 or 144.
+    const long long slots = N <= 64 ? 2LL * sm_count : sm_count;
+    const int max_splits = nkb >= 8 ? (nkb / 4 < 64 ? nkb / 4 : 64) : 1;
     int splits = 1;
-    // narrow outputs (N <= 64: the convolution kernels, two CTAs per SM) aim at two CTAs per SM; wide ones split only when
-    // the tiles leave more than half of the SMs idle (at 128 tiles a 2-way split costs a second wave and a reduce pass)
-    const long long target = N <= 64 ? 2LL * sm_count : sm_count;
-    if ((N <= 64 ? tiles < target : 2 * tiles <= target) && nkb >= 8) {
-        splits = (int)((target + tiles - 1) / tiles);
-        if (splits > nkb / 4) splits = nkb / 4;
-        if (splits < 1) splits = 1;
+    double best = 0.0;
+    for (int s = 1; s <= max_splits; ++s) {
+        const int kb = (nkb + s - 1) / s;
+        const int s_eff = (nkb + kb - 1) / kb;
+        if (s_eff != s) continue;
+        const long long waves = (tiles * s + slots - 1) / slots;
+        double cost = (double)waves * (kb + 6);
+        if (s > 1) cost += (3.0 + (double)(s + 1) * M * N * 4.0 / 5.0e6) / 0.4;      // launch + slices read once, result written once
+        if (s == 1 || cost < best * 0.97) { best = cost; splits = s; }               // a split has to pay for itself
     }
     int kbps = (nkb + splits - 1) / splits;
     splits = (nkb + kbps - 1) / kbps;
