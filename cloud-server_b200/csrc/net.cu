@@ -692,13 +692,20 @@ static int forward_impl(nc_net* net, const float* x, int n, cudaStream_t st, boo
             const Layer& c = net->layers[0];
             const FirstGeom fg = first_geom(c, L);
             const size_t smem = (size_t)fg.th * fg.tw * fg.ic * sizeof(float);
-            const int blocks = n < sms * 4 ? n : sms * 4;
+            const bool c1x2 = c.ic == 1 && c.fh == 5 && c.fw == 5 && (fg.pw_ & 1) == 0 && (fg.tw & 3) == 0 && !getenv("NC_NO_C1X2");
+            // whole pictures per CTA, the same number for every CTA of the one resident wave (3 CTAs per SM for the
+            // pair kernel, 4 for the others)
+            const bool c1x4 = c1x2 && (fg.poh & 1) == 0 && !getenv("NC_NO_C1X4");
+            const int slots = sms * (c1x2 && !c1x4 ? 3 : 4);       // one resident wave; pictures are dealt round-robin
+            const int blocks = n < slots ? n : slots;
             const float* cw = net->params + c.w_off;
             const float* cb = c.b_off >= 0 ? net->params + c.b_off : nullptr;
             uint8_t* argp = net->aux + L.aux_off * net->cap;
             const bool c1 = c.ic == 1 && (fg.tw & 1) == 0;       // compile-time filter variants: 5x5 and 3x3 on one channel
             for (int ob = 0; ob < (c.oc + 31) / 32; ++ob) {
-                if (c1 && c.fh == 5 && c.fw == 5) first_conv_relu_pool_fwd_c1_kernel<5, 5><<<blocks, 256, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
+                if (c1x4) first_conv_relu_pool_fwd_c1x4_kernel<<<blocks, 224, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
+                else if (c1x2) first_conv_relu_pool_fwd_c1x2_kernel<<<blocks, 256, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
+                else if (c1 && c.fh == 5 && c.fw == 5) first_conv_relu_pool_fwd_c1_kernel<5, 5><<<blocks, 256, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
                 else if (c1 && c.fh == 3 && c.fw == 3) first_conv_relu_pool_fwd_c1_kernel<3, 3><<<blocks, 256, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
                 else first_conv_relu_pool_fwd_kernel<<<blocks, 256, smem, st>>>(x, cw, cb, out, argp, fg, n, ob);
                 NET_LAUNCH(net);
@@ -1052,7 +1059,11 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
         }
         if (net->fuse_first && li == 0) {
             const Layer& P = net->layers[2];
-            const FirstGeom fg = first_geom(L, P);
+            FirstGeom fg = first_geom(L, P);
+            // lanes (channels) read the window of their own argmax: offsets {0, 1, tw, tw + 1} from a common base.  A row
+            // pitch of 0 / +-1 mod 32 words puts two of them in one bank (every shared load replayed); two columns of padding
+            // (loaded as zeros, never addressed) make the four banks distinct.
+            if (L.ic == 1 && ((fg.tw & 31) <= 1 || (fg.tw & 31) == 31) && !getenv("NC_NO_C1_PAD")) fg.tw += 2;
             const size_t smem = (size_t)fg.th * fg.tw * fg.ic * sizeof(float);
             const int K = L.fh * L.fw * L.ic, N = L.oc;
             const int blocks = n < sms * 2 ? n : sms * 2;
@@ -1064,8 +1075,18 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             const int npool = fg.poh * fg.pw_;
             const size_t smem_c1 = (size_t)((fg.th * fg.tw + 3) & ~3) * sizeof(float) + (size_t)npool * 32 * 5;
             const bool c1 = L.ic == 1 && (fg.tw & 1) == 0 && smem_c1 <= 48 * 1024 && ((L.fh == 5 && L.fw == 5) || (L.fh == 3 && L.fw == 3));
+            // pipelined variant: whole 32-channel groups, 16-byte aligned rows, two CTAs per SM
+            const size_t smem_c1p = (size_t)(2 * ((fg.th * fg.tw + 3) & ~3) + 3 * npool * 32) * sizeof(float) + (size_t)2 * npool * 32;
+            const bool c1p = c1 && (N & 31) == 0 && smem_c1p <= 110 * 1024 && !getenv("NC_NO_C1P") &&
+                             ((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(act_ptr(net, P)) | reinterpret_cast<uintptr_t>(argp)) & 15) == 0;
+            if (c1p) {
+                if (L.fh == 5) NET_CUDA(net, cudaFuncSetAttribute(first_conv_wgrad_from_pool_c1p_kernel<5, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c1p));
+                else NET_CUDA(net, cudaFuncSetAttribute(first_conv_wgrad_from_pool_c1p_kernel<3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c1p));
+            }
             for (int ob = 0; ob < (N + 31) / 32; ++ob) {
-                if (c1 && L.fh == 5) first_conv_wgrad_from_pool_c1_kernel<5, 5><<<blocks, 256, smem_c1, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
+                if (c1p && L.fh == 5) first_conv_wgrad_from_pool_c1p_kernel<5, 5><<<blocks, 256, smem_c1p, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
+                else if (c1p) first_conv_wgrad_from_pool_c1p_kernel<3, 3><<<blocks, 256, smem_c1p, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
+                else if (c1 && L.fh == 5) first_conv_wgrad_from_pool_c1_kernel<5, 5><<<blocks, 256, smem_c1, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
                 else if (c1) first_conv_wgrad_from_pool_c1_kernel<3, 3><<<blocks, 256, smem_c1, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
                 else first_conv_wgrad_from_pool_kernel<<<blocks, 256, smem, st>>>(x, d, argp, act_ptr(net, P), pw, pb, fg, n, ob);
                 NET_LAUNCH(net);

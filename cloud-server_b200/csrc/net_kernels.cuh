@@ -835,6 +835,148 @@ first_conv_relu_pool_fwd_c1_kernel(const float* __restrict__ x, const float* __r
     }
 }
 
+// Two horizontally adjacent pooled pixels per warp pass (5x5, one input channel, pooled width even, tile rows a multiple of
+// 16 bytes): their common 6 x 8 input patch is 12 16-byte shared loads for 200 fmas, and the loop overhead (addresses, the
+// argmax selects, the stores) is paid once per two pixels -- the one-pixel kernel above spends 60 % of its issue slots on it.
+// Same fma order per output: identical bytes.
+__global__ void __launch_bounds__(256, 3)
+first_conv_relu_pool_fwd_c1x2_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                                     float* __restrict__ y, uint8_t* __restrict__ arg, FirstGeom g, int n, int ob) {
+    extern __shared__ __align__(16) float tile[];
+    constexpr int FH = 5, FW = 5, T = FH * FW;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    float wreg[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) wreg[t] = co < g.oc ? __ldg(w + (long long)t * g.oc + co) : 0.0f;
+    const float bv = (bias && co < g.oc) ? __ldg(bias + co) : 0.0f;
+    const int npool = g.poh * g.pw_;
+    const int ppr = g.pw_ >> 1, npairs = g.poh * ppr;
+    const int tw = g.tw;
+    for (int img = blockIdx.x; img < n; img += gridDim.x) {
+        __syncthreads();
+        first_load_tile(tile, x + (long long)img * g.ih * g.iw, g);
+        __syncthreads();
+        int py = warp / ppr, pq = warp - py * ppr;
+        for (int q = warp; q < npairs; q += 8) {
+            const float* b = tile + (2 * py) * tw + 4 * pq;          // 16-byte aligned: tw % 4 == 0
+            float pt[FH + 1][8];
+#pragma unroll
+            for (int r = 0; r <= FH; ++r) {
+                const float4 v0 = *reinterpret_cast<const float4*>(b + r * tw);
+                const float4 v1 = *reinterpret_cast<const float4*>(b + r * tw + 4);
+                pt[r][0] = v0.x; pt[r][1] = v0.y; pt[r][2] = v0.z; pt[r][3] = v0.w;
+                pt[r][4] = v1.x; pt[r][5] = v1.y; pt[r][6] = v1.z; pt[r][7] = v1.w;
+            }
+            float a[2][4];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) { a[h][0] = 0.0f; a[h][1] = 0.0f; a[h][2] = 0.0f; a[h][3] = 0.0f; }
+#pragma unroll
+            for (int r = 0; r < FH; ++r)
+#pragma unroll
+                for (int c = 0; c < FW; ++c) {
+                    const float wv = wreg[r * FW + c];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        a[h][0] = fmaf(pt[r][2 * h + c], wv, a[h][0]);
+                        a[h][1] = fmaf(pt[r][2 * h + c + 1], wv, a[h][1]);
+                        a[h][2] = fmaf(pt[r + 1][2 * h + c], wv, a[h][2]);
+                        a[h][3] = fmaf(pt[r + 1][2 * h + c + 1], wv, a[h][3]);
+                    }
+                }
+            const bool vy = 2 * py + 1 < g.coh;
+            const long long o0 = ((long long)img * npool + py * g.pw_ + 2 * pq) * g.oc + co;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const bool vx = 2 * (2 * pq + h) + 1 < g.cow;
+                float best = fmaxf(a[h][0] + bv, 0.0f); int bi = 0;
+                if (vx) { const float v = fmaxf(a[h][1] + bv, 0.0f); if (v > best) { best = v; bi = 1; } }
+                if (vy) { const float v = fmaxf(a[h][2] + bv, 0.0f); if (v > best) { best = v; bi = 2; } }
+                if (vy && vx) { const float v = fmaxf(a[h][3] + bv, 0.0f); if (v > best) { best = v; bi = 3; } }
+                if (co < g.oc) {
+                    y[o0 + (long long)h * g.oc] = best;
+                    arg[o0 + (long long)h * g.oc] = (uint8_t)bi;
+                }
+            }
+            pq += 8;
+            while (pq >= ppr) { pq -= ppr; ++py; }
+        }
+    }
+}
+
+// A 2 x 2 block of pooled pixels (4 x 4 convolution outputs) per warp pass, the 8 x 8 input patch streamed row by row: two
+// 16-byte shared loads per input row feed up to 80 fmas, only one patch row is live in registers, and the per-pixel overhead
+// is paid once per four pooled pixels.  Launched with 224 threads (7 warps: 49 blocks per 28 x 28 picture).  Input row i meets
+// filter row r = i - dy of output row dy, so every output still adds its taps in (r, c) order: identical bytes.
+__global__ void __launch_bounds__(224, 4)
+first_conv_relu_pool_fwd_c1x4_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                                     float* __restrict__ y, uint8_t* __restrict__ arg, FirstGeom g, int n, int ob) {
+    extern __shared__ __align__(16) float tile[];
+    constexpr int FH = 5, FW = 5, T = FH * FW;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+    const int co = ob * 32 + lane;
+    float wreg[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) wreg[t] = co < g.oc ? __ldg(w + (long long)t * g.oc + co) : 0.0f;
+    const float bv = (bias && co < g.oc) ? __ldg(bias + co) : 0.0f;
+    const int npool = g.poh * g.pw_;
+    const int qpr = g.pw_ >> 1, nquad = (g.poh >> 1) * qpr;
+    const int tw = g.tw;
+    for (int img = blockIdx.x; img < n; img += gridDim.x) {
+        __syncthreads();
+        first_load_tile(tile, x + (long long)img * g.ih * g.iw, g);
+        __syncthreads();
+        int qy = warp / qpr, qx = warp - qy * qpr;
+        for (int q = warp; q < nquad; q += nwarp) {
+            const float* b = tile + (4 * qy) * tw + 4 * qx;          // 16-byte aligned: tw % 4 == 0
+            float a[4][4];
+#pragma unroll
+            for (int dy = 0; dy < 4; ++dy)
+#pragma unroll
+                for (int dx = 0; dx < 4; ++dx) a[dy][dx] = 0.0f;
+#pragma unroll
+            for (int i = 0; i < FH + 3; ++i) {
+                const float4 v0 = *reinterpret_cast<const float4*>(b + i * tw);
+                const float4 v1 = *reinterpret_cast<const float4*>(b + i * tw + 4);
+                const float p[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+                for (int dy = 0; dy < 4; ++dy) {
+                    const int r = i - dy;
+                    if (r >= 0 && r < FH) {
+#pragma unroll
+                        for (int c = 0; c < FW; ++c) {
+                            const float wv = wreg[r * FW + c];
+#pragma unroll
+                            for (int dx = 0; dx < 4; ++dx) a[dy][dx] = fmaf(p[c + dx], wv, a[dy][dx]);
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int hy = 0; hy < 2; ++hy) {
+                const int py = 2 * qy + hy;
+                const bool vy = 2 * py + 1 < g.coh;
+#pragma unroll
+                for (int hx = 0; hx < 2; ++hx) {
+                    const int px = 2 * qx + hx;
+                    const bool vx = 2 * px + 1 < g.cow;
+                    float best = fmaxf(a[2 * hy][2 * hx] + bv, 0.0f); int bi = 0;
+                    if (vx) { const float v = fmaxf(a[2 * hy][2 * hx + 1] + bv, 0.0f); if (v > best) { best = v; bi = 1; } }
+                    if (vy) { const float v = fmaxf(a[2 * hy + 1][2 * hx] + bv, 0.0f); if (v > best) { best = v; bi = 2; } }
+                    if (vy && vx) { const float v = fmaxf(a[2 * hy + 1][2 * hx + 1] + bv, 0.0f); if (v > best) { best = v; bi = 3; } }
+                    if (co < g.oc) {
+                        const long long o = ((long long)img * npool + py * g.pw_ + px) * g.oc + co;
+                        y[o] = best;
+                        arg[o] = (uint8_t)bi;
+                    }
+                }
+            }
+            qx += nwarp;
+            while (qx >= qpr) { qx -= qpr; ++qy; }
+        }
+    }
+}
+
 // The matching weight gradient: the picture's masked pooled gradient and argmax bytes are staged in shared memory by the
 // whole CTA first (one exposed global latency per picture instead of one per pooled pixel), taps at compile-time offsets.
 // dynamic smem: tile | gm[npool][32] floats | am[npool][32] bytes
@@ -915,6 +1057,122 @@ first_conv_wgrad_from_pool_c1_kernel(const float* __restrict__ x, const float* _
             for (int r = 0; r < FH; ++r)
 #pragma unroll
                 for (int c = 0; c < FW; ++c) acc[r * FW + c] = fmaf(q0[r * g.tw + c], gv, acc[r * FW + c]);
+        }
+    }
+#pragma unroll
+    for (int t = 0; t <= T; ++t) {
+        __syncthreads();
+        red[warp][lane] = t < T ? acc[t < T ? t : 0] : accb;
+        __syncthreads();
+        if (warp == 0 && co < g.oc) {
+            float sum = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) sum += red[k][lane];
+            if (t < T) partial_w[(size_t)blockIdx.x * T * g.oc + (size_t)t * g.oc + co] = sum;
+            else partial_b[(size_t)blockIdx.x * g.oc + co] = sum;
+        }
+    }
+}
+
+// Pipelined variant (32 channels per launch, 16-byte aligned rows): while the warps accumulate picture i from shared memory,
+// cp.async brings picture i + 1 (input tile, pooled gradient, pooled output, argmax bytes) into the other buffers, so the
+// global-memory latency that made up half of the kernel above is paid once per CTA, not once per picture.  The relu mask is
+// applied in place between two pictures.  Same fma order per tap and channel: identical bytes.
+// dynamic smem: tile[2][tf] | rg[2][npool * 32] floats | rp[npool * 32] floats | ra[2][npool * 32] bytes
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_4_zfill(void* smem_dst, const void* gsrc, bool valid) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(valid ? 4 : 0) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+template <int FH, int FW>
+__global__ void __launch_bounds__(256, 2)
+first_conv_wgrad_from_pool_c1p_kernel(const float* __restrict__ x, const float* __restrict__ dpool, const uint8_t* __restrict__ arg,
+                                      const float* __restrict__ pooled, float* __restrict__ partial_w, float* __restrict__ partial_b,
+                                      FirstGeom g, int n, int ob) {
+    extern __shared__ __align__(16) float tile[];
+    __shared__ float red[8][33];
+    constexpr int T = FH * FW;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co = ob * 32 + lane;
+    const int npool = g.poh * g.pw_;
+    const int tf = (g.th * g.tw + 3) & ~3;
+    float* rg = tile + 2 * tf;
+    float* rp = rg + 2 * npool * 32;
+    uint8_t* ra = reinterpret_cast<uint8_t*>(rp + npool * 32);
+    const int tw = g.tw;
+
+    auto fetch = [&](int img, int buf) {
+        const float* xi = x + (long long)img * g.ih * g.iw;
+        float* tb = tile + buf * tf;
+        const int total = g.th * tw;
+        for (int e = threadIdx.x; e < total; e += 256) {
+            const int r = e / tw, c = e - r * tw;
+            const int iy = r - g.pt, ix = c - g.pl;
+            const bool ok = iy >= 0 && iy < g.ih && ix >= 0 && ix < g.iw;
+            cp_async_4_zfill(tb + e, ok ? xi + (long long)iy * g.iw + ix : xi, ok);
+        }
+        const long long base = (long long)img * npool * g.oc + ob * 32;
+        float* gb = rg + buf * npool * 32;
+        for (int e = threadIdx.x; e < npool * 8; e += 256) {
+            const long long o = base + (long long)(e >> 3) * g.oc + (e & 7) * 4;
+            cp_async_16(gb + e * 4, dpool + o);
+            cp_async_16(rp + e * 4, pooled + o);
+        }
+        uint8_t* ab = ra + buf * npool * 32;
+        for (int e = threadIdx.x; e < npool * 2; e += 256) cp_async_16(ab + e * 16, arg + base + (long long)(e >> 1) * g.oc + (e & 1) * 16);
+    };
+    auto mask = [&](int buf) {                              // relu under the pool, in place
+        float4* gb = reinterpret_cast<float4*>(rg + buf * npool * 32);
+        const float4* pb = reinterpret_cast<const float4*>(rp);
+        for (int e = threadIdx.x; e < npool * 8; e += 256) {
+            float4 m = gb[e]; const float4 pv = pb[e];
+            if (!(pv.x > 0.0f)) m.x = 0.0f;
+            if (!(pv.y > 0.0f)) m.y = 0.0f;
+            if (!(pv.z > 0.0f)) m.z = 0.0f;
+            if (!(pv.w > 0.0f)) m.w = 0.0f;
+            gb[e] = m;
+        }
+    };
+
+    float acc[T];
+#pragma unroll
+    for (int t = 0; t < T; ++t) acc[t] = 0.0f;
+    float accb = 0.0f;
+    int buf = 0;
+    if ((int)blockIdx.x < n) {
+        fetch(blockIdx.x, 0);
+        cp_async_wait_all();
+        __syncthreads();
+        mask(0);
+        __syncthreads();
+    }
+    for (int img = blockIdx.x; img < n; img += gridDim.x, buf ^= 1) {
+        const int next = img + gridDim.x;
+        if (next < n) fetch(next, buf ^ 1);
+        const float* tb = tile + buf * tf;
+        const float* gm = rg + buf * npool * 32;
+        const uint8_t* am = ra + buf * npool * 32;
+        int py = warp / g.pw_, px = warp - py * g.pw_;
+        for (int pp = warp; pp < npool; pp += 8) {
+            const float gv = gm[pp * 32 + lane];
+            const int a = am[pp * 32 + lane];
+            accb += gv;
+            const float* q0 = tb + (2 * py + (a >> 1)) * tw + 2 * px + (a & 1);
+#pragma unroll
+            for (int r = 0; r < FH; ++r)
+#pragma unroll
+                for (int c = 0; c < FW; ++c) acc[r * FW + c] = fmaf(q0[r * tw + c], gv, acc[r * FW + c]);
+            px += 8;
+            while (px >= g.pw_) { px -= g.pw_; ++py; }
+        }
+        if (next < n) {
+            cp_async_wait_all();
+            __syncthreads();                 // everyone is done with rg[buf] / tile[buf], and picture `next` has landed
+            mask(buf ^ 1);
+            __syncthreads();
         }
     }
 #pragma unroll
