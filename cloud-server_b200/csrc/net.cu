@@ -1455,7 +1455,11 @@ static int attach_common(nc_net* net, int rank, int world) {
             if (!net->comm_norm) net->split_layer = -1;       // this NCCL cannot split: everything stays on one stream
         }
         if (net->split_layer >= 0 && !net->comm_stream) {
-            NET_CUDA(net, cudaStreamCreateWithFlags(&net->comm_stream, cudaStreamNonBlocking));
+            // highest priority: the exchange kernels (a few dozen CTAs) take the first CTA slots that come free under the
+            // backward pass instead of queueing behind its waves -- every rank waits for the slowest rank's exchange CTAs
+            int prio_lo = 0, prio_hi = 0;
+            NET_CUDA(net, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+            NET_CUDA(net, cudaStreamCreateWithPriority(&net->comm_stream, cudaStreamNonBlocking, prio_hi));
             NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_tail_ready, cudaEventDisableTiming));
             NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_tail_done, cudaEventDisableTiming));
             NET_CUDA(net, cudaEventCreateWithFlags(&net->ev_head_ready, cudaEventDisableTiming));

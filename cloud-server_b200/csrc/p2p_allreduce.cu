@@ -78,24 +78,38 @@ p2p_allreduce_kernel(PeerPtrs a, long long off, long long count, unsigned* seq, 
     const long long lo = off + (long long)rank * chunk;
     long long hi = lo + chunk;
     if (hi > off + count) hi = off + count;
+    // U float4 per rank in flight per thread: with few ranks one 16-byte load per peer leaves the NVLink round trip exposed
+    constexpr int U = W <= 2 ? 4 : (W <= 4 ? 2 : 1);
     const long long stride = (long long)gridDim.x * kThreads * 4;
-    for (long long i = lo + ((long long)blockIdx.x * kThreads + threadIdx.x) * 4; i < hi; i += stride) {
-        if (i + 4 <= hi) {
-            float4 v[W];
+    for (long long i0 = lo + ((long long)blockIdx.x * kThreads + threadIdx.x) * 4; i0 < hi; i0 += stride * U) {
+        float4 v[U][W];
+        bool full[U];
 #pragma unroll
-            for (int p = 0; p < W; ++p) v[p] = ld_peer4(a.g[p] + i);
-            float4 r = v[0];
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            full[u] = i + 4 <= hi;
+            if (full[u]) {
 #pragma unroll
-            for (int p = 1; p < W; ++p) { r.x += v[p].x; r.y += v[p].y; r.z += v[p].z; r.w += v[p].w; }
+                for (int p = 0; p < W; ++p) v[u][p] = ld_peer4(a.g[p] + i);
+            }
+        }
 #pragma unroll
-            for (int p = 0; p < W; ++p) *reinterpret_cast<float4*>(a.g[p] + i) = r;
-        } else {
-            for (long long j = i; j < hi; ++j) {
-                float r = ld_peer1(a.g[0] + j);
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            if (full[u]) {
+                float4 r = v[u][0];
 #pragma unroll
-                for (int p = 1; p < W; ++p) r += ld_peer1(a.g[p] + j);
+                for (int p = 1; p < W; ++p) { r.x += v[u][p].x; r.y += v[u][p].y; r.z += v[u][p].z; r.w += v[u][p].w; }
 #pragma unroll
-                for (int p = 0; p < W; ++p) a.g[p][j] = r;
+                for (int p = 0; p < W; ++p) *reinterpret_cast<float4*>(a.g[p] + i) = r;
+            } else if (i < hi) {
+                for (long long j = i; j < hi; ++j) {
+                    float r = ld_peer1(a.g[0] + j);
+#pragma unroll
+                    for (int p = 1; p < W; ++p) r += ld_peer1(a.g[p] + j);
+#pragma unroll
+                    for (int p = 0; p < W; ++p) a.g[p][j] = r;
+                }
             }
         }
     }
@@ -177,7 +191,8 @@ int nc_p2p_allreduce(nc_ctx* ctx, nc_p2p* p, long long off, long long count, cud
     // enough CTAs to keep ~W peer loads x 16 B per thread in flight over the chunk, few enough to leave the SMs to the backward pass
     const long long chunk4 = (count / p->ptrs.world + 3) / 4;
     long long blocks = (chunk4 + kThreads - 1) / kThreads;
-    if (blocks > 48) blocks = 48;
+    static const int max_blocks = [] { const char* e = getenv("NC_P2P_CTAS"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 48; }();
+    if (blocks > max_blocks) blocks = max_blocks;
     if (blocks < 1) blocks = 1;
     unsigned* seq = p->flags + 16; unsigned* ticket = p->flags + 17; int* err = reinterpret_cast<int*>(p->flags + 18);
 #define NC_P2P(W_) p2p_allreduce_kernel<W_><<<(int)blocks, kThreads, 0, st>>>(p->ptrs, off, count, seq, ticket, err)

@@ -208,3 +208,30 @@ def test_profile_stages_cover_the_step(ctx):
     assert all(ms >= 0 for _, ms in stages) and 0 < sum(ms for _, ms in stages) < 50
     assert net.profile(lambda: None) == []
     net.close()
+
+
+def test_first_layer_kernel_variants_are_bit_identical(ctx, monkeypatch):
+    """The first block's kernels come in variants picked by shape: forward over 2 x 2 pooled blocks (c1x4), pooled pairs
+    (c1x2) or single pooled pixels (c1); the weight gradient with cp.async double buffering over a CTA's pictures (c1p) or
+    staged per picture (c1).  All keep the fma order per output, so at 700 pictures (several per CTA: the pipelined loop
+    runs) the pooled activations and every gradient agree to the bit in math mode 0."""
+    from cloud_server_b200.net import Net
+    rng = np.random.default_rng(31)
+    n = 700
+    x = torch.from_numpy(rng.random((n, 784), dtype=np.float32)).cuda()
+    y = torch.nn.functional.one_hot(torch.from_numpy(rng.integers(0, 10, n)).cuda(), 10).float()
+    net = Net(tfref.LENET, ctx, seed=6)
+    net.set_math(0)
+    out = []
+    for env in ((), ("NC_NO_C1X4",), ("NC_NO_C1X4", "NC_NO_C1X2"), ("NC_NO_C1P",), ("NC_NO_C1P", "NC_NO_C1_PAD")):
+        for e in env:
+            monkeypatch.setenv(e, "1")
+        logits = net.forward(x).clone()
+        net.backward(x, y, "entropy")
+        out.append((logits, net.grads.clone()))
+        for e in env:
+            monkeypatch.delenv(e)
+    for lg, g in out[1:]:
+        assert torch.equal(lg, out[0][0])
+        assert torch.equal(g, out[0][1])
+    net.close()

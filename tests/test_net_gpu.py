@@ -291,7 +291,13 @@ def test_fused_first_block_equals_separate_kernels(ctx, n, monkeypatch):
                               {"layer": "pool"}, {"layer": "connect", "hidden": 32}]}]     # no bias, 2 output-channel blocks
     cfgs.append({"middle_layer": [{"layer": "conv", "filter": [3, 3, 8], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
                                   {"layer": "pool"}, {"layer": "connect", "hidden": 16}]})   # 3x3 on one channel, odd picture size
-    for cfg, (h, w, c) in zip(cfgs, [(28, 28, 1), (13, 11, 3), (15, 11, 1)]):
+    # pooled height odd: the pooled-pair forward kernel (c1x2) instead of the 2x2-block one; 3x3x32 on an even picture:
+    # the pipelined weight-gradient kernel at its other filter size
+    cfgs.append({"middle_layer": [{"layer": "conv", "filter": [5, 5, 32], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
+                                  {"layer": "pool"}, {"layer": "connect", "hidden": 16}]})
+    cfgs.append({"middle_layer": [{"layer": "conv", "filter": [3, 3, 32], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
+                                  {"layer": "pool"}, {"layer": "connect", "hidden": 16}]})
+    for cfg, (h, w, c) in zip(cfgs, [(28, 28, 1), (13, 11, 3), (15, 11, 1), (26, 28, 1), (16, 12, 1)]):
         rng = np.random.default_rng(8)
         x = torch.from_numpy(rng.random((n, h * w * c), dtype=np.float32)).cuda()
         y = torch.nn.functional.one_hot(torch.from_numpy(rng.integers(0, 10, n)).cuda(), 10).float()
