@@ -365,6 +365,9 @@ void nc_tc_conv_dims(int mode, const nck::ConvGeom& g, int batch, int* M, int* N
 
 int nc_tc_conv(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, const float* src, const float* wmat, float* out,
                const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3) {
+    // input gradient of a small picture: the padded picture stays in shared memory, one fetch per pixel instead of one per tap
+    if (!x3 && !bias && batch >= ctx->sm_count && nc_tc_conv_strip_supported(mode, g, src, wmat, out))     // one picture per SM at least
+        return nc_tc_conv_strip_dgrad(ctx, g, batch, src, wmat, out, st);
     // forward / dgrad of a stride-1 SAME convolution: let the TMA unit do the im2col walk (no gather threads)
     if (nc_tc_conv_i2c_supported(mode, g, src, wmat))
         return nc_tc_conv_i2c(ctx, mode, g, batch, src, wmat, out, bias, ws, ws_bytes, st, x3);

@@ -33,3 +33,8 @@ bool nc_tc_conv_i2c_supported(int mode, const nck::ConvGeom& g, const float* src
 int nc_tc_conv_i2c(nc_ctx* ctx, int mode, const nck::ConvGeom& g, int batch, const float* src, const float* wmat, float* out,
                    const float* bias, float* ws, size_t ws_bytes, cudaStream_t st, bool x3, int act = 0);
 
+
+// input gradient with the zero-padded picture resident in shared memory (conv_strip.cu): stride 1, SAME, Cin == 32,
+// Cout 32 or 64, small pictures (H * (W + fw - 1) <= 384); single rounded TF32 products only
+bool nc_tc_conv_strip_supported(int mode, const nck::ConvGeom& g, const float* src, const float* wmat, float* out);
+int nc_tc_conv_strip_dgrad(nc_ctx* ctx, const nck::ConvGeom& g, int batch, const float* dy, const float* wmat, float* dx, cudaStream_t st);
