@@ -235,3 +235,36 @@ def test_first_layer_kernel_variants_are_bit_identical(ctx, monkeypatch):
         assert torch.equal(lg, out[0][0])
         assert torch.equal(g, out[0][1])
     net.close()
+
+
+@pytest.mark.parametrize("f2,c2", [(5, 64), (3, 64), (3, 32)])
+def test_picture_resident_input_gradient_equals_im2col_kernel(ctx, monkeypatch, f2, c2):
+    """conv_strip.cu (the padded picture of dy loaded once, filter taps as row-shifted matrix descriptors) computes the same
+    single-product TF32 input gradient as the TMA-im2col kernel it replaces at batch >= SM count: every parameter gradient
+    agrees to accumulation-order rounding, and the conv1 gradients -- the ones downstream of it -- with them."""
+    from cloud_server_b200.net import Net
+    cfg = {"middle_layer": [{"layer": "conv", "filter": [5, 5, 32], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
+                            {"layer": "pool"},
+                            {"layer": "conv", "filter": [f2, f2, c2], "isBias": "True"}, {"layer": "active", "active_func": "relu"},
+                            {"layer": "pool"}, {"layer": "connect", "hidden": 64}]}
+    rng = np.random.default_rng(41)
+    n = 333                                                   # several pictures per CTA, uneven
+    x = torch.from_numpy(rng.random((n, 784), dtype=np.float32)).cuda()
+    y = torch.nn.functional.one_hot(torch.from_numpy(rng.integers(0, 10, n)).cuda(), 10).float()
+    net = Net(cfg, ctx, seed=9)                               # default math: gradients as single rounded-TF32 products
+    grads = []
+    for off in (True, False):
+        if off:
+            monkeypatch.setenv("NC_CONV_STRIP", "0")
+        before = ctx.launches
+        net.backward(x, y, "entropy")
+        grads.append((net.grads.cpu().numpy().copy(), ctx.launches - before))
+        if off:
+            monkeypatch.delenv("NC_CONV_STRIP")
+    (g0, _), (g1, _) = grads
+    assert np.isfinite(g1).all()
+    assert rel(g1, g0) < 1e-5
+    n1 = 5 * 5 * 32 + 32
+    assert rel(g1[:n1], g0[:n1]) < 1e-5
+    assert not np.array_equal(g1[:n1], g0[:n1])              # a different kernel really ran (another summation order)
+    net.close()
