@@ -266,5 +266,6 @@ def test_picture_resident_input_gradient_equals_im2col_kernel(ctx, monkeypatch, 
     assert rel(g1, g0) < 1e-5
     n1 = 5 * 5 * 32 + 32
     assert rel(g1[:n1], g0[:n1]) < 1e-5
-    assert not np.array_equal(g1[:n1], g0[:n1])              # a different kernel really ran (another summation order)
+    if c2 > 32:        # two channel panels: panel-major summation differs from the im2col kernel's tap-major order in the last bits
+        assert not np.array_equal(g1[:n1], g0[:n1])          # (one panel: same order, same bits) -- the other kernel really ran
     net.close()
