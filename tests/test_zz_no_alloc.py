@@ -35,23 +35,21 @@ def test_noalloc_dense_matches_net_forward_twice(ctx):
     w = net.params[w_off:w_off + w_size]
     b = net.params[b_off:b_off + b_size]
     g = torch.Generator(device="cuda").manual_seed(3)
-    out = torch.empty((64, N), dtype=torch.float32, device="cuda")     # caller-owned output, allocated up front
+    outs = [torch.empty((64, N), dtype=torch.float32, device="cuda") for _ in range(2)]   # caller-owned outputs, allocated up front
     # inputs and the reference results of both calls first: torch's caching allocator and nc_net_forward (malloc'ed workspace)
     # may take device memory, and neither is what this test is about
     xs = [torch.randn((m, K), device="cuda", generator=g) for m in (64, 37)]          # two calls in a row; the second is smaller
     wants = [net.forward(x).clone() for x in xs]                                        # existing entry point
-    scratch = (xs[0][:1] - wants[0][:1, :1]).abs().max() / wants[0].abs().max()         # torch loads its own kernels lazily too
     torch.cuda.synchronize()
-    free_after_first = None
-    for x, want in zip(xs, wants):
+    _call(ctx, xs[0], w, b, outs[0])                     # new entry point (fixed scratch); the first call on a device does the
+    torch.cuda.synchronize()                             # one-time set-up (and CUDA loads the kernels lazily)
+    free_after_first = torch.cuda.mem_get_info()[0]
+    _call(ctx, xs[1], w, b, outs[1])
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free_after_first, "a later call changed free device memory"
+    for x, want, out in zip(xs, wants, outs):
         m = x.shape[0]
-        got = _call(ctx, x, w, b, out)[:m]               # new entry point (fixed scratch)
-        torch.cuda.synchronize()
-        if free_after_first is None:
-            # the first call on a device does the one-time set-up (and CUDA loads the kernels lazily)
-            free_after_first = torch.cuda.mem_get_info()[0]
-        else:
-            assert torch.cuda.mem_get_info()[0] == free_after_first, "a later call changed free device memory"
+        got = out[:m]
         err = float((got - want).abs().max() / want.abs().max())
         assert err < 2e-5, (m, err)                      # tolerance of the fp32 SIMT path (tests/test_net_gpu.py)
     # against float64 on the host as well
