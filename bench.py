@@ -430,20 +430,24 @@ def run_train_bench(torch, ctx, args, rank, world, device, peaks, dist_on, sampl
                 i = k["i"] % 4
                 k["i"] += 1
                 if graph is not None:
-                    graph.x.copy_(hx[i], non_blocking=True)
-                    graph.y.copy_(hy[i], non_blocking=True)
-                    graph.graph.replay()
-                    lh.copy_(graph.loss, non_blocking=True)
+                    # the public host-fed loop: step on the batch whose copy was started a step ago, start the next copy
+                    loss, _ = graph.run_prefetched()
+                    lh.copy_(loss, non_blocking=True)
+                    graph.prefetch(hx[i], hy[i])
                 else:
                     xd.copy_(hx[i], non_blocking=True)
                     yd.copy_(hy[i], non_blocking=True)
                     loss, _ = dp.train_step(xd, yd, "entropy", "compat")
                     lh.copy_(loss, non_blocking=True)
 
+            if graph is not None:
+                graph.prefetch(hx[3], hy[3])
             ms = max_over_ranks(torch, time_steps(torch, e2e, steps, 3, dist_on), dist_on, device)
             res["e2e"] = {"value": global_batch * steps / (ms * 1e-3), "unit": "images/s",
                           "h2d_bytes_per_step": world * local * (784 + 10) * 4, "d2h_bytes_per_step": 4 * world,
-                          "mode": "per rank: pinned host batch (pictures + labels) -> H2D -> graph replay of the step -> loss D2H"}
+                          "mode": "per rank, every step: H2D of one batch (pictures + labels) from pinned host memory on a copy stream -- the "
+                                  "batch of the NEXT step, in flight under this step (GraphedTrainStep.prefetch / run_prefetched) -> graph "
+                                  "replay of the step on the batch copied a step ago -> loss D2H"}
         del graph
         return res
 

@@ -280,6 +280,42 @@ class GraphedTrainStep:
         _lib.check(self.net.ctx.handle, _lib.lib().nc_net_advance_step(self.net.handle, 1))
         return self.loss, self.correct
 
+    # ---- batches that live in (pinned) host memory: the copy of batch i + 1 runs on a copy stream under the step on batch i
+    def prefetch(self, hx, hy):
+        """Start the host -> device copy of a coming batch (pinned CPU tensors [batch, features], [batch, classes]) on the
+        copy stream.  At most two batches may be in flight; run_prefetched() consumes them in order."""
+        dev = self.net.ctx.tdev
+        if getattr(self, "_copy", None) is None:
+            self._copy = torch.cuda.Stream(device=dev)
+            self._stage = [(torch.empty_like(self.x), torch.empty_like(self.y)) for _ in range(2)]
+            self._ready = [torch.cuda.Event(), torch.cuda.Event()]
+            self._free = [None, None]
+            self._fill, self._queue = 0, []
+        if len(self._queue) >= 2:
+            raise RuntimeError("two batches are already in flight: call run_prefetched() first")
+        slot = self._fill
+        self._fill ^= 1
+        if self._free[slot] is not None:
+            self._copy.wait_event(self._free[slot])          # the step that read this staging slot has copied it out
+        with torch.cuda.stream(self._copy):
+            self._stage[slot][0].copy_(hx.reshape(self.batch, -1), non_blocking=True)
+            self._stage[slot][1].copy_(hy.reshape(self.batch, -1), non_blocking=True)
+            self._ready[slot].record(self._copy)
+        self._queue.append(slot)
+
+    def run_prefetched(self):
+        """One step on the oldest prefetched batch; returns (loss, correct) device tensors like __call__."""
+        if not getattr(self, "_queue", None):
+            raise RuntimeError("no batch in flight: call prefetch(hx, hy) first")
+        slot = self._queue.pop(0)
+        main = torch.cuda.current_stream(self.net.ctx.tdev)
+        main.wait_event(self._ready[slot])
+        out = self(self._stage[slot][0], self._stage[slot][1])
+        if self._free[slot] is None:
+            self._free[slot] = torch.cuda.Event()
+        self._free[slot].record(main)
+        return out
+
 
 def find_libnccl():
     """Path of the NCCL this process should share with torch: the one already mapped if torch loaded it,

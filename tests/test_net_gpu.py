@@ -354,3 +354,29 @@ def test_graphed_train_step_equals_eager(ctx, opt, lr):
     with pytest.raises(ValueError):
         GraphedTrainStep(graphed, 64, "entropy", "adam", 1e-3)
     eager.close(); graphed.close()
+
+
+def test_host_fed_graphed_steps_equal_device_fed_ones(ctx):
+    """GraphedTrainStep.prefetch / run_prefetched: batches in pinned host memory, the copy of the next batch in flight on a copy
+    stream under the current step.  Same batches in the same order as device-fed replays: identical losses and weights; more
+    than two batches in flight, or a run without a prefetched batch, is refused."""
+    from cloud_server_b200.net import Net, GraphedTrainStep
+    rng = np.random.default_rng(13)
+    hx = [torch.from_numpy(rng.random((64, 784), dtype=np.float32)).pin_memory() for _ in range(5)]
+    hy = [torch.nn.functional.one_hot(torch.from_numpy(rng.integers(0, 10, 64)), 10).float().pin_memory() for _ in range(5)]
+    a, b = Net(tfref.LENET, ctx, seed=9), Net(tfref.LENET, ctx, seed=9)
+    sa, sb = GraphedTrainStep(a, 64, "entropy", "sgd", 0.01), GraphedTrainStep(b, 64, "entropy", "sgd", 0.01)
+    with pytest.raises(RuntimeError):
+        sb.run_prefetched()
+    sb.prefetch(hx[0], hy[0])
+    for i in range(5):
+        la, _ = sa(hx[i].cuda(), hy[i].cuda())
+        if i + 1 < 5:
+            sb.prefetch(hx[i + 1], hy[i + 1])            # two in flight
+            if i == 0:
+                with pytest.raises(RuntimeError):
+                    sb.prefetch(hx[0], hy[0])
+        lb, _ = sb.run_prefetched()
+        assert float(la.item()) == float(lb.item())
+    assert np.array_equal(a.get_params(), b.get_params()) and a.global_step == b.global_step == 5
+    a.close(); b.close()
