@@ -456,6 +456,8 @@ def run_train_bench(torch, ctx, args, rank, world, device, peaks, dist_on, sampl
     note("main line done; other train configurations")
     main.update(m)
     main["grad_exchange"] = "p2p" if getattr(dp, "p2p", False) else ("nccl" if world > 1 else None)
+    if getattr(dp, "p2p", False) and net.p2p_timed_out():
+        raise RuntimeError("the peer-memory gradient exchange gave up waiting for a rank: the timed steps are void")
     if world == 1:
         out["train_b256"] = bench_train(256, want_profile=True, want_e2e=True)       # C3
     else:

@@ -14,7 +14,7 @@
 //   phase 2   the last CTA to finish announces "chunk r is written" to every peer and waits for all peers' announcements, so
 //             the kernel ends only when this rank's whole bucket is summed and no peer still reads this rank's buffer
 // Sequence numbers live in device memory and are advanced by the kernel itself, so a CUDA graph that contains the launch can
-// be replayed.  Waits give up after ~2 s (a peer that never launches) and raise a device-side error flag instead of hanging.
+// be replayed.  Waits give up after ~20 s (a peer that never launches) and raise a device-side error flag instead of hanging.
 // TMA is not involved: these are ordinary ld / st to peer addresses.
 #include "nc_internal.h"
 
@@ -54,7 +54,7 @@ __device__ __forceinline__ bool wait_flags(const unsigned* flags, int n, unsigne
     if ((int)threadIdx.x < n) {
         const long long t0 = clock64();
         while ((int)(ld_acquire_sys(flags + threadIdx.x) - want) < 0) {
-            if (clock64() - t0 > 4000000000LL) { *err = 1; ok = false; break; }
+            if (clock64() - t0 > 40000000000LL) { *err = 1; ok = false; break; }     // ~20 s: far beyond any start-up skew between ranks
             __nanosleep(64);
         }
     }
@@ -210,7 +210,7 @@ int nc_p2p_allreduce(nc_ctx* ctx, nc_p2p* p, long long off, long long count, cud
     return NC_OK;
 }
 
-// 0 = fine, 1 = a wait gave up (a peer did not arrive within ~2 s); synchronises nothing: read after a stream synchronise
+// 0 = fine, 1 = a wait gave up (a peer did not arrive within ~20 s); synchronises nothing: read after a stream synchronise
 int nc_p2p_error(nc_ctx* ctx, nc_p2p* p, int* out) {
     *out = 0;
     if (!p || !p->flags) return NC_OK;

@@ -306,7 +306,7 @@ int nc_net_detach_nccl(nc_net* net);
  *   nc_net_p2p_handles  after nc_net_attach_nccl: 128 bytes = the CUDA IPC handles of this rank's gradient buffer and flag words
  *   nc_net_p2p_attach   all_handles = world x 128 bytes in rank order (gathered by the host through any channel); maps the
  *                       peers (NC_EUNSUPPORTED if two GPUs have no peer access: the net then keeps using NCCL)
- *   nc_net_p2p_status   *timed_out = 1 if a wait inside the kernel gave up (~2 s: a peer never launched its step)
+ *   nc_net_p2p_status   *timed_out = 1 if a wait inside the kernel gave up (~20 s: a peer never launched its step)
  * Every rank must call nc_net_train_step / nc_net_allreduce_grads in the same order, as with NCCL. */
 int nc_net_p2p_handles(nc_net* net, unsigned char out[128]);
 int nc_net_p2p_attach(nc_net* net, const unsigned char* all_handles, int rank, int world);
