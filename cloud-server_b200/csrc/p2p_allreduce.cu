@@ -161,6 +161,7 @@ int nc_p2p_export(nc_ctx* ctx, nc_p2p** pp, float* grads, unsigned char out[128]
 int nc_p2p_attach(nc_ctx* ctx, nc_p2p* p, float* grads, const unsigned char* all_handles, int rank, int world) {
     if (!p || !p->flags) return nc_set_error(ctx, NC_EINVAL, "nc_net_p2p_handles must be called first");
     if (world < 2 || world > kMaxRanks || rank < 0 || rank >= world) return nc_set_error(ctx, NC_EINVAL, "peer all-reduce takes 2..8 ranks");
+    if (p->ready || p->nmapped) return nc_set_error(ctx, NC_EINVAL, "the peers are already mapped (detach the communicator first)");
     p->ptrs.world = world; p->ptrs.rank = rank;
     for (int r = 0; r < world; ++r) {
         if (r == rank) { p->ptrs.g[r] = grads; p->ptrs.f[r] = p->flags; continue; }
@@ -172,6 +173,9 @@ int nc_p2p_attach(nc_ctx* ctx, nc_p2p* p, float* grads, const unsigned char* all
         if (e == cudaSuccess) e = cudaIpcOpenMemHandle(&f, hf, cudaIpcMemLazyEnablePeerAccess);
         if (e != cudaSuccess) {
             cudaGetLastError();
+            if (g) cudaIpcCloseMemHandle(g);
+            for (int i = 0; i < p->nmapped; ++i) cudaIpcCloseMemHandle(p->mapped[i]);      // leave nothing half-mapped behind
+            p->nmapped = 0;
             return nc_set_error(ctx, NC_EUNSUPPORTED, "cudaIpcOpenMemHandle(rank %d): %s (no peer access between these GPUs?)", r, cudaGetErrorString(e));
         }
         p->mapped[p->nmapped++] = g; p->mapped[p->nmapped++] = f;
