@@ -18,9 +18,13 @@ namespace {
 const unsigned char kZigzag[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
                                    35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
+// q95 pictures carry many large coefficients whose (run, size) codes are 10-16 bits long: with a 9-bit table a third of the symbols
+// fell through to the bit-by-bit search
+constexpr int kLook = 12;
+
 struct HuffTab {
     bool present = false;
-    unsigned char look_nbits[512], look_sym[512];   // 9-bit lookahead
+    unsigned char look_nbits[1 << kLook], look_sym[1 << kLook];   // lookahead table: codes of up to kLook bits in one step
     int maxcode[18];                                // largest code of each length (-1 if none), [17] = sentinel
     int valoffset[17];
     unsigned char vals[256];
@@ -63,10 +67,10 @@ bool build_hufftab(const unsigned char* counts, const unsigned char* syms, int n
     t->maxcode[17] = 0xFFFFF;
     memset(t->look_nbits, 0, sizeof(t->look_nbits));
     p = 0;
-    for (int l = 1; l <= 9; ++l)
+    for (int l = 1; l <= kLook; ++l)
         for (int i = 0; i < counts[l - 1]; ++i, ++p) {
-            const int look = huffcode[p] << (9 - l);
-            for (int c = 0; c < (1 << (9 - l)); ++c) { t->look_nbits[look + c] = (unsigned char)l; t->look_sym[look + c] = syms[p]; }
+            const int look = huffcode[p] << (kLook - l);
+            for (int c = 0; c < (1 << (kLook - l)); ++c) { t->look_nbits[look + c] = (unsigned char)l; t->look_sym[look + c] = syms[p]; }
         }
     memcpy(t->vals, syms, nsym);
     t->present = true;
@@ -163,9 +167,9 @@ int parse_header(const unsigned char* d, size_t n, Header* h, const char** msg) 
 
 struct BitReader {
     const unsigned char* p; const unsigned char* end;
-    unsigned long long acc = 0; int nbits = 0;
+    unsigned long long acc = 0; int nbits = 0;       // the low `nbits` bits of acc are unread data, oldest bit highest
     bool hit_marker = false;
-    inline void fill() {
+    inline void fill_bytes() {
         while (nbits <= 56) {
             unsigned b = 0;
             if (!hit_marker && p < end) {
@@ -180,18 +184,35 @@ struct BitReader {
             nbits += 8;
         }
     }
-    inline unsigned peek(int k) { if (nbits < k) fill(); return (unsigned)((acc >> (nbits - k)) & ((1u << k) - 1)); }
-    inline void drop(int k) { nbits -= k; }
-    inline unsigned get(int k) { const unsigned v = peek(k); nbits -= k; return v; }
-    inline int decode(const HuffTab& t) {
-        const unsigned look = peek(9);
+    // at least 57 bits afterwards.  Fast path: the next 8 bytes hold no 0xFF (no stuffing, no marker): take as many whole bytes
+    // as fit with one load and one byte swap
+    inline void fill() {
+        if (!hit_marker && p + 8 <= end) {
+            unsigned long long v;
+            memcpy(&v, p, 8);
+            const unsigned long long x = ~v;
+            if (!((x - 0x0101010101010101ull) & ~x & 0x8080808080808080ull)) {
+                const int nbytes = (64 - nbits) >> 3;
+                v = __builtin_bswap64(v);
+                acc = nbytes == 8 ? v : ((acc << (8 * nbytes)) | (v >> (64 - 8 * nbytes)));
+                p += nbytes; nbits += 8 * nbytes;
+                return;
+            }
+        }
+        fill_bytes();
+    }
+    // the *_nc forms assume the caller made sure enough bits are buffered (need32() covers one Huffman code + its value bits)
+    inline void need32() { if (nbits < 32) fill(); }
+    inline unsigned peek_nc(int k) const { return (unsigned)((acc >> (nbits - k)) & ((1u << k) - 1)); }
+    inline unsigned get_nc(int k) { nbits -= k; return (unsigned)((acc >> nbits) & ((1u << k) - 1)); }
+    inline int decode_nc(const HuffTab& t) {
+        const unsigned look = peek_nc(kLook);
         int nb = t.look_nbits[look];
-        if (nb) { drop(nb); return t.look_sym[look]; }
-        nb = 10;
-        if (nbits < 16) fill();
-        int code = (int)((acc >> (nbits - nb)) & ((1u << nb) - 1));
-        while (code > t.maxcode[nb]) { ++nb; if (nb > 16) return -1; code = (int)((acc >> (nbits - nb)) & ((1u << nb) - 1)); }
-        drop(nb);
+        if (nb) { nbits -= nb; return t.look_sym[look]; }
+        nb = kLook + 1;
+        int code = (int)peek_nc(nb);
+        while (code > t.maxcode[nb]) { ++nb; if (nb > 16) return -1; code = (int)peek_nc(nb); }
+        nbits -= nb;
         const int idx = code + t.valoffset[nb];
         return (idx >= 0 && idx < 256) ? t.vals[idx] : -1;
     }
@@ -233,11 +254,13 @@ void decode_one(const unsigned char* d, size_t n, int want_w, int want_h, Decode
     }
     out->mask.assign(nblocks, 0ull);
     out->off.assign(nblocks, 0u);
-    out->vals.clear();
-    out->vals.reserve(nblocks * 24);
+    out->vals.resize(nblocks * 64);              // worst case; shrunk to what was decoded at the end
+    short* const v0 = out->vals.data();
+    short* vp = v0;
     BitReader br{h.ecs, h.ecs + h.ecs_len};
     int pred[3] = {0, 0, 0};
     long long cnt = 0;
+#define NC_JPEG_FAIL(m_) do { out->vals.clear(); out->rc = NC_EINVAL; out->msg = m_; return; } while (0)
     // values are appended in DECODE order (MCU interleaved); every block records where its own run starts
     for (int my = 0; my < mcuy; ++my) {
         for (int mx = 0; mx < mcux; ++mx) {
@@ -250,22 +273,23 @@ void decode_one(const unsigned char* d, size_t n, int want_w, int want_h, Decode
                     for (int bx = 0; bx < h.comp[c].h; ++bx) {
                         const size_t b = base[c] + (size_t)(my * h.comp[c].v + by) * out->bw[c] + (mx * h.comp[c].h + bx);
                         unsigned long long m = 0;
-                        out->off[b] = (unsigned)out->vals.size();
-                        int s = br.decode(dct);
-                        if (s < 0 || s > 15) { out->rc = NC_EINVAL; out->msg = "corrupt Huffman data (DC)"; return; }
-                        if (s) pred[c] += extend(br.get(s), s);
-                        if (pred[c]) { m |= 1ull; out->vals.push_back((short)pred[c]); }
+                        out->off[b] = (unsigned)(vp - v0);
+                        br.need32();                          // one code (<= 16 bits) + its value bits (<= 15)
+                        int s = br.decode_nc(dct);
+                        if (s < 0 || s > 15) NC_JPEG_FAIL("corrupt Huffman data (DC)");
+                        if (s) pred[c] += extend(br.get_nc(s), s);
+                        if (pred[c]) { m |= 1ull; *vp++ = (short)pred[c]; }
                         for (int k = 1; k < 64;) {
-                            const int rs = br.decode(act);
-                            if (rs < 0) { out->rc = NC_EINVAL; out->msg = "corrupt Huffman data (AC)"; return; }
+                            br.need32();
+                            const int rs = br.decode_nc(act);
+                            if (rs < 0) NC_JPEG_FAIL("corrupt Huffman data (AC)");
                             const int r = rs >> 4;
                             s = rs & 15;
                             if (s == 0) { if (r == 15) { k += 16; continue; } break; }
                             k += r;
-                            if (k > 63) { out->rc = NC_EINVAL; out->msg = "corrupt Huffman data (run past the block)"; return; }
-                            const int v = extend(br.get(s), s);
+                            if (k > 63) NC_JPEG_FAIL("corrupt Huffman data (run past the block)");
                             m |= 1ull << k;
-                            out->vals.push_back((short)v);
+                            *vp++ = (short)extend(br.get_nc(s), s);
                             ++k;
                         }
                         out->mask[b] = m;
@@ -274,6 +298,8 @@ void decode_one(const unsigned char* d, size_t n, int want_w, int want_h, Decode
             }
         }
     }
+#undef NC_JPEG_FAIL
+    out->vals.resize((size_t)(vp - v0));
 }
 
 // ------------------------------------------------------------------------------------------------------------ device
