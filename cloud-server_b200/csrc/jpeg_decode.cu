@@ -300,6 +300,7 @@ void decode_one(const unsigned char* d, size_t n, int want_w, int want_h, Decode
     }
 #undef NC_JPEG_FAIL
     out->vals.resize((size_t)(vp - v0));
+    out->vals.shrink_to_fit();                   // a batch keeps every picture's values until they are packed: give the slack back
 }
 
 // ------------------------------------------------------------------------------------------------------------ device
