@@ -254,13 +254,16 @@ void decode_one(const unsigned char* d, size_t n, int want_w, int want_h, Decode
     }
     out->mask.assign(nblocks, 0ull);
     out->off.assign(nblocks, 0u);
-    out->vals.resize(nblocks * 64);              // worst case; shrunk to what was decoded at the end
-    short* const v0 = out->vals.data();
+    // decode into a per-thread scratch of the worst-case size (no capacity check per value, no zero fill per picture), then keep
+    // exactly what was decoded
+    static thread_local std::vector<short> scratch;
+    if (scratch.size() < nblocks * 64) scratch.resize(nblocks * 64);
+    short* const v0 = scratch.data();
     short* vp = v0;
     BitReader br{h.ecs, h.ecs + h.ecs_len};
     int pred[3] = {0, 0, 0};
     long long cnt = 0;
-#define NC_JPEG_FAIL(m_) do { out->vals.clear(); out->rc = NC_EINVAL; out->msg = m_; return; } while (0)
+#define NC_JPEG_FAIL(m_) do { out->rc = NC_EINVAL; out->msg = m_; return; } while (0)
     // values are appended in DECODE order (MCU interleaved); every block records where its own run starts
     for (int my = 0; my < mcuy; ++my) {
         for (int mx = 0; mx < mcux; ++mx) {
@@ -299,8 +302,7 @@ void decode_one(const unsigned char* d, size_t n, int want_w, int want_h, Decode
         }
     }
 #undef NC_JPEG_FAIL
-    out->vals.resize((size_t)(vp - v0));
-    out->vals.shrink_to_fit();                   // a batch keeps every picture's values until they are packed: give the slack back
+    out->vals.assign(v0, vp);
 }
 
 // ------------------------------------------------------------------------------------------------------------ device
