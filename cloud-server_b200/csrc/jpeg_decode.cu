@@ -28,6 +28,10 @@ struct HuffTab {
     int maxcode[18];                                // largest code of each length (-1 if none), [17] = sentinel
     int valoffset[17];
     unsigned char vals[256];
+    // AC tables: one load per coefficient where the code AND its value bits fit the lookahead.  Entry: bits 0-4 bits consumed,
+    // bit 5 'symbol only' (bits 8-15 = run << 4 | size, value bits follow in the stream), bit 6 'value included' (bits 8-11 run,
+    // bits 16-31 the extended coefficient); 0 = code longer than the lookahead
+    unsigned fast[1 << kLook];
 };
 
 struct Comp { int id = 0, h = 1, v = 1, tq = 0, td = 0, ta = 0; };
@@ -71,6 +75,22 @@ bool build_hufftab(const unsigned char* counts, const unsigned char* syms, int n
         for (int i = 0; i < counts[l - 1]; ++i, ++p) {
             const int look = huffcode[p] << (kLook - l);
             for (int c = 0; c < (1 << (kLook - l)); ++c) { t->look_nbits[look + c] = (unsigned char)l; t->look_sym[look + c] = syms[p]; }
+        }
+    memset(t->fast, 0, sizeof(t->fast));
+    p = 0;
+    for (int l = 1; l <= kLook; ++l)
+        for (int i = 0; i < counts[l - 1]; ++i, ++p) {
+            const int rs = syms[p], r = rs >> 4, sz = rs & 15;
+            const int rest = kLook - l;
+            for (int c = 0; c < (1 << rest); ++c) {
+                unsigned e = (unsigned)l | 0x20u | ((unsigned)rs << 8);
+                if (sz && sz <= rest) {
+                    const int bits = c >> (rest - sz);
+                    const int v = bits < (1 << (sz - 1)) ? bits - (1 << sz) + 1 : bits;
+                    e = (unsigned)(l + sz) | 0x40u | ((unsigned)r << 8) | ((unsigned)(v & 0xFFFF) << 16);
+                }
+                t->fast[(huffcode[p] << rest) + c] = e;
+            }
         }
     memcpy(t->vals, syms, nsym);
     t->present = true;
@@ -284,7 +304,19 @@ void decode_one(const unsigned char* d, size_t n, int want_w, int want_h, Decode
                         if (pred[c]) { m |= 1ull; *vp++ = (short)pred[c]; }
                         for (int k = 1; k < 64;) {
                             br.need32();
-                            const int rs = br.decode_nc(act);
+                            const unsigned e = act.fast[br.peek_nc(kLook)];
+                            if (e & 0x40u) {                       // code and value bits in one table entry
+                                br.nbits -= (int)(e & 31u);
+                                k += (int)((e >> 8) & 15u);
+                                if (k > 63) NC_JPEG_FAIL("corrupt Huffman data (run past the block)");
+                                m |= 1ull << k;
+                                *vp++ = (short)((int)e >> 16);
+                                ++k;
+                                continue;
+                            }
+                            int rs;
+                            if (e & 0x20u) { br.nbits -= (int)(e & 31u); rs = (int)((e >> 8) & 255u); }
+                            else rs = br.decode_nc(act);
                             if (rs < 0) NC_JPEG_FAIL("corrupt Huffman data (AC)");
                             const int r = rs >> 4;
                             s = rs & 15;
