@@ -1162,7 +1162,7 @@ extern "C" int nc_net_backward(nc_net* net, const float* x, const float* y_oneho
             }
             if (!done && smallc_tc_ok(net, L, W, d)) {
                 // first layer: dW[K][N] = col^T[K][M] . dY[M][N] on the tensor cores over an explicit im2col
-                int Kp;
+                int Kp = 0;
                 rc = smallc_im2col(net, L, n, in, st, &Kp);
                 if (rc != NC_OK) return rc;
                 rc = reserve_ws(net, nc_tc_gemm_workspace(sms, K, N, M, nullptr, nullptr));
